@@ -1,0 +1,152 @@
+// extern "C" surface of libfinito_b200.so (include/finito_b200.h).  Exceptions stop here.
+#include <cstring>
+#include <new>
+
+#include "engine.hpp"
+
+struct fin_index {
+    std::unique_ptr<fin::DeviceIndex> dev;
+};
+
+namespace {
+
+thread_local std::string g_error;
+
+template <class F> fin_status guarded(F&& f) {
+    try {
+        f();
+        g_error.clear();
+        return FIN_OK;
+    } catch (const fin::arg_error& e) { g_error = e.what(); return FIN_ERR_ARG;
+    } catch (const fin::io_error& e) { g_error = e.what(); return FIN_ERR_IO;
+    } catch (const fin::format_error& e) { g_error = e.what(); return FIN_ERR_FORMAT;
+    } catch (const fin::cuda_error& e) { g_error = e.what(); cudaGetLastError(); return FIN_ERR_CUDA;
+    } catch (const fin::domain_error& e) { g_error = e.what(); return FIN_ERR_DOMAIN;
+    } catch (const fin::limit_error& e) { g_error = e.what(); return FIN_ERR_LIMIT;
+    } catch (const std::bad_alloc&) { g_error = "out of host memory"; return FIN_ERR_IO;
+    } catch (const std::exception& e) { g_error = e.what(); return FIN_ERR_ARG; }
+}
+
+void require(bool ok, const char* what) {
+    if (!ok) throw fin::arg_error(what);
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* fin_last_error(void) { return g_error.c_str(); }
+
+int fin_abi_version(void) { return 1; }
+
+int fin_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+fin_status fin_index_load(const char* prefix, int device, fin_index** out) {
+    return guarded([&] {
+        require(prefix && out, "fin_index_load: null argument");
+        *out = nullptr;
+        fin::IndexHost host = fin::load_index_files(prefix);
+        std::unique_ptr<fin_index> h(new fin_index());
+        h->dev.reset(new fin::DeviceIndex(host, device));
+        *out = h.release();
+    });
+}
+
+void fin_index_free(fin_index* index) { delete index; }
+
+fin_status fin_index_info_get(const fin_index* index, fin_index_info* out) {
+    return guarded([&] {
+        require(index && out, "fin_index_info_get: null argument");
+        *out = index->dev->info();
+    });
+}
+
+uint64_t fin_count_kmers(const uint64_t* read_offsets, uint64_t n_reads, int64_t k) {
+    uint64_t total = 0;
+    if (!read_offsets || k < 1) return 0;
+    for (uint64_t i = 0; i < n_reads; i++) {
+        const uint64_t len = read_offsets[i + 1] - read_offsets[i];
+        if (len >= (uint64_t)k) total += len - (uint64_t)k + 1;
+    }
+    return total;
+}
+
+fin_status fin_search_batch(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
+                            int64_t* out_pairs, uint64_t out_capacity, fin_search_counts* counts) {
+    return guarded([&] {
+        require(index && read_offsets && (seqs || n_reads == 0) && (out_pairs || out_capacity == 0), "fin_search_batch: null argument");
+        index->dev->search_host<int64_t>(seqs, read_offsets, n_reads, out_pairs, out_capacity, counts);
+    });
+}
+
+fin_status fin_search_batch32(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
+                              int32_t* out_pairs, uint64_t out_capacity, fin_search_counts* counts) {
+    return guarded([&] {
+        require(index && read_offsets && (seqs || n_reads == 0) && (out_pairs || out_capacity == 0), "fin_search_batch32: null argument");
+        index->dev->search_host<int32_t>(seqs, read_offsets, n_reads, out_pairs, out_capacity, counts);
+    });
+}
+
+fin_status fin_search_device(fin_index* index, const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads,
+                             uint64_t n_bases, uint64_t total_kmers, void* d_out, int hit_bytes, fin_search_counts* counts,
+                             float* kernel_ms) {
+    return guarded([&] {
+        require(index && d_read_offsets && (d_seqs || n_bases == 0) && (d_out || total_kmers == 0), "fin_search_device: null argument");
+        index->dev->search_device(d_seqs, d_read_offsets, n_reads, n_bases, total_kmers, d_out, hit_bytes, counts, kernel_ms);
+    });
+}
+
+fin_status fin_search_access_counters(const fin_index* index, fin_access_counters* out) {
+    return guarded([&] {
+        require(index && out, "fin_search_access_counters: null argument");
+        *out = index->dev->last_access;
+    });
+}
+
+uint64_t fin_launch_count(void) { return fin::g_launches; }
+
+fin_status fin_host_alloc(size_t bytes, void** out) {
+    return guarded([&] {
+        require(out != nullptr, "fin_host_alloc: null argument");
+        *out = nullptr;
+        FIN_CUDA(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+    });
+}
+
+void fin_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
+fin_status fin_build(const char* sbwt_path, const char* unitig_path, const char* out_prefix, const char* type, int64_t t,
+                     const char* lcs_path, int device, char* stats_out, size_t stats_cap) {
+    return guarded([&] {
+        require(sbwt_path && unitig_path && out_prefix && type, "fin_build: null argument");
+        const std::string stats =
+            fin::build_fmin_device(sbwt_path, unitig_path, out_prefix, type, t, lcs_path ? lcs_path : "", device);
+        if (stats_out && stats_cap) {
+            strncpy(stats_out, stats.c_str(), stats_cap - 1);
+            stats_out[stats_cap - 1] = 0;
+        }
+    });
+}
+
+fin_status fin_lcs(const char* sbwt_path, int with_variant_header, int device, uint8_t* out, uint64_t out_capacity,
+                   uint64_t* n_nodes) {
+    return guarded([&] {
+        require(sbwt_path && out, "fin_lcs: null argument");
+        fin::SbwtHost s = fin::load_sbwt_file(sbwt_path, with_variant_header != 0);
+        if (n_nodes) *n_nodes = (uint64_t)s.n_nodes;
+        require((uint64_t)s.n_nodes <= out_capacity, "fin_lcs: output buffer too small");
+        std::vector<uint8_t> l = fin::lcs_device(s, device);
+        memcpy(out, l.data(), (size_t)s.n_nodes);
+    });
+}
+
+}  // extern "C"

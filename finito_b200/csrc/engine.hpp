@@ -1,0 +1,104 @@
+// Host-side engine objects behind the C ABI (include/finito_b200.h).
+#pragma once
+#include <cstdint>
+#include <memory>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+
+#include "device_index.cuh"
+#include "formats.hpp"
+#include "../../include/finito_b200.h"
+
+namespace fin {
+
+struct cuda_error : std::runtime_error { using std::runtime_error::runtime_error; };
+
+#define FIN_CUDA(expr)                                                                                         \
+    do {                                                                                                       \
+        cudaError_t _e = (expr);                                                                               \
+        if (_e != cudaSuccess)                                                                                 \
+            throw ::fin::cuda_error(std::string(#expr) + ": " + cudaGetErrorString(_e) + " (" + __FILE__ + ":" + \
+                                    std::to_string(__LINE__) + ")");                                           \
+    } while (0)
+
+extern thread_local uint64_t g_launches;  // kernels launched by this library on this thread
+
+// RAII device allocation
+template <class T> struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    DevBuf() {}
+    explicit DevBuf(size_t count) { alloc(count); }
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept : p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept {
+        if (this != &o) { release(); p = o.p; n = o.n; o.p = nullptr; o.n = 0; }
+        return *this;
+    }
+    ~DevBuf() { release(); }
+    void alloc(size_t count) {
+        release();
+        n = count;
+        if (count) FIN_CUDA(cudaMalloc((void**)&p, count * sizeof(T)));
+    }
+    void ensure(size_t count) { if (count > n) alloc(count); }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    size_t bytes() const { return n * sizeof(T); }
+};
+
+// 32-byte rank sectors {ones before block, 3 words} over a bit vector; `rows` interleaved rows per block.
+// rows[r] points at the words of row r (at least ceil(n_bits/64) words).  Returns 4*rows u64 per block for
+// n_bits/192 + 1 blocks, so rank(n_bits) is addressable.
+std::vector<uint64_t> make_rank_sectors(const uint64_t* const* rows, int n_rows, uint64_t n_bits, uint64_t* totals);
+
+// The seven files of a FinimizerIndex as the reference holds them in memory (FinimizerIndex.hh:108-115)
+struct IndexHost {
+    SbwtHost sbwt;
+    PackedVec lcs, fmin, offsets, text, ends, ustart;
+};
+IndexHost load_index_files(const std::string& prefix);
+void save_index_files(const IndexHost& ix, const std::string& prefix);
+
+struct SearchSlot;  // per-stream staging buffers of the batch pipeline
+
+class DeviceIndex {
+   public:
+    DeviceIndex(const IndexHost& host, int device);
+    ~DeviceIndex();
+    const IndexView& view() const { return view_; }
+    int device() const { return device_; }
+    fin_index_info info() const { return info_; }
+    bool fits_hit32() const { return fits32_; }
+
+    // search_fmin.hh:43-72 for a batch in host memory / in device memory
+    template <class HitT>
+    void search_host(const char* seqs, const uint64_t* read_offsets, uint64_t n_reads, HitT* out_pairs, uint64_t out_capacity,
+                     fin_search_counts* counts);
+    void search_device(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases,
+                       uint64_t total_kmers, void* d_out, int hit_bytes, fin_search_counts* counts, float* kernel_ms);
+    fin_access_counters last_access{};
+    bool count_accesses = false;
+
+   private:
+    int device_;
+    IndexView view_{};
+    fin_index_info info_{};
+    bool fits32_ = true;
+    DevBuf<uint64_t> matrix_, ustart_, fmin_, tstart_, text_;
+    DevBuf<uint8_t> lcs_;
+    DevBuf<uint32_t> offsets_, ends_;
+    std::vector<std::unique_ptr<SearchSlot>> slots_;
+    // scratch of search_device
+    DevBuf<uint64_t> dev_packed_, dev_out_offsets_;
+    DevBuf<uint8_t> dev_scan_tmp_;
+    DevBuf<uint8_t> dev_totals_;
+};
+
+// build-fmin on the device (build.cu)
+std::string build_fmin_device(const std::string& sbwt_path, const std::string& unitig_path, const std::string& out_prefix,
+                              const std::string& type, int64_t t, const std::string& lcs_path, int device);
+std::vector<uint8_t> lcs_device(const SbwtHost& sbwt, int device);
+
+}  // namespace fin

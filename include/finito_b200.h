@@ -1,0 +1,147 @@
+/*
+ * finito_b200 — C ABI of the B200-native finimizer hot path.
+ *
+ * The reference (ElenaBiagi/Finito @ ae6e702) has no FFI; the path sits behind its C++ object API
+ * and its two CLI commands.  Each entry point below replaces one reference interface, batched so
+ * that one call keeps a whole GPU busy.  Reference citations are file:line under the reference root.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; the caller owns every buffer it passes in, the library owns
+ *     device memory behind the opaque handles;
+ *   - every function returns fin_status; on failure fin_last_error() (thread local) says why;
+ *   - no exception crosses this boundary, no CPU fallback exists: without a usable CUDA device every
+ *     compute entry point returns FIN_ERR_CUDA;
+ *   - a handle is bound to one CUDA device; one host thread drives one handle at a time.
+ */
+#ifndef FINITO_B200_H
+#define FINITO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum fin_status {
+    FIN_OK = 0,
+    FIN_ERR_ARG = 1,     /* bad argument (null pointer, capacity too small, unknown type string) */
+    FIN_ERR_IO = 2,      /* file missing / truncated / not writable */
+    FIN_ERR_FORMAT = 3,  /* file is not what the reference would have written (variant, version) */
+    FIN_ERR_CUDA = 4,    /* CUDA runtime failure or no device */
+    FIN_ERR_DOMAIN = 5,  /* input outside the parity domain: non-ACGT base, unitig < k ... */
+    FIN_ERR_LIMIT = 6    /* index too large for the index width this build supports */
+} fin_status;
+
+/* Thread-local message of the last failing call on this thread ("" if none). */
+const char* fin_last_error(void);
+
+/* ABI version of this header (bumped on any signature change). */
+int fin_abi_version(void);
+
+/* Number of visible CUDA devices (0 when there is none; never fails). */
+int fin_device_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * FinimizerIndex  (include/FinimizerIndex.hh:108-115 members, :209-241 load)
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct fin_index fin_index;
+
+typedef struct fin_index_info {
+    int64_t k;             /* sbwt->get_k() */
+    int64_t n_nodes;       /* sbwt->number_of_subsets() */
+    int64_t n_kmers;       /* sbwt->number_of_kmers() */
+    int64_t n_unitigs;     /* unitigs.ends.size() */
+    int64_t text_len;      /* unitigs.concat.size() */
+    int64_t n_finimizers;  /* global_offsets.size() */
+    int64_t device_bytes;  /* bytes of HBM held by the device layout */
+    int64_t device;        /* CUDA device ordinal */
+} fin_index_info;
+
+/* FinimizerIndex::load(prefix) (FinimizerIndex.hh:209-241): reads <prefix>.{LCS,FBV,O,packed_unitigs,
+ * unitig_endpoints,Ustart}.sdsl and <prefix>.sbwt, re-lays them out for the device and uploads them
+ * to CUDA device `device`. */
+fin_status fin_index_load(const char* prefix, int device, fin_index** out);
+void fin_index_free(fin_index* index);
+fin_status fin_index_info_get(const fin_index* index, fin_index_info* out);
+
+/* ------------------------------------------------------------------------------------------------
+ * search-fmin  (include/search_fmin.hh:43-72 = per read: FinimizerIndex::search(read),
+ * FinimizerIndex::search(reverse complement), merge; FinimizerIndex.hh:119-185; common.hh:78-186)
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct fin_search_counts {
+    int64_t found_fwd;     /* sum of QueryResult::n_found over the forward searches   (search_fmin.hh:66) */
+    int64_t found_rc;      /* ... over the reverse-complement searches                (search_fmin.hh:67) */
+    int64_t positive;      /* merged k-mer positions with a hit                       (search_fmin.hh:58) */
+    int64_t n_queries;     /* k-mer positions answered = sum max(0, len-k+1)          (search_fmin.hh:69) */
+} fin_search_counts;
+
+/* Number of k-mer positions of a batch: sum over reads of max(0, len - k + 1).  Pure host arithmetic. */
+uint64_t fin_count_kmers(const uint64_t* read_offsets, uint64_t n_reads, int64_t k);
+
+/* One batch of reads, HOST buffers.  `seqs` holds the reads back to back (ASCII, upper or lower case
+ * ACGT, no separators), read i = seqs[read_offsets[i] .. read_offsets[i+1]).  `out_pairs` receives,
+ * read after read, one (unitig id, offset) pair per k-mer position, (-1,-1) where neither strand has
+ * the k-mer — exactly the numbers search-fmin prints (search_fmin.hh:54-65).  `out_capacity` is in
+ * pairs and must be >= fin_count_kmers().  The call copies the reads to the device, runs the
+ * kernels and copies the hits back (pipelined in sub-batches); it returns when `out_pairs` is complete.
+ * A non-ACGT character gives FIN_ERR_DOMAIN (the reference has undefined behaviour there,
+ * common.hh:108-111).  Pinned host buffers (fin_host_alloc) make the copies asynchronous. */
+fin_status fin_search_batch(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
+                            int64_t* out_pairs, uint64_t out_capacity, fin_search_counts* counts);
+
+/* Same, 2 x int32 per k-mer position (halves the device->host traffic).  FIN_ERR_LIMIT if a unitig id
+ * or offset of this index cannot be represented. */
+fin_status fin_search_batch32(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
+                              int32_t* out_pairs, uint64_t out_capacity, fin_search_counts* counts);
+
+/* Same computation on buffers that already live on the index's device (used to time the kernels
+ * without the PCIe copies).  d_seqs: ASCII reads; d_read_offsets: n_reads+1 offsets; d_out: 2 x int32
+ * (hit_bytes == 4) or 2 x int64 (hit_bytes == 8) per k-mer position; total_kmers = fin_count_kmers of
+ * the batch (the caller knows it from the host copy of the offsets).  Synchronous: returns after the
+ * kernels have finished.  kernel_ms (may be NULL) receives the CUDA-event time of the kernels. */
+fin_status fin_search_device(fin_index* index, const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads,
+                             uint64_t n_bases, uint64_t total_kmers, void* d_out, int hit_bytes,
+                             fin_search_counts* counts, float* kernel_ms);
+
+/* Access counters of the last search call on this handle, the ones SURVEY.md section 8(d) builds the
+ * algorithmic-bytes figure from (only filled by a library built with -DFIN_COUNTERS=1, else zeros). */
+typedef struct fin_access_counters {
+    int64_t n_rank, n_lcs_reads, n_ustart_reads, n_anchor, n_anchor_branch, n_walk_words, n_bases, n_kmers;
+} fin_access_counters;
+fin_status fin_search_access_counters(const fin_index* index, fin_access_counters* out);
+
+/* Number of kernel launches issued by this library on this thread's handles since load (bench.py's
+ * gpu_launches claim is read from here). */
+uint64_t fin_launch_count(void);
+
+/* Pinned host memory for the batch buffers (cudaHostAlloc / cudaFreeHost). */
+fin_status fin_host_alloc(size_t bytes, void** out);
+void fin_host_free(void* p);
+
+/* ------------------------------------------------------------------------------------------------
+ * build-fmin  (include/build_fmin.hh:302-401 driver; FinimizerIndex.hh:273-389 builder;
+ * lcs_basic_parallel_algorithm.hpp:52-120; PackedStrings.hh:104-137)
+ * ---------------------------------------------------------------------------------------------- */
+
+/* build-fmin -i sbwt_path -u unitig_path -o out_prefix --type type -t t [--lcs lcs_path].
+ *   sbwt_path : plain-matrix .sbwt as written by `sbwt build` (with the variant string).
+ *   unitig_path: FASTA/FASTQ (optionally .gz) or a .txt list of such files (build_fmin.hh:338).
+ *   type      : "rarest" | "shortest" | "verify" (build_fmin.hh:367-371).  rarest with t != 1 fails
+ *               with the reference's message (build_fmin.hh:245-247).
+ *   lcs_path  : NULL or "" = compute the LCS on the device and write <out_prefix>.LCS.sdsl
+ *               (build_fmin.hh:373-380).
+ * rarest writes the seven index files byte-identical to the reference's; every type appends
+ * "<t>,<stats>\n" to <out_prefix>_stats.txt (build_fmin.hh:386-395).  stats_out (may be NULL)
+ * receives <stats>. */
+fin_status fin_build(const char* sbwt_path, const char* unitig_path, const char* out_prefix, const char* type,
+                     int64_t t, const char* lcs_path, int device, char* stats_out, size_t stats_cap);
+
+/* LCS array only (lcs_basic_parallel_algorithm.hpp:52-120) as one byte per SBWT column. */
+fin_status fin_lcs(const char* sbwt_path, int with_variant_header, int device, uint8_t* out, uint64_t out_capacity,
+                   uint64_t* n_nodes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FINITO_B200_H */
