@@ -1,0 +1,231 @@
+"""finito_b200 — ctypes binding of the C ABI in include/finito_b200.h.
+
+The product is the CUDA library ``finito_b200/lib/libfinito_b200.so`` (built by
+``__graft_entry__.build()`` / ``make -C finito_b200/csrc``) and the ``finito_b200`` CLI next to it.
+This module only mirrors the reference's object API (``FinimizerIndex::load`` / ``search``,
+include/FinimizerIndex.hh:119,209 and the ``build-fmin`` driver, include/build_fmin.hh:302) on top of
+those entry points so that tests and ``bench.py`` can call them.  There is no Python or CPU
+implementation behind it: if the library is missing, or no CUDA device is visible, calls fail loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libfinito_b200.so")
+CLI_PATH = os.path.join(_HERE, "lib", "finito_b200")
+
+
+class FinitoError(RuntimeError):
+    def __init__(self, status: int, message: str):
+        super().__init__(f"[fin_status {status}] {message}")
+        self.status = status
+        self.message = message
+
+
+FIN_OK, FIN_ERR_ARG, FIN_ERR_IO, FIN_ERR_FORMAT, FIN_ERR_CUDA, FIN_ERR_DOMAIN, FIN_ERR_LIMIT = range(7)
+
+
+class _Info(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in
+                ("k", "n_nodes", "n_kmers", "n_unitigs", "text_len", "n_finimizers", "device_bytes", "device")]
+
+
+class _Counts(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("found_fwd", "found_rc", "positive", "n_queries")]
+
+
+class _Access(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in
+                ("n_rank", "n_lcs_reads", "n_ustart_reads", "n_anchor", "n_anchor_branch", "n_walk_words", "n_bases",
+                 "n_kmers")]
+
+
+# every symbol include/finito_b200.h declares: name -> (restype, argtypes)
+_u64p = C.POINTER(C.c_uint64)
+ABI = {
+    "fin_last_error": (C.c_char_p, []),
+    "fin_abi_version": (C.c_int, []),
+    "fin_device_count": (C.c_int, []),
+    "fin_index_load": (C.c_int, [C.c_char_p, C.c_int, C.POINTER(C.c_void_p)]),
+    "fin_index_free": (None, [C.c_void_p]),
+    "fin_index_info_get": (C.c_int, [C.c_void_p, C.POINTER(_Info)]),
+    "fin_count_kmers": (C.c_uint64, [C.c_void_p, C.c_uint64, C.c_int64]),
+    "fin_search_batch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                   C.POINTER(_Counts)]),
+    "fin_search_forward": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                     C.POINTER(_Counts)]),
+    "fin_search_batch32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                     C.POINTER(_Counts)]),
+    "fin_search_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p,
+                                    C.c_int, C.POINTER(_Counts), C.POINTER(C.c_float)]),
+    "fin_search_access_counters": (C.c_int, [C.c_void_p, C.POINTER(_Access)]),
+    "fin_launch_count": (C.c_uint64, []),
+    "fin_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
+    "fin_host_free": (None, [C.c_void_p]),
+    "fin_build": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int, C.c_char_p,
+                            C.c_size_t]),
+    "fin_lcs": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, _u64p]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load libfinito_b200.so (once) and declare every entry point.  Raises if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FinitoError(FIN_ERR_IO, f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                                          "or `make -C finito_b200/csrc` (there is no fallback implementation)")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in ABI.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def _check(status: int) -> None:
+    if status != FIN_OK:
+        raise FinitoError(status, lib().fin_last_error().decode("utf-8", "replace"))
+
+
+def device_count() -> int:
+    return int(lib().fin_device_count())
+
+
+def launch_count() -> int:
+    return int(lib().fin_launch_count())
+
+
+def _as_batch(reads):
+    """list of str/bytes, or (uint8 array, uint64 offsets) -> (uint8 array, uint64 offsets)."""
+    if isinstance(reads, tuple):
+        seqs, offs = reads
+        return np.ascontiguousarray(seqs, dtype=np.uint8), np.ascontiguousarray(offs, dtype=np.uint64)
+    bs = [r.encode() if isinstance(r, str) else bytes(r) for r in reads]
+    offs = np.zeros(len(bs) + 1, dtype=np.uint64)
+    if bs:
+        offs[1:] = np.cumsum([len(b) for b in bs], dtype=np.uint64)
+    seqs = np.frombuffer(b"".join(bs), dtype=np.uint8) if bs else np.zeros(0, dtype=np.uint8)
+    return seqs, offs
+
+
+@dataclass
+class SearchCounts:
+    found_fwd: int
+    found_rc: int
+    positive: int
+    n_queries: int
+
+
+class FinimizerIndex:
+    """FinimizerIndex on one CUDA device (include/FinimizerIndex.hh:105-241)."""
+
+    def __init__(self, handle: int):
+        self._h = C.c_void_p(handle)
+
+    @classmethod
+    def load(cls, prefix: str, device: int = 0) -> "FinimizerIndex":
+        out = C.c_void_p()
+        _check(lib().fin_index_load(os.fsencode(prefix), device, C.byref(out)))
+        return cls(out.value)
+
+    def close(self) -> None:
+        if self._h:
+            lib().fin_index_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    @property
+    def info(self) -> dict:
+        i = _Info()
+        _check(lib().fin_index_info_get(self._h, C.byref(i)))
+        return {n: int(getattr(i, n)) for n, _ in _Info._fields_}
+
+    def search_batch(self, reads, hit_bits: int = 64, out: np.ndarray | None = None, forward_only: bool = False):
+        """search-fmin for a batch: (hits[n_kmers, 2], SearchCounts); hits are (unitig, offset) or (-1, -1)."""
+        seqs, offs = _as_batch(reads)
+        n = len(offs) - 1
+        k = self.info["k"]
+        total = int(lib().fin_count_kmers(offs.ctypes.data, n, k))
+        dtype = np.int64 if hit_bits == 64 else np.int32
+        if out is None:
+            out = np.empty((total, 2), dtype=dtype)
+        assert out.dtype == dtype and out.size >= 2 * total and out.flags.c_contiguous
+        c = _Counts()
+        fn = lib().fin_search_batch if hit_bits == 64 else lib().fin_search_batch32
+        if forward_only:
+            assert hit_bits == 64
+            fn = lib().fin_search_forward
+        _check(fn(self._h, seqs.ctypes.data, offs.ctypes.data, n, out.ctypes.data, out.size // 2, C.byref(c)))
+        return out[:total], SearchCounts(c.found_fwd, c.found_rc, c.positive, c.n_queries)
+
+    def search(self, query: str):
+        """FinimizerIndex::search(query): forward strand only (include/FinimizerIndex.hh:119-185)."""
+        hits, _ = self.search_batch([query], forward_only=True)
+        return [tuple(int(x) for x in row) for row in hits]
+
+    def search_both_strands(self, query: str):
+        """One query, both strands merged — what search-fmin prints for it (include/search_fmin.hh:43-65)."""
+        hits, _ = self.search_batch([query])
+        return [tuple(int(x) for x in row) for row in hits]
+
+    def search_device(self, d_seqs: int, d_offsets: int, n_reads: int, n_bases: int, total_kmers: int, d_out: int,
+                      hit_bytes: int = 4):
+        """Same on device-resident buffers (raw device pointers); returns (SearchCounts, kernel milliseconds)."""
+        c = _Counts()
+        ms = C.c_float()
+        _check(lib().fin_search_device(self._h, d_seqs, d_offsets, n_reads, n_bases, total_kmers, d_out, hit_bytes,
+                                       C.byref(c), C.byref(ms)))
+        return SearchCounts(c.found_fwd, c.found_rc, c.positive, c.n_queries), float(ms.value)
+
+    def access_counters(self) -> dict:
+        a = _Access()
+        _check(lib().fin_search_access_counters(self._h, C.byref(a)))
+        return {n: int(getattr(a, n)) for n, _ in _Access._fields_}
+
+
+def build_fmin(sbwt_path: str, unitig_path: str, out_prefix: str, type: str = "rarest", t: int = 1,
+               lcs_path: str | None = None, device: int = 0) -> str:
+    """build-fmin (include/build_fmin.hh:302-401); returns the stats string (empty for rarest)."""
+    buf = C.create_string_buffer(512)
+    _check(lib().fin_build(os.fsencode(sbwt_path), os.fsencode(unitig_path), os.fsencode(out_prefix), type.encode(), t,
+                           os.fsencode(lcs_path) if lcs_path else None, device, buf, len(buf)))
+    return buf.value.decode()
+
+
+def lcs_array(sbwt_path: str, with_variant_header: bool = True, device: int = 0) -> np.ndarray:
+    """LCS bytes of an SBWT file (include/lcs_basic_parallel_algorithm.hpp:52-120)."""
+    n = C.c_uint64()
+    cap = max(1, os.path.getsize(sbwt_path) * 2)  # 4 bit rows of n bits each: n < 2 * file bytes
+    out = np.empty(cap, dtype=np.uint8)
+    _check(lib().fin_lcs(os.fsencode(sbwt_path), int(with_variant_header), device, out.ctypes.data, cap, C.byref(n)))
+    return out[: n.value].copy()
+
+
+def format_hits(hits: np.ndarray, kmers_per_read) -> str:
+    """Text of search-fmin's output file for already computed hits (include/search_fmin.hh:54-65)."""
+    lines, pos = [], 0
+    for n in kmers_per_read:
+        rows = hits[pos:pos + n]
+        lines.append(" ".join(f"({int(u)},{int(p)})" for u, p in rows))
+        pos += n
+    return "\n".join(lines) + ("\n" if lines else "")

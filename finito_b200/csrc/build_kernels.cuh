@@ -1,0 +1,248 @@
+// Kernels of the build-fmin path.  The per-thread bodies are FIN_D functions so that tests/emu can run the
+// same source on the host; build.cu holds the host driver.
+//   lcs_round_kernel     : one round of the label-propagation LCS algorithm — update + propagate fused
+//                          (include/lcs_basic_parallel_algorithm.hpp:10-27, rounds :80-109)
+//   first_kmer_kernel    : SBWT column of every unitig's first k-mer = colex sort key and Ustart mark
+//                          (include/PackedStrings.hh:104-137, SBWT.hh:320-347)
+//   build_stream_kernel  : FinimizerIndexBuilder::add_sequence (include/FinimizerIndex.hh:321-389) over chunks
+//                          of unitigs; the order-dependent overwrite rule (:370-378) becomes one atomicMax
+#pragma once
+#include "search_kernels.cuh"
+#include "build_host.hpp"  // BuildChunk
+
+namespace fin {
+
+#ifdef FIN_EMU
+inline void fin_atomic_max(unsigned long long* p, unsigned long long v) { if (*p < v) *p = v; }
+inline void fin_atomic_or(unsigned int* p, unsigned int v) { *p |= v; }
+#else
+FIN_D void fin_atomic_max(unsigned long long* p, unsigned long long v) { atomicMax(p, v); }
+FIN_D void fin_atomic_or(unsigned int* p, unsigned int v) { atomicOr(p, v); }
+#endif
+
+// =====================================================================================================
+// B1  LCS
+// =====================================================================================================
+struct LcsArgs {
+    const uint64_t* __restrict__ rows;      // rows[c * n_words + w]: word w of row c, bits past n cleared
+    const uint32_t* __restrict__ word_dst;  // word_dst[c * n_words + w] = rank_c(64 w)
+    uint64_t n, n_words;
+    uint32_t C[4];
+    uint8_t k;
+};
+
+// first column from the C array (lcs_basic_parallel_algorithm.hpp:29-50): 0 = '$', 1..4 = A,C,G,T
+FIN_D uint8_t lcs_first_column(const LcsArgs& a, uint64_t i) {
+    return i < a.C[0] ? 0 : i < a.C[1] ? 1 : i < a.C[2] ? 2 : i < a.C[3] ? 3 : 4;
+}
+
+// One thread owns 64 consecutive columns (one word of each row).
+//   update   : lcs[i] = round where still unset (== k) and last[i] != last[i-1]     (:21-27)
+//   propagate: next[C[c] + rank_c(i)] = last[i] for every set bit (i, c)            (:10-19)
+// The edges of a word land on consecutive bytes of `next`.  All three byte arrays are padded to
+// 64 * n_words + 64 bytes, so the whole-word vector accesses stay in bounds.
+FIN_D void lcs_round_word(const LcsArgs& a, const uint8_t* __restrict__ last, uint8_t* __restrict__ next,
+                          uint8_t* __restrict__ lcs, const uint64_t w, const uint8_t round) {
+    const uint64_t i0 = w * 64;
+    if (w == 0) next[0] = 0;  // the root has no incoming edge (:86)
+    uint32_t lv[16], cv[16];
+    {
+        const uint4* lp = reinterpret_cast<const uint4*>(last + i0);
+        const uint4* cp = reinterpret_cast<const uint4*>(lcs + i0);
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint4 x = lp[q], y = cp[q];
+            lv[4 * q] = x.x; lv[4 * q + 1] = x.y; lv[4 * q + 2] = x.z; lv[4 * q + 3] = x.w;
+            cv[4 * q] = y.x; cv[4 * q + 1] = y.y; cv[4 * q + 2] = y.z; cv[4 * q + 3] = y.w;
+        }
+    }
+    uint32_t prev = i0 ? last[i0 - 1] : 0xFFu;  // column 0 always differs from its (absent) predecessor
+    bool changed = false;
+#pragma unroll
+    for (int j = 0; j < 16; j++) {
+#pragma unroll
+        for (int b = 0; b < 4; b++) {
+            const uint32_t ch = (lv[j] >> (8 * b)) & 0xFFu;
+            const uint32_t cur = (cv[j] >> (8 * b)) & 0xFFu;
+            if (cur == a.k && ch != prev && i0 + 4 * j + b < a.n) {
+                cv[j] = (cv[j] & ~(0xFFu << (8 * b))) | ((uint32_t)round << (8 * b));
+                changed = true;
+            }
+            prev = ch;
+        }
+    }
+    if (changed) {
+        uint4* cp = reinterpret_cast<uint4*>(lcs + i0);
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            uint4 y;
+            y.x = cv[4 * q]; y.y = cv[4 * q + 1]; y.z = cv[4 * q + 2]; y.w = cv[4 * q + 3];
+            cp[q] = y;
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const uint64_t bits = a.rows[(uint64_t)c * a.n_words + w];
+        if (!bits) continue;
+        uint8_t* dst = next + a.C[c] + a.word_dst[(uint64_t)c * a.n_words + w];
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                if ((bits >> (4 * j + b)) & 1ULL) *dst++ = (uint8_t)((lv[j] >> (8 * b)) & 0xFFu);
+            }
+        }
+    }
+}
+
+// =====================================================================================================
+// B2  first k-mer of every unitig -> SBWT column
+// =====================================================================================================
+FIN_D int text_base(const uint64_t* __restrict__ text, uint64_t pos) {
+    return (int)((__ldg(text + (pos >> 5)) >> (2 * (pos & 31))) & 3);
+}
+
+// column of text[s .. s+k), 0xFFFFFFFF when the k-mer is not a single SBWT column (SBWT.hh:320-347)
+FIN_D uint32_t first_kmer_column(const IndexView& ix, const uint64_t* __restrict__ text, const uint64_t s) {
+    Ival I{0, ix.n_nodes - 1};
+    for (int i = 0; i < ix.k && !is_empty(I); i++) I = extend(ix, I, text_base(text, s + (uint64_t)i));
+    return (!is_empty(I) && I.l == I.r) ? I.l : 0xFFFFFFFFu;
+}
+
+// =====================================================================================================
+// B3  add_sequence over chunks of unitigs
+// =====================================================================================================
+
+// table[colex]: 0 = unset; (end_local << 32) | (0xFFFFFFFF - global_off) for end_local > 0; global_off + 1 otherwise.
+// A max over it is the closed form of the overwrite rule (FinimizerIndex.hh:370-378): the winner is the
+// first event (= smallest global offset) among those with the largest unitig-local end, and with all ends
+// equal to 0 — where the reference's "0 means unset" makes every event overwrite — the last one.
+FIN_D unsigned long long fmin_key(uint32_t end_local, uint32_t global_off) {
+    return end_local ? (((unsigned long long)end_local << 32) | (unsigned long long)(0xFFFFFFFFu - global_off))
+                     : (unsigned long long)global_off + 1ULL;
+}
+FIN_D uint32_t fmin_key_offset(unsigned long long key) {  // key != 0
+    return (key >> 32) ? 0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFu) : (uint32_t)(key - 1);
+}
+
+template <int KCAP>
+FIN_D void build_stream_chunk(const IndexView& ix, const uint64_t* __restrict__ text, const BuildChunk ch,
+                              unsigned long long* __restrict__ table, unsigned int* __restrict__ error_flags) {
+    const int k = ix.k;
+    const idx_t N = ix.n_nodes;
+    uint64_t dq[KCAP];
+    int dq_head = 0, dq_n = 0;
+    unsigned dummy = 0, err = 0;
+    Ival I{0, N - 1};
+    int64_t start = ch.first_pos;     // unitig-local left end of the current finimizer window
+    unsigned long long last_key = 0;  // consecutive windows mostly share their finimizer: one atomic per change
+    idx_t last_colex = 0;
+    bool have_last = false;
+    uint64_t word = 0;
+    for (uint32_t s = 0; s < ch.n_stream; s++) {
+        const uint64_t tp = (uint64_t)ch.text_begin + s;
+        if (s == 0 || (tp & 31) == 0) word = __ldg(text + (tp >> 5));
+        const int c = (int)((word >> (2 * (tp & 31))) & 3);
+        const int64_t end = (int64_t)ch.first_pos + s;
+        I = extend(ix, I, c);  // :346, unitigs are in the SBWT so this cannot become empty
+        if (is_empty(I)) {
+            err |= kErrLookupRange;
+            break;
+        }
+        const int64_t kmer = end - (k - 1);  // start of the window that ends here
+        if (I.l == I.r) {                    // :349-366
+            uint64_t cur;
+            do {
+                // candidate ends are kept relative to the chunk so that they fit the 24-bit field
+                cur = cand_pack((int)(end - start + 1), I.l, (int)s);
+                start++;
+                I = drop_first_char<false>(ix, (int)(end - start + 1), I, dummy);
+            } while (I.l == I.r);
+            while (dq_n > 0 && (int64_t)ch.first_pos + cand_start(dq[dq_head]) < kmer) {
+                dq_head = (dq_head + 1) & (KCAP - 1);
+                dq_n--;
+            }
+            while (dq_n > 0 && dq[(dq_head + dq_n - 1) & (KCAP - 1)] > cur) dq_n--;
+            if (dq_n == KCAP) {
+                err |= kErrWindowUnderflow;
+                dq_n--;
+            }
+            dq[(dq_head + dq_n) & (KCAP - 1)] = cur;
+            dq_n++;
+        }
+        if (end >= (int64_t)ch.first_emit) {
+            while (dq_n > 0 && (int64_t)ch.first_pos + cand_start(dq[dq_head]) < kmer) {
+                dq_head = (dq_head + 1) & (KCAP - 1);
+                dq_n--;
+            }
+            if (dq_n == 0) {  // the reference would record its sentinel here (:328,:384): not a DSPSS of this SBWT
+                err |= kErrWindowUnderflow;
+            } else {
+                const uint64_t w = dq[dq_head];
+                const uint32_t end_local = ch.first_pos + (uint32_t)cand_end(w);
+                const unsigned long long key = fmin_key(end_local, ch.unitig_start + end_local);
+                const idx_t colex = cand_colex(w);
+                if (!have_last || colex != last_colex || key != last_key) {
+                    fin_atomic_max(table + colex, key);
+                    last_key = key;
+                    last_colex = colex;
+                    have_last = true;
+                }
+            }
+        }
+    }
+    if (err) fin_atomic_or(error_flags, err);
+}
+
+#ifdef __CUDACC__
+// ones per 64-column word of each row -> (after an exclusive scan) destination of the word's first edge
+static __global__ void row_popcount_kernel(const uint64_t* __restrict__ rows, uint64_t n_words, uint32_t* __restrict__ counts) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;  // over 4 * n_words
+    if (i < 4 * n_words) counts[i] = (uint32_t)__popcll(rows[i]);
+}
+
+static __global__ void lcs_init_kernel(const LcsArgs a, uint8_t* __restrict__ last, uint8_t* __restrict__ lcs) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.n) return;
+    last[i] = lcs_first_column(a, i);
+    lcs[i] = a.k;  // "not set yet" (:76-78)
+}
+
+static __global__ void __launch_bounds__(128) lcs_round_kernel(const LcsArgs a, const uint8_t* __restrict__ last,
+                                                               uint8_t* __restrict__ next, uint8_t* __restrict__ lcs,
+                                                               uint8_t round) {
+    const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w < a.n_words) lcs_round_word(a, last, next, lcs, w, round);
+}
+
+static __global__ void first_kmer_kernel(const IndexView ix, const uint64_t* __restrict__ text,
+                                         const uint64_t* __restrict__ starts, uint32_t n_unitigs, uint32_t* __restrict__ columns) {
+    const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+    if (u < n_unitigs) columns[u] = first_kmer_column(ix, text, starts[u]);
+}
+
+template <int KCAP>
+__global__ void __launch_bounds__(128) build_stream_kernel(const IndexView ix, const uint64_t* __restrict__ text,
+                                                           const BuildChunk* __restrict__ chunks, uint32_t n_chunks,
+                                                           unsigned long long* __restrict__ table,
+                                                           unsigned int* __restrict__ error_flags) {
+    const uint32_t cid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cid < n_chunks) build_stream_chunk<KCAP>(ix, text, chunks[cid], table, error_flags);
+}
+
+// fmin bit vector (one ballot per 32 columns) and the offset of every column (0xFFFFFFFF where unset)
+static __global__ void fmin_bits_kernel(const unsigned long long* __restrict__ table, uint64_t n, uint32_t* __restrict__ bits32,
+                                        uint32_t* __restrict__ offs_or_sentinel) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned long long key = i < n ? table[i] : 0ULL;
+    const unsigned mask = __ballot_sync(0xFFFFFFFFu, key != 0ULL);
+    if ((threadIdx.x & 31) == 0 && i < ((n + 31) / 32) * 32) bits32[i >> 5] = mask;
+    if (i < n) offs_or_sentinel[i] = key ? fmin_key_offset(key) : 0xFFFFFFFFu;
+}
+
+struct NotSentinel {
+    __host__ __device__ bool operator()(const uint32_t& v) const { return v != 0xFFFFFFFFu; }
+};
+#endif  // __CUDACC__
+
+}  // namespace fin

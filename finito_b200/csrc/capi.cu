@@ -86,6 +86,14 @@ fin_status fin_search_batch(fin_index* index, const char* seqs, const uint64_t* 
     });
 }
 
+fin_status fin_search_forward(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
+                              int64_t* out_pairs, uint64_t out_capacity, fin_search_counts* counts) {
+    return guarded([&] {
+        require(index && read_offsets && (seqs || n_reads == 0) && (out_pairs || out_capacity == 0), "fin_search_forward: null argument");
+        index->dev->search_host<int64_t>(seqs, read_offsets, n_reads, out_pairs, out_capacity, counts, 1);
+    });
+}
+
 fin_status fin_search_batch32(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
                               int32_t* out_pairs, uint64_t out_capacity, fin_search_counts* counts) {
     return guarded([&] {

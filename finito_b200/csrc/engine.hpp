@@ -8,6 +8,7 @@
 
 #include "device_index.cuh"
 #include "formats.hpp"
+#include "layout_host.hpp"
 #include "../../include/finito_b200.h"
 
 namespace fin {
@@ -48,19 +49,6 @@ template <class T> struct DevBuf {
     size_t bytes() const { return n * sizeof(T); }
 };
 
-// 32-byte rank sectors {ones before block, 3 words} over a bit vector; `rows` interleaved rows per block.
-// rows[r] points at the words of row r (at least ceil(n_bits/64) words).  Returns 4*rows u64 per block for
-// n_bits/192 + 1 blocks, so rank(n_bits) is addressable.
-std::vector<uint64_t> make_rank_sectors(const uint64_t* const* rows, int n_rows, uint64_t n_bits, uint64_t* totals);
-
-// The seven files of a FinimizerIndex as the reference holds them in memory (FinimizerIndex.hh:108-115)
-struct IndexHost {
-    SbwtHost sbwt;
-    PackedVec lcs, fmin, offsets, text, ends, ustart;
-};
-IndexHost load_index_files(const std::string& prefix);
-void save_index_files(const IndexHost& ix, const std::string& prefix);
-
 struct SearchSlot;  // per-stream staging buffers of the batch pipeline
 
 class DeviceIndex {
@@ -75,7 +63,7 @@ class DeviceIndex {
     // search_fmin.hh:43-72 for a batch in host memory / in device memory
     template <class HitT>
     void search_host(const char* seqs, const uint64_t* read_offsets, uint64_t n_reads, HitT* out_pairs, uint64_t out_capacity,
-                     fin_search_counts* counts);
+                     fin_search_counts* counts, int n_strands = 2);
     void search_device(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases,
                        uint64_t total_kmers, void* d_out, int hit_bytes, fin_search_counts* counts, float* kernel_ms);
     fin_access_counters last_access{};

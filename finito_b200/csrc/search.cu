@@ -15,66 +15,6 @@ namespace fin {
 thread_local uint64_t g_launches = 0;
 
 // -------------------------------------------------------------------------------------------------------
-// rank sectors
-// -------------------------------------------------------------------------------------------------------
-std::vector<uint64_t> make_rank_sectors(const uint64_t* const* rows, int n_rows, uint64_t n_bits, uint64_t* totals) {
-    const uint64_t n_blocks = n_bits / kRankBlockBits + 1;
-    const uint64_t n_words = (n_bits + 63) >> 6;
-    std::vector<uint64_t> s(n_blocks * 4 * (uint64_t)n_rows, 0);
-    for (int r = 0; r < n_rows; r++) {
-        uint64_t cum = 0;
-        const uint64_t* w = rows[r];
-        const uint64_t tail_bits = n_bits & 63;
-        for (uint64_t b = 0; b < n_blocks; b++) {
-            uint64_t* sec = &s[(b * (uint64_t)n_rows + (uint64_t)r) * 4];
-            sec[0] = cum;
-            for (int j = 0; j < 3; j++) {
-                const uint64_t wi = b * 3 + (uint64_t)j;
-                uint64_t x = wi < n_words ? w[wi] : 0;
-                if (tail_bits && wi == n_words - 1) x &= (1ULL << tail_bits) - 1;  // bits past the end never count
-                sec[1 + j] = x;
-                cum += (uint64_t)__builtin_popcountll(x);
-            }
-        }
-        if (totals) totals[r] = cum;
-    }
-    return s;
-}
-
-// -------------------------------------------------------------------------------------------------------
-// index files (FinimizerIndex.hh:187-241)
-// -------------------------------------------------------------------------------------------------------
-IndexHost load_index_files(const std::string& prefix) {
-    IndexHost ix;
-    ix.lcs = load_packed_file(prefix + ".LCS.sdsl", 0);
-    ix.fmin = load_packed_file(prefix + ".FBV.sdsl", 1);
-    ix.offsets = load_packed_file(prefix + ".O.sdsl", 0);
-    ix.text = load_packed_file(prefix + ".packed_unitigs.sdsl", 2);
-    ix.ends = load_packed_file(prefix + ".unitig_endpoints.sdsl", 0);
-    ix.ustart = load_packed_file(prefix + ".Ustart.sdsl", 1);
-    ix.sbwt = load_sbwt_file(prefix + ".sbwt", false);
-    const uint64_t N = (uint64_t)ix.sbwt.n_nodes;
-    if (ix.lcs.size() != N || ix.fmin.size() != N || ix.ustart.size() != N)
-        throw format_error("index files under " + prefix + " disagree on the number of SBWT columns");
-    return ix;
-}
-
-void save_index_files(const IndexHost& ix, const std::string& prefix) {
-    save_packed_file(prefix + ".O.sdsl", ix.offsets, true);
-    save_packed_file(prefix + ".FBV.sdsl", ix.fmin, false);
-    save_packed_file(prefix + ".packed_unitigs.sdsl", ix.text, false);
-    save_packed_file(prefix + ".unitig_endpoints.sdsl", ix.ends, true);
-    save_packed_file(prefix + ".Ustart.sdsl", ix.ustart, false);
-    save_packed_file(prefix + ".LCS.sdsl", ix.lcs, true);
-    const std::string path = prefix + ".sbwt";
-    FILE* f = fopen(path.c_str(), "wb");
-    if (!f) throw io_error("cannot write " + path);
-    const size_t n = ix.sbwt.body.size();
-    const bool ok = fwrite(ix.sbwt.body.data(), 1, n, f) == n;
-    if (fclose(f) != 0 || !ok) throw io_error("short write on " + path);
-}
-
-// -------------------------------------------------------------------------------------------------------
 // per-stream staging of the host pipeline
 // -------------------------------------------------------------------------------------------------------
 struct SearchSlot {
@@ -109,66 +49,15 @@ DeviceIndex::DeviceIndex(const IndexHost& h, int device) : device_(device) {
     if (device < 0 || device >= n_dev) throw arg_error("CUDA device ordinal out of range");
     FIN_CUDA(cudaSetDevice(device));
 
-    const uint64_t N = (uint64_t)h.sbwt.n_nodes, T = h.text.size(), U = h.ends.size(), F = h.offsets.size();
-    const uint64_t lim = 0xFFFFFFFFull - 256;
-    if (N >= lim || T >= lim) throw limit_error("index too large for the 32-bit column/text positions of this build");
-    if (N < 2) throw domain_error("SBWT with fewer than 2 columns");
-    if (U == 0 || (U && h.ends.get(U - 1) != T)) throw format_error("unitig end points do not match the packed text");
-
-    {  // subset matrix
-        const uint64_t* rows[4] = {h.sbwt.bits[0].words.data(), h.sbwt.bits[1].words.data(), h.sbwt.bits[2].words.data(),
-                                   h.sbwt.bits[3].words.data()};
-        std::vector<uint64_t> s = make_rank_sectors(rows, 4, N, nullptr);
-        matrix_ = upload(s.data(), s.size());
-    }
-    {
-        const uint64_t* r[1] = {h.ustart.words.data()};
-        std::vector<uint64_t> s = make_rank_sectors(r, 1, N, nullptr);
-        ustart_ = upload(s.data(), s.size());
-    }
-    {
-        const uint64_t* r[1] = {h.fmin.words.data()};
-        uint64_t total = 0;
-        std::vector<uint64_t> s = make_rank_sectors(r, 1, N, &total);
-        fmin_ = upload(s.data(), s.size());
-        (void)total;
-    }
-    std::vector<uint32_t> ends(U);
-    {
-        std::vector<uint64_t> ts((T >> 6) + 2, 0);
-        uint64_t prev = 0;
-        for (uint64_t u = 0; u < U; u++) {
-            const uint64_t e = h.ends.get(u);
-            if (e <= prev || e > T) throw format_error("unitig end points are not strictly increasing");
-            ts[prev >> 6] |= 1ULL << (prev & 63);
-            ends[u] = (uint32_t)e;
-            prev = e;
-        }
-        const uint64_t* r[1] = {ts.data()};
-        std::vector<uint64_t> s = make_rank_sectors(r, 1, T, nullptr);
-        tstart_ = upload(s.data(), s.size());
-    }
-    ends_ = upload(ends.data(), ends.size());
-    {
-        std::vector<uint8_t> l(N + 64, 0);
-        for (uint64_t i = 0; i < N; i++) l[i] = (uint8_t)h.lcs.get(i);
-        lcs_ = upload(l.data(), l.size());
-    }
-    {
-        std::vector<uint32_t> o(F + 1, 0);
-        for (uint64_t i = 0; i < F; i++) {
-            const uint64_t v = h.offsets.get(i);
-            if (v >= lim) throw limit_error("finimizer offset beyond 32 bits");
-            o[i] = (uint32_t)v;
-        }
-        offsets_ = upload(o.data(), o.size());
-    }
-    {
-        const uint64_t nw = (T + 31) / 32 + 2;
-        std::vector<uint64_t> t(nw, 0);
-        memcpy(t.data(), h.text.words.data(), std::min<uint64_t>(nw, h.text.words.size()) * 8);
-        text_ = upload(t.data(), t.size());
-    }
+    const HostLayout L = build_host_layout(h);
+    matrix_ = upload(L.matrix.data(), L.matrix.size());
+    ustart_ = upload(L.ustart.data(), L.ustart.size());
+    fmin_ = upload(L.fmin.data(), L.fmin.size());
+    tstart_ = upload(L.tstart.data(), L.tstart.size());
+    text_ = upload(L.text.data(), L.text.size());
+    lcs_ = upload(L.lcs.data(), L.lcs.size());
+    offsets_ = upload(L.offsets.data(), L.offsets.size());
+    ends_ = upload(L.ends.data(), L.ends.size());
 
     view_.matrix = reinterpret_cast<const ulonglong2*>(matrix_.p);
     view_.ustart = reinterpret_cast<const ulonglong2*>(ustart_.p);
@@ -178,26 +67,20 @@ DeviceIndex::DeviceIndex(const IndexHost& h, int device) : device_(device) {
     view_.offsets = offsets_.p;
     view_.ends = ends_.p;
     view_.text = text_.p;
-    for (int c = 0; c < 4; c++) view_.C[c] = (idx_t)h.sbwt.C[c];
-    view_.n_nodes = (idx_t)N;
-    view_.text_len = (idx_t)T;
-    view_.n_unitigs = (uint32_t)U;
-    view_.n_fmin = (uint32_t)F;
-    view_.k = (int32_t)h.sbwt.k;
+    for (int c = 0; c < 4; c++) view_.C[c] = (idx_t)L.C[c];
+    view_.n_nodes = (idx_t)L.n_nodes;
+    view_.text_len = (idx_t)L.text_len;
+    view_.n_unitigs = (uint32_t)L.n_unitigs;
+    view_.n_fmin = (uint32_t)L.n_fmin;
+    view_.k = (int32_t)L.k;
+    fits32_ = L.n_unitigs < 0x7FFFFFFFull && L.max_unitig_len < 0x7FFFFFFFull;
 
-    uint64_t max_len = 0, prev = 0;
-    for (uint64_t u = 0; u < U; u++) {
-        max_len = std::max<uint64_t>(max_len, ends[u] - prev);
-        prev = ends[u];
-    }
-    fits32_ = U < 0x7FFFFFFFull && max_len < 0x7FFFFFFFull;
-
-    info_.k = h.sbwt.k;
-    info_.n_nodes = (int64_t)N;
-    info_.n_kmers = h.sbwt.n_kmers;
-    info_.n_unitigs = (int64_t)U;
-    info_.text_len = (int64_t)T;
-    info_.n_finimizers = (int64_t)F;
+    info_.k = L.k;
+    info_.n_nodes = (int64_t)L.n_nodes;
+    info_.n_kmers = L.n_kmers;
+    info_.n_unitigs = (int64_t)L.n_unitigs;
+    info_.text_len = (int64_t)L.text_len;
+    info_.n_finimizers = (int64_t)L.n_fmin;
     info_.device = device;
     info_.device_bytes = (int64_t)(matrix_.bytes() + ustart_.bytes() + fmin_.bytes() + tstart_.bytes() + lcs_.bytes() +
                                    offsets_.bytes() + ends_.bytes() + text_.bytes());
@@ -217,15 +100,15 @@ static int window_capacity(int k) { return k <= 32 ? 32 : k <= 64 ? 64 : k <= 12
 
 template <class HitT, bool COUNT>
 static void launch_search_t(const IndexView& v, const uint64_t* packed, const uint64_t* offsets, uint64_t n_reads,
-                            const uint64_t* out_offsets, void* out, SearchTotals* totals, cudaStream_t st) {
+                            const uint64_t* out_offsets, void* out, SearchTotals* totals, int n_strands, cudaStream_t st) {
     const unsigned threads = 128;
     const unsigned blocks = (unsigned)((n_reads + threads - 1) / threads);
     HitPair<HitT>* o = reinterpret_cast<HitPair<HitT>*>(out);
     switch (window_capacity(v.k)) {
-        case 32: search_reads_kernel<32, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals); break;
-        case 64: search_reads_kernel<64, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals); break;
-        case 128: search_reads_kernel<128, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals); break;
-        default: search_reads_kernel<256, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals); break;
+        case 32: search_reads_kernel<32, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands); break;
+        case 64: search_reads_kernel<64, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands); break;
+        case 128: search_reads_kernel<128, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands); break;
+        default: search_reads_kernel<256, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands); break;
     }
     g_launches++;
     FIN_CUDA(cudaGetLastError());
@@ -235,7 +118,7 @@ static void launch_search_t(const IndexView& v, const uint64_t* packed, const ui
 static void launch_pipeline(const IndexView& v, const uint8_t* d_ascii, uint64_t n_bases, const uint64_t* d_offsets,
                             uint64_t n_reads, uint64_t* d_packed, uint64_t* d_out_offsets, void* d_scan_tmp,
                             size_t scan_tmp_bytes, void* d_out, int hit_bytes, SearchTotals* d_totals, bool count,
-                            cudaStream_t st) {
+                            int n_strands, cudaStream_t st) {
     if (n_reads == 0) return;
     const uint64_t n_words = (n_bases + 31) / 32 + 1;
     {
@@ -251,11 +134,11 @@ static void launch_pipeline(const IndexView& v, const uint8_t* d_ascii, uint64_t
     FIN_CUDA(cub::DeviceScan::ExclusiveSum(d_scan_tmp, scan_tmp_bytes, d_out_offsets, d_out_offsets, (int64_t)n_reads, st));
     g_launches += 2;
     if (hit_bytes == 4) {
-        if (count) launch_search_t<int32_t, true>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, st);
-        else launch_search_t<int32_t, false>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, st);
+        if (count) launch_search_t<int32_t, true>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, n_strands, st);
+        else launch_search_t<int32_t, false>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, n_strands, st);
     } else {
-        if (count) launch_search_t<int64_t, true>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, st);
-        else launch_search_t<int64_t, false>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, st);
+        if (count) launch_search_t<int64_t, true>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, n_strands, st);
+        else launch_search_t<int64_t, false>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, n_strands, st);
     }
 }
 
@@ -310,7 +193,7 @@ void DeviceIndex::search_device(const void* d_seqs, const uint64_t* d_read_offse
     FIN_CUDA(cudaEventCreate(&e1));
     FIN_CUDA(cudaEventRecord(e0, 0));
     launch_pipeline(view_, (const uint8_t*)d_seqs, n_bases, d_read_offsets, n_reads, dev_packed_.p, dev_out_offsets_.p,
-                    dev_scan_tmp_.p, tmp, d_out, hit_bytes, (SearchTotals*)dev_totals_.p, count_accesses, 0);
+                    dev_scan_tmp_.p, tmp, d_out, hit_bytes, (SearchTotals*)dev_totals_.p, count_accesses, 2, 0);
     FIN_CUDA(cudaEventRecord(e1, 0));
     SearchTotals t;
     FIN_CUDA(cudaMemcpy(&t, dev_totals_.p, sizeof t, cudaMemcpyDeviceToHost));
@@ -337,7 +220,7 @@ static constexpr int kSlots = 3;
 
 template <class HitT>
 void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, uint64_t n_reads, HitT* out_pairs,
-                              uint64_t out_capacity, fin_search_counts* counts) {
+                              uint64_t out_capacity, fin_search_counts* counts, int n_strands) {
     if (sizeof(HitT) == 4 && !fits32_) throw limit_error("this index needs 64-bit hits (use fin_search_batch)");
     FIN_CUDA(cudaSetDevice(device_));
     const int k = view_.k;
@@ -409,7 +292,7 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
         FIN_CUDA(cudaMemcpyAsync(s.ascii.p, seqs + base0, nb, cudaMemcpyHostToDevice, s.stream));
         FIN_CUDA(cudaMemcpyAsync(s.offsets.p, s.h_offsets_pinned, (nr + 1) * 8, cudaMemcpyHostToDevice, s.stream));
         launch_pipeline(view_, s.ascii.p, nb, s.offsets.p, nr, s.packed.p, s.out_offsets.p, s.scan_tmp.p, tmp, s.hits.p,
-                        (int)sizeof(HitT), (SearchTotals*)s.totals.p, count_accesses, s.stream);
+                        (int)sizeof(HitT), (SearchTotals*)s.totals.p, count_accesses, n_strands, s.stream);
         if (nkm)
             FIN_CUDA(cudaMemcpyAsync(out_pairs + 2 * out_pos, s.hits.p, nkm * 2 * sizeof(HitT), cudaMemcpyDeviceToHost, s.stream));
         FIN_CUDA(cudaMemcpyAsync(s.h_totals, s.totals.p, sizeof(SearchTotals), cudaMemcpyDeviceToHost, s.stream));
@@ -423,7 +306,7 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
     if (counts) *counts = c;
 }
 
-template void DeviceIndex::search_host<int32_t>(const char*, const uint64_t*, uint64_t, int32_t*, uint64_t, fin_search_counts*);
-template void DeviceIndex::search_host<int64_t>(const char*, const uint64_t*, uint64_t, int64_t*, uint64_t, fin_search_counts*);
+template void DeviceIndex::search_host<int32_t>(const char*, const uint64_t*, uint64_t, int32_t*, uint64_t, fin_search_counts*, int);
+template void DeviceIndex::search_host<int64_t>(const char*, const uint64_t*, uint64_t, int64_t*, uint64_t, fin_search_counts*, int);
 
 }  // namespace fin

@@ -120,7 +120,7 @@ constexpr int kMaxReadLen = (1 << 24) - 1;
 // non-decreasing along the deque, so at most k live entries exist).
 template <int KCAP, class HitT, bool COUNT>
 FIN_D void search_one_read(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t b0, const uint64_t len64,
-                           HitPair<HitT>* __restrict__ o, ReadCounters& rc) {
+                           HitPair<HitT>* __restrict__ o, ReadCounters& rc, const int n_strands = 2) {
     unsigned (&found)[2] = rc.found;
     unsigned &positive = rc.positive, &n_q = rc.n_q, &err = rc.err;
     unsigned &c_rank = rc.c_rank, &c_lcs = rc.c_lcs, &c_ustart = rc.c_ustart, &c_anchor = rc.c_anchor, &c_branch = rc.c_branch,
@@ -136,7 +136,7 @@ FIN_D void search_one_read(const IndexView& ix, const uint64_t* __restrict__ pac
             n_q = (unsigned)nk;
             uint64_t dq[KCAP];
 
-            for (int strand = 0; strand < 2; strand++) {
+            for (int strand = 0; strand < n_strands; strand++) {
                 int start = 0, kmer_start = 0;
                 Ival I{0, N - 1}, Ik{0, N - 1};
                 int dq_head = 0, dq_n = 0;
@@ -327,13 +327,14 @@ template <int KCAP, class HitT, bool COUNT>
 __global__ void __launch_bounds__(128) search_reads_kernel(const IndexView ix, const uint64_t* __restrict__ packed,
                                                            const uint64_t* __restrict__ read_offsets, const uint64_t n_reads,
                                                            const uint64_t* __restrict__ out_offsets,
-                                                           HitPair<HitT>* __restrict__ out, SearchTotals* __restrict__ totals) {
+                                                           HitPair<HitT>* __restrict__ out, SearchTotals* __restrict__ totals,
+                                                           const int n_strands) {
     const uint64_t rid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     ReadCounters rc;
     if (rid < n_reads) {
         const uint64_t b0 = __ldg(read_offsets + rid);
         const uint64_t len64 = __ldg(read_offsets + rid + 1) - b0;
-        search_one_read<KCAP, HitT, COUNT>(ix, packed, b0, len64, out + __ldg(out_offsets + rid), rc);
+        search_one_read<KCAP, HitT, COUNT>(ix, packed, b0, len64, out + __ldg(out_offsets + rid), rc, n_strands);
     }
     const unsigned err = rc.err;
     const unsigned c_rank = rc.c_rank, c_lcs = rc.c_lcs, c_ustart = rc.c_ustart, c_anchor = rc.c_anchor, c_branch = rc.c_branch,

@@ -90,6 +90,12 @@ uint64_t fin_count_kmers(const uint64_t* read_offsets, uint64_t n_reads, int64_t
 fin_status fin_search_batch(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
                             int64_t* out_pairs, uint64_t out_capacity, fin_search_counts* counts);
 
+/* FinimizerIndex::search(query) for every read of the batch (include/FinimizerIndex.hh:119-185): the forward
+ * strand only, no reverse-complement search and no merge — the call the reference's own tests make
+ * (src/tests.cpp:86-101).  counts->found_fwd is the sum of QueryResult::n_found. */
+fin_status fin_search_forward(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
+                              int64_t* out_pairs, uint64_t out_capacity, fin_search_counts* counts);
+
 /* Same, 2 x int32 per k-mer position (halves the device->host traffic).  FIN_ERR_LIMIT if a unitig id
  * or offset of this index cannot be represented. */
 fin_status fin_search_batch32(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,

@@ -1,0 +1,193 @@
+// TEST INFRASTRUCTURE ONLY.  Compiles the per-thread bodies of the CUDA kernels (finito_b200/csrc/*.cuh,
+// built with -DFIN_EMU) for the host, one "thread" after the other, so that the kernel logic can be diffed
+// against the oracle in the CPU-only container before any GPU time is spent.  Nothing in the product links
+// or loads this file; the shipped library has no CPU path.
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+struct ulonglong2 { unsigned long long x, y; };
+struct uint4 { unsigned int x, y, z, w; };
+template <class T> static inline T __ldg(const T* p) { return *p; }
+static inline int __popcll(unsigned long long x) { return __builtin_popcountll(x); }
+using std::max;
+using std::min;
+
+#define FIN_EMU 1
+#include "../../finito_b200/csrc/build_kernels.cuh"
+
+using namespace fin;
+
+static thread_local std::string g_err;
+template <class F> static int guarded(F f) {
+    try { f(); return 0; } catch (const std::exception& e) { g_err = e.what(); return 1; }
+}
+
+static IndexView view_of(const HostLayout& L) {
+    IndexView v{};
+    v.matrix = reinterpret_cast<const ulonglong2*>(L.matrix.data());
+    v.ustart = reinterpret_cast<const ulonglong2*>(L.ustart.data());
+    v.fmin = reinterpret_cast<const ulonglong2*>(L.fmin.data());
+    v.tstart = reinterpret_cast<const ulonglong2*>(L.tstart.data());
+    v.lcs = L.lcs.data();
+    v.offsets = L.offsets.data();
+    v.ends = L.ends.data();
+    v.text = L.text.data();
+    for (int c = 0; c < 4; c++) v.C[c] = (idx_t)L.C[c];
+    v.n_nodes = (idx_t)L.n_nodes;
+    v.text_len = (idx_t)L.text_len;
+    v.n_unitigs = (uint32_t)L.n_unitigs;
+    v.n_fmin = (uint32_t)L.n_fmin;
+    v.k = (int32_t)L.k;
+    return v;
+}
+
+template <class HitT, bool COUNT>
+static void run_read(const IndexView& v, const uint64_t* packed, uint64_t b0, uint64_t len, HitPair<HitT>* o, ReadCounters& rc,
+                     int n_strands) {
+    const int k = v.k;
+    if (k <= 32) search_one_read<32, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
+    else if (k <= 64) search_one_read<64, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
+    else if (k <= 128) search_one_read<128, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
+    else search_one_read<256, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
+}
+
+static std::vector<uint8_t> emu_lcs_bytes(const SbwtHost& s) {
+    uint64_t nw = 0;
+    std::vector<uint64_t> rows = sbwt_row_words(s, nw);
+    std::vector<uint32_t> word_dst(4 * nw);
+    for (int c = 0; c < 4; c++) {
+        uint32_t cum = 0;
+        for (uint64_t w = 0; w < nw; w++) {
+            word_dst[c * nw + w] = cum;
+            cum += (uint32_t)__builtin_popcountll(rows[c * nw + w]);
+        }
+    }
+    const uint64_t padded = nw * 64 + 64;
+    std::vector<uint8_t> last(padded, 0), next(padded, 0), lcs(padded, 0);
+    LcsArgs a{};
+    a.rows = rows.data();
+    a.word_dst = word_dst.data();
+    a.n = (uint64_t)s.n_nodes;
+    a.n_words = nw;
+    for (int c = 0; c < 4; c++) a.C[c] = (uint32_t)s.C[c];
+    a.k = (uint8_t)s.k;
+    for (uint64_t i = 0; i < a.n; i++) { last[i] = lcs_first_column(a, i); lcs[i] = a.k; }
+    for (int64_t r = 0; r < s.k; r++) {
+        for (uint64_t w = 0; w < nw; w++) lcs_round_word(a, last.data(), next.data(), lcs.data(), w, (uint8_t)r);
+        last.swap(next);
+    }
+    lcs.resize((size_t)s.n_nodes);
+    return lcs;
+}
+
+extern "C" {
+
+const char* emu_last_error() { return g_err.c_str(); }
+
+// counts4: found_fwd, found_rc, positive, n_queries; access8: the eight access counters; flags: error bits
+int emu_search(const char* prefix, const char* seqs, const uint64_t* offs, uint64_t n_reads, int64_t* out, int64_t* counts4,
+               int64_t* access8, uint32_t* flags, int n_strands) {
+    return guarded([&] {
+        IndexHost h = load_index_files(prefix);
+        HostLayout L = build_host_layout(h);
+        IndexView v = view_of(L);
+        const uint64_t nb = offs[n_reads];
+        std::vector<uint64_t> packed(nb / 32 + 2, 0);
+        *flags = 0;
+        for (uint64_t i = 0; i < nb; i++) {
+            const uint32_t ch = (uint8_t)seqs[i] & ~32u;
+            if (!(ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T')) *flags |= kErrBadBase;
+            packed[i >> 5] |= (uint64_t)(((ch >> 1) ^ (ch >> 2)) & 3u) << (2 * (i & 31));
+        }
+        uint64_t o = 0;
+        for (int i = 0; i < 4; i++) counts4[i] = 0;
+        for (int i = 0; i < 8; i++) access8[i] = 0;
+        for (uint64_t r = 0; r < n_reads; r++) {
+            ReadCounters rc;
+            const uint64_t len = offs[r + 1] - offs[r];
+            run_read<int64_t, true>(v, packed.data(), offs[r], len, reinterpret_cast<HitPair<int64_t>*>(out) + o, rc, n_strands);
+            if (len >= (uint64_t)v.k) o += len - v.k + 1;
+            counts4[0] += rc.found[0]; counts4[1] += rc.found[1]; counts4[2] += rc.positive; counts4[3] += rc.n_q;
+            const unsigned a[8] = {rc.c_rank, rc.c_lcs, rc.c_ustart, rc.c_anchor, rc.c_branch, rc.c_walk, rc.c_bases, rc.c_kmers};
+            for (int i = 0; i < 8; i++) access8[i] += a[i];
+            *flags |= rc.err;
+        }
+    });
+}
+
+int emu_lcs(const char* sbwt_path, int with_variant, uint8_t* out, uint64_t cap) {
+    return guarded([&] {
+        SbwtHost s = load_sbwt_file(sbwt_path, with_variant != 0);
+        if ((uint64_t)s.n_nodes > cap) throw arg_error("buffer too small");
+        std::vector<uint8_t> l = emu_lcs_bytes(s);
+        memcpy(out, l.data(), l.size());
+    });
+}
+
+// build-fmin --type rarest with the kernel bodies; per_chunk = 0 lets the planner choose
+int emu_build(const char* sbwt_path, const char* unitig_path, const char* out_prefix, uint64_t per_chunk) {
+    return guarded([&] {
+        const std::vector<std::string> files = unitig_file_list(unitig_path);
+        SbwtHost sbwt = load_sbwt_file(sbwt_path, true);
+        check_sbwt_limits(sbwt);
+        const uint64_t N = (uint64_t)sbwt.n_nodes;
+        const int k = (int)sbwt.k;
+        PackedVec lcs_file = lcs_bytes_to_packed(emu_lcs_bytes(sbwt), N, k);
+        SeqBatch unitigs;
+        append_sequences(files[0], unitigs);
+        check_unitigs(unitigs, k);
+        const uint64_t U = unitigs.size();
+        std::vector<uint64_t> matrix = matrix_sectors(sbwt);
+        std::vector<uint8_t> lb = lcs_bytes(lcs_file);
+        IndexView ix{};
+        ix.matrix = reinterpret_cast<const ulonglong2*>(matrix.data());
+        ix.lcs = lb.data();
+        for (int c = 0; c < 4; c++) ix.C[c] = (idx_t)sbwt.C[c];
+        ix.n_nodes = (idx_t)N;
+        ix.k = k;
+        std::vector<uint64_t> order(U), starts;
+        for (uint64_t u = 0; u < U; u++) order[u] = u;
+        PackedVec text;
+        pack_unitigs(unitigs, order, text, starts);
+        text.words.resize(text.words.size() + 2, 0);
+        std::vector<uint32_t> cols(U);
+        for (uint64_t u = 0; u < U; u++) cols[u] = first_kmer_column(ix, text.words.data(), starts[u]);
+        PackedVec ustart;
+        order = unitig_order(cols, N, ustart);
+        pack_unitigs(unitigs, order, text, starts);
+        text.words.resize(text.words.size() + 2, 0);
+        PackedVec ends = unitig_ends(unitigs, order, starts);
+        std::vector<BuildChunk> chunks = plan_build_chunks(starts, ends, k, per_chunk);
+        std::vector<unsigned long long> table(N, 0);
+        unsigned err = 0;
+        for (const BuildChunk& ch : chunks) {
+            if (k <= 32) build_stream_chunk<32>(ix, text.words.data(), ch, table.data(), &err);
+            else if (k <= 64) build_stream_chunk<64>(ix, text.words.data(), ch, table.data(), &err);
+            else if (k <= 128) build_stream_chunk<128>(ix, text.words.data(), ch, table.data(), &err);
+            else build_stream_chunk<256>(ix, text.words.data(), ch, table.data(), &err);
+        }
+        if (err) throw domain_error("emu: build stream error flags " + std::to_string(err));
+        IndexHost out;
+        out.fmin.assign(N, 1);
+        std::vector<uint32_t> offs;
+        for (uint64_t i = 0; i < N; i++)
+            if (table[i]) {
+                out.fmin.words[i >> 6] |= 1ULL << (i & 63);
+                offs.push_back(fmin_key_offset(table[i]));
+            }
+        out.offsets = pack_offsets(offs);
+        text.words.resize(text.disk_words() + 1);
+        out.sbwt = std::move(sbwt);
+        out.lcs = std::move(lcs_file);
+        out.text = std::move(text);
+        out.ends = std::move(ends);
+        out.ustart = std::move(ustart);
+        save_index_files(out, out_prefix);
+        append_stats_line(out_prefix, 1, "");
+    });
+}
+
+}  // extern "C"

@@ -1,0 +1,65 @@
+"""GPU parity tests of build-fmin through the C ABI: index files byte-identical to the reference's (golden
+fixtures) and to the oracle's on seeded synthetic inputs; LCS kernel against the oracle."""
+import os
+
+import numpy as np
+import pytest
+
+import helpers as H
+from conftest import golden_cases
+from datasets import make_dataset
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("case", golden_cases())
+def test_golden_index_files(case, gpu_lib, tmp_path):
+    fb = gpu_lib
+    d = os.path.join(H.GOLDEN, case)
+    prefix = str(tmp_path / "gpu")
+    assert fb.build_fmin(os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), prefix) == ""
+    for suf in H.INDEX_SUFFIXES + ["_stats.txt"]:
+        assert H.files_equal(prefix + suf, os.path.join(d, "ref" + suf)), suf
+
+
+@pytest.mark.parametrize("case", golden_cases())
+def test_golden_lcs(case, gpu_lib):
+    fb = gpu_lib
+    d = os.path.join(H.GOLDEN, case)
+    lcs = fb.lcs_array(os.path.join(d, "input.sbwt"))
+    want = H.oracle_lcs(os.path.join(d, "input.sbwt"), len(lcs))
+    assert np.array_equal(lcs, want)
+
+
+@pytest.mark.parametrize("k,genome_len", [(31, 1_000_000), (63, 300_000), (20, 200_000)])
+def test_synthetic_build_matches_oracle(k, genome_len, gpu_lib, tmp_path):
+    fb = gpu_lib
+    ds = make_dataset("gpub", genome_len=genome_len, k=k, n_reads=2000, read_len=150, seed=100 + k)
+    gp, op = str(tmp_path / "gpu"), str(tmp_path / "orc")
+    fb.build_fmin(ds["sbwt"], ds["unitigs"], gp)
+    H.oracle_build(ds["sbwt"], ds["unitigs"], op)
+    for suf in H.INDEX_SUFFIXES + ["_stats.txt"]:
+        assert H.files_equal(gp + suf, op + suf), suf
+    # the GPU-built index answers queries like the oracle's
+    seqs, offs = ds["reads"]
+    want, _ = H.Oracle(op).search_reads(seqs, offs)
+    with fb.FinimizerIndex.load(gp) as ix:
+        got, _ = ix.search_batch((seqs, offs))
+    assert np.array_equal(got, want)
+
+
+def test_build_with_given_lcs_and_error_paths(gpu_lib, tmp_path):
+    fb = gpu_lib
+    d = os.path.join(H.GOLDEN, "syn_k31")
+    prefix = str(tmp_path / "gpu")
+    fb.build_fmin(os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), prefix, lcs_path=os.path.join(d, "ref.LCS.sdsl"))
+    for suf in H.INDEX_SUFFIXES:
+        assert H.files_equal(prefix + suf, os.path.join(d, "ref" + suf)), suf
+    with pytest.raises(fb.FinitoError) as e:  # build_fmin.hh:245-247
+        fb.build_fmin(os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), prefix, t=4)
+    assert "t != 1 does not make sense with rarest type" in e.value.message
+    with pytest.raises(fb.FinitoError):
+        fb.build_fmin(os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), prefix, type="nonsense")
+    with pytest.raises(fb.FinitoError) as e:  # the index member has no variant header
+        fb.build_fmin(os.path.join(d, "ref.sbwt"), os.path.join(d, "unitigs.fna"), prefix)
+    assert e.value.status == fb.FIN_ERR_FORMAT

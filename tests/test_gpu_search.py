@@ -1,0 +1,150 @@
+"""GPU parity tests of search-fmin, through the C ABI (finito_b200.lib()).  Bit-exact against the reference's
+golden outputs and against the oracle on seeded synthetic inputs."""
+import os
+
+import numpy as np
+import pytest
+
+import helpers as H
+from conftest import golden_cases
+from datasets import make_dataset
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("case", golden_cases())
+def test_golden_search_output(case, gpu_lib):
+    fb = gpu_lib
+    d = os.path.join(H.GOLDEN, case)
+    reads = H.read_fasta(os.path.join(d, "queries.fna"))
+    want = H.parse_output(os.path.join(d, "ref_out.txt"))
+    with fb.FinimizerIndex.load(os.path.join(d, "ref")) as ix:
+        got, counts = ix.search_batch(reads)
+        assert np.array_equal(got, want)
+        assert counts.positive == int((want[:, 0] != -1).sum())
+        got32, _ = ix.search_batch(reads, hit_bits=32)
+        assert np.array_equal(got32.astype(np.int64), want)
+        k = ix.info["k"]
+        text = fb.format_hits(got, [max(0, len(r) - k + 1) for r in reads])
+        assert text == open(os.path.join(d, "ref_out.txt")).read()
+
+
+def colex_rank(unitigs, k, u):
+    return sorted(unitigs, key=lambda s: s[:k][::-1]).index(u)
+
+
+def test_reference_known_answers(kat, gpu_lib):
+    fb = gpu_lib
+    for case in kat:
+        with fb.FinimizerIndex.load(os.path.join(H.GOLDEN, "kat_" + case["name"], "ref")) as ix:
+            for q in case["queries"]:
+                if "fwd" in q:
+                    assert [list(t) for t in ix.search(q["q"])] == q["fwd"], case["name"]
+                if q.get("fwd_unitig_of_query_rank"):
+                    assert ix.search(q["q"]) == [(colex_rank(case["unitigs"], case["k"], q["q"]), 0)]
+                if "merged" in q:
+                    assert [list(t) for t in ix.search_both_strands(q["q"])] == q["merged"]
+
+
+@pytest.fixture(scope="module")
+def synthetic(gpu_lib, tmp_path_factory):
+    ds = make_dataset("gpu", genome_len=1_000_000, k=31, n_reads=20_000, read_len=150, seed=5)
+    prefix = str(tmp_path_factory.mktemp("idx") / "orc")
+    H.oracle_build(ds["sbwt"], ds["unitigs"], prefix)
+    return ds, prefix
+
+
+def test_synthetic_matches_oracle(synthetic, gpu_lib):
+    fb = gpu_lib
+    ds, prefix = synthetic
+    seqs, offs = ds["reads"]
+    orc = H.Oracle(prefix)
+    want, wc = orc.search_reads(seqs, offs)
+    with fb.FinimizerIndex.load(prefix) as ix:
+        got, c = ix.search_batch((seqs, offs))
+        assert np.array_equal(got, want)
+        assert [c.found_fwd, c.found_rc, c.positive, c.n_queries] == [int(x) for x in wc]
+        got32, c32 = ix.search_batch((seqs, offs), hit_bits=32)
+        assert np.array_equal(got32.astype(np.int64), want) and c32 == c
+
+
+def test_ragged_and_edge_inputs(synthetic, gpu_lib):
+    fb = gpu_lib
+    ds, prefix = synthetic
+    seqs, offs = ds["reads"]
+    base = [bytes(seqs[int(offs[i]):int(offs[i + 1])]).decode() for i in range(64)]
+    k = ds["k"]
+    reads = []
+    for i, r in enumerate(base):
+        reads.append(r[: (i * 7) % 151])  # lengths 0..150, including 0, < k, == k
+    reads += ["", "A", base[0][:k - 1], base[1][:k], base[2].lower(), base[3] * 40, "ACGT" * 100]
+    s2, o2 = H.batch_of(reads)
+    orc = H.Oracle(prefix)
+    want, wc = orc.search_reads(s2, o2)
+    with fb.FinimizerIndex.load(prefix) as ix:
+        got, c = ix.search_batch(reads)
+        assert np.array_equal(got, want)
+        assert c.n_queries == int(wc[3]) and c.positive == int(wc[2])
+        empty, c0 = ix.search_batch([])
+        assert empty.shape == (0, 2) and c0.n_queries == 0
+        with pytest.raises(fb.FinitoError) as e:
+            ix.search_batch(["ACGTNACGT" * 10])
+        assert e.value.status == fb.FIN_ERR_DOMAIN
+        # the handle stays usable after an error
+        again, _ = ix.search_batch(reads)
+        assert np.array_equal(again, want)
+
+
+def test_batch_split_is_invisible(synthetic, gpu_lib):
+    """Sub-batching inside fin_search_batch must not change anything: one call == many small calls."""
+    fb = gpu_lib
+    ds, prefix = synthetic
+    seqs, offs = ds["reads"]
+    n = 3000
+    with fb.FinimizerIndex.load(prefix) as ix:
+        whole, cw = ix.search_batch((seqs[: int(offs[n])], offs[: n + 1]))
+        parts, found = [], 0
+        for a in range(0, n, 700):
+            b = min(n, a + 700)
+            sub = seqs[int(offs[a]):int(offs[b])]
+            h, c = ix.search_batch((sub, offs[a:b + 1] - offs[a]))
+            parts.append(h)
+            found += c.positive
+        assert np.array_equal(np.concatenate(parts), whole) and found == cw.positive
+
+
+def test_long_queries_unitigs_against_themselves(synthetic, gpu_lib):
+    """Config #1 plumbing: every unitig queried against its own index is found at (its colex rank, 0..)."""
+    fb = gpu_lib
+    ds, prefix = synthetic
+    unitigs = H.read_fasta(ds["unitigs"])
+    k = ds["k"]
+    order = sorted(range(len(unitigs)), key=lambda i: unitigs[i][:k][::-1])
+    rank = {u: r for r, u in enumerate(order)}
+    with fb.FinimizerIndex.load(prefix) as ix:
+        hits, c = ix.search_batch(unitigs)
+    pos = 0
+    for i, u in enumerate(unitigs):
+        n = len(u) - k + 1
+        assert (hits[pos:pos + n, 0] == rank[i]).all()
+        assert (hits[pos:pos + n, 1] == np.arange(n)).all()
+        pos += n
+    assert c.positive == c.n_queries == pos
+
+
+def test_device_resident_entry_point(synthetic, gpu_lib):
+    import torch
+
+    fb = gpu_lib
+    ds, prefix = synthetic
+    seqs, offs = ds["reads"]
+    with fb.FinimizerIndex.load(prefix) as ix:
+        want, wc = ix.search_batch((seqs, offs), hit_bits=32)
+        d_seqs = torch.from_numpy(seqs).cuda()
+        d_offs = torch.from_numpy(offs.astype(np.int64)).cuda()
+        d_out = torch.empty((want.shape[0], 2), dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        c, ms = ix.search_device(d_seqs.data_ptr(), d_offs.data_ptr(), len(offs) - 1, len(seqs), want.shape[0],
+                                 d_out.data_ptr(), 4)
+        assert ms > 0 and c == wc
+        assert np.array_equal(d_out.cpu().numpy(), want)

@@ -1,0 +1,55 @@
+"""The per-thread bodies of the CUDA kernels (finito_b200/csrc/*.cuh compiled for the host by tests/emu) against
+the oracle and the reference's golden files.  This checks the kernel LOGIC on the CPU-only box; the GPU parity
+tests proper are test_gpu_*.py.  The emulation is test infrastructure, not a product path."""
+import os
+
+import numpy as np
+import pytest
+
+import helpers as H
+from conftest import golden_cases
+from datasets import make_dataset
+
+
+@pytest.mark.parametrize("case", golden_cases())
+def test_search_bodies_match_reference_output(case):
+    d = os.path.join(H.GOLDEN, case)
+    reads = H.read_fasta(os.path.join(d, "queries.fna"))
+    seqs, offs = H.batch_of(reads)
+    got, counts, _, flags = H.emu_search(os.path.join(d, "ref"), seqs, offs)
+    assert flags == 0
+    want = H.parse_output(os.path.join(d, "ref_out.txt"))
+    assert np.array_equal(got, want)
+    assert counts[2] == int((want[:, 0] != -1).sum())
+
+
+@pytest.mark.parametrize("case", golden_cases())
+@pytest.mark.parametrize("per_chunk", [0, 1, 5])
+def test_build_bodies_match_reference_files(case, per_chunk, tmp_path):
+    d = os.path.join(H.GOLDEN, case)
+    prefix = str(tmp_path / "emu")
+    H.emu_build(os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), prefix, per_chunk)
+    for suf in H.INDEX_SUFFIXES + ["_stats.txt"]:
+        assert H.files_equal(prefix + suf, os.path.join(d, "ref" + suf)), suf
+
+
+@pytest.mark.parametrize("k,genome_len", [(31, 150_000), (63, 60_000), (17, 40_000)])
+def test_search_and_build_bodies_match_oracle_on_synthetic(k, genome_len, tmp_path):
+    ds = make_dataset("cpu", genome_len=genome_len, k=k, n_reads=400, read_len=150, seed=k)
+    orc_prefix = str(tmp_path / "orc")
+    H.oracle_build(ds["sbwt"], ds["unitigs"], orc_prefix)
+    emu_prefix = str(tmp_path / "emu")
+    H.emu_build(ds["sbwt"], ds["unitigs"], emu_prefix, 0)
+    for suf in H.INDEX_SUFFIXES:
+        assert H.files_equal(emu_prefix + suf, orc_prefix + suf), suf
+    seqs, offs = ds["reads"]
+    orc = H.Oracle(orc_prefix)
+    want, wc = orc.search_reads(seqs, offs)
+    oc = orc.counters()
+    got, gc, acc, flags = H.emu_search(orc_prefix, seqs, offs)
+    assert flags == 0 and oc["n_deque_underflow"] == 0 and oc["n_out_of_domain"] == 0
+    assert np.array_equal(got, want) and np.array_equal(gc, wc)
+    # the access counters behind the algorithmic-bytes figure agree between the oracle and the kernel bodies
+    for name in ("n_rank", "n_lcs_reads", "n_ustart_reads", "n_anchor", "n_anchor_branch", "n_walk_words", "n_bases", "n_kmers"):
+        assert acc[name] == oc[name], name
+    assert 0.5 < wc[2] / wc[3] < 0.95  # most k-mers of 1 %-error reads are found
