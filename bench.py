@@ -1,0 +1,386 @@
+#!/usr/bin/env python
+"""search-fmin throughput on B200: k-mers localized per second (BASELINE.json metric, config #2:
+5 Mbp genome unitigs, k=31, t=1 rarest, 10M simulated 150 bp reads at 1 % error per GPU).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--reads R] [--genome G]
+
+One step = one pass of the hot path over one batch of R reads (both strands, merged).  `value` is measured
+with the batch already in HBM (fin_search_device, CUDA events inside the library, on the stream the kernels
+run on); `e2e` goes through fin_search_batch32 with pinned HOST buffers, copies included.  Under torchrun every
+rank searches its own R reads against a replicated index (weak scaling, no data-path collective).
+--impl reference times the reference's own CPU implementation (oracle/_ref/finito_ref, one process per host
+core over disjoint read shards) on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import re
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "search-fmin k-mers localized/sec"
+UNIT = "k-mers/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--reads", type=int, default=10_000_000, help="reads per GPU per step")
+    ap.add_argument("--genome", type=int, default=5_000_000)
+    ap.add_argument("--k", type=int, default=31)
+    ap.add_argument("--read-len", type=int, default=150)
+    ap.add_argument("--cpu-sample-reads", type=int, default=0, help="reads of the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def dataset(args, rank=0):
+    from datasets import make_dataset
+
+    # planted repeats as in SURVEY.md §8(d) config 2: 50 families x 5 copies x 2 kb at 1 % divergence per 5 Mbp
+    return make_dataset("bench", genome_len=args.genome, k=args.k, n_reads=args.reads, read_len=args.read_len,
+                        seed=20260102 + rank, families=max(1, args.genome // 100_000))
+
+
+def workload_name(args):
+    return (f"synthetic {args.genome / 1e6:g} Mbp genome with planted repeats, flipped unitigs, k={args.k}, t=1 rarest, "
+            f"{args.reads} simulated {args.read_len} bp reads at 1% error per GPU (BASELINE.json configs[1])")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks and throttle reasons during the timed region."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device = device
+        self.rows = []
+        self.stop_flag = threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                r = subprocess.run(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5)
+                if r.returncode == 0 and r.stdout.strip():
+                    self.rows.append([x.strip() for x in r.stdout.strip().split(",")])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.2)
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) > 2 + i and r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def algorithmic_bytes(acc, n_bases_in, n_kmers, hit_bytes=8):
+    """SURVEY.md §8(d) sector model: one 32-byte sector per semantically required random access."""
+    return (32 * (acc["n_rank"] + acc["n_lcs_reads"] + acc["n_ustart_reads"] + 3 * acc["n_anchor"] + acc["n_walk_words"])
+            + 0.25 * n_bases_in + hit_bytes * n_kmers)
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+    return 6650.0, "B200_PROFILING.md fallback (of fallback)"
+
+
+def profiled_traffic():
+    """dram bytes per launch of the search kernel from the committed ncu capture, if there is one."""
+    p = os.path.join(ROOT, "profiles", "search_kernel_traffic.json")
+    if os.path.exists(p):
+        return json.load(open(p))
+    return None
+
+
+# ---------------------------------------------------------------------------------------------------------
+# reference CPU implementation
+# ---------------------------------------------------------------------------------------------------------
+def reference_binary():
+    p = os.path.join(ROOT, "oracle", "_ref", "finito_ref")
+    return p if os.path.exists(p) else None
+
+
+def cpu_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def write_fasta_shards(seqs, read_len, n_reads, shards, out_dir):
+    paths = []
+    per = (n_reads + shards - 1) // shards
+    arr = seqs[: n_reads * read_len].reshape(n_reads, read_len)
+    for s in range(shards):
+        a, b = s * per, min(n_reads, (s + 1) * per)
+        if a >= b:
+            break
+        p = os.path.join(out_dir, f"cpu_shard{s}.fna")
+        rows = arr[a:b]
+        rec = np.empty((b - a, read_len + 3), dtype=np.uint8)
+        rec[:, 0] = ord(">")
+        rec[:, 1] = ord("\n")
+        rec[:, 2:2 + read_len] = rows
+        rec[:, -1] = ord("\n")
+        rec.tofile(p)
+        paths.append((p, b - a))
+    return paths
+
+
+def run_reference_sample(index_prefix, seqs, read_len, k, n_reads, threads, work_dir):
+    """P reference processes over P disjoint shards; returns (k-mers/s over the wall time of the slowest, detail)."""
+    ref = reference_binary()
+    shards = write_fasta_shards(seqs, read_len, n_reads, threads, work_dir)
+    t0 = time.perf_counter()
+    procs = [subprocess.Popen([ref, "search-fmin", "-i", index_prefix, "-q", p, "-o", p + ".out"], stdout=subprocess.DEVNULL,
+                              stderr=subprocess.PIPE, text=True) for p, _ in shards]
+    logs = [pr.communicate()[1] for pr in procs]
+    wall = time.perf_counter() - t0
+    for pr in procs:
+        if pr.returncode != 0:
+            raise RuntimeError("reference search-fmin failed: " + logs[0][-500:])
+    kmers = sum(n for _, n in shards) * (read_len - k + 1)
+    us = [float(m.group(1)) for log in logs for m in re.finditer(r"us/query: ([0-9.]+) \(excluding", log)]
+    for p, _ in shards:
+        for f in (p, p + ".out"):
+            if os.path.exists(f):
+                os.remove(f)
+    for junk in (index_prefix + ".stats", index_prefix + "stats.txt"):
+        if os.path.exists(junk):
+            os.remove(junk)
+    return kmers / wall, {"wall_s": wall, "kmers": kmers, "processes": len(shards),
+                          "ref_us_per_kmer_excl_io": float(np.mean(us)) if us else None}
+
+
+def oracle_port_sample(index_prefix, seqs, offs, n_reads):
+    import helpers as H
+
+    orc = H.Oracle(index_prefix)
+    t0 = time.perf_counter()
+    _, c = orc.search_reads(seqs[: int(offs[n_reads])], offs[: n_reads + 1])
+    wall = time.perf_counter() - t0
+    return int(c[3]) / wall, {"wall_s": wall, "kmers": int(c[3]), "processes": 1}
+
+
+def cpu_baseline(index_prefix, ds, args, all_threads, sample_reads=None):
+    seqs, offs = ds["reads"]
+    threads = cpu_threads() if all_threads else 1
+    per_core_rate = 1.0e6  # k-mers/s, survey figure; only sizes the sample
+    if not sample_reads:
+        sample_reads = int(min(args.reads, max(2000, 15 * per_core_rate * threads / (args.read_len - args.k + 1))))
+    if reference_binary():
+        v, detail = run_reference_sample(index_prefix, seqs, args.read_len, args.k, sample_reads, threads, ds["dir"])
+        kind = "reference"
+    else:
+        v, detail = oracle_port_sample(index_prefix, seqs, offs, min(sample_reads, 100_000))
+        kind, threads = "port", 1
+    return {"value": v, "unit": UNIT, "cores": threads, "kind": kind,
+            "sample": f"first {sample_reads} reads of the workload ({detail['kmers']} k-mer positions) in {detail['processes']} "
+                      f"process(es), wall {detail['wall_s']:.1f} s incl. index load and text output",
+            "detail": detail}
+
+
+# ---------------------------------------------------------------------------------------------------------
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        reference_arm(args)
+        return
+
+    import torch
+    import torch.distributed as dist
+
+    import finito_b200 as fb
+
+    if not torch.cuda.is_available() or fb.device_count() < 1:
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    ds = dataset(args, rank)
+    prefix = os.path.join(ds["dir"], "index")
+    if not os.path.exists(prefix + ".FBV.sdsl"):
+        t0 = time.perf_counter()
+        fb.build_fmin(ds["sbwt"], ds["unitigs"], prefix, device=local_rank)
+        build_s = time.perf_counter() - t0
+    else:
+        build_s = None
+    ix = fb.FinimizerIndex.load(prefix, device=local_rank)
+    info = ix.info
+    seqs, offs = ds["reads"]
+    n_reads = args.reads
+    n_bases = int(offs[-1])
+    kmers_per_step = n_reads * (args.read_len - args.k + 1)
+
+    # ---- device-resident arm
+    d_seqs = torch.from_numpy(seqs).cuda()
+    d_offs = torch.from_numpy(offs.astype(np.int64)).cuda()
+    d_out = torch.empty((kmers_per_step, 2), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+
+    def device_step():
+        c, ms = ix.search_device(d_seqs.data_ptr(), d_offs.data_ptr(), n_reads, n_bases, kmers_per_step, d_out.data_ptr(), 4)
+        return c, ms, ix.last_timing()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    launches0 = fb.launch_count()
+    for _ in range(args.warmup):
+        device_step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches1 = fb.launch_count()
+    pipeline_ms, search_ms = [], []
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        counts, ms, tm = device_step()
+        pipeline_ms.append(ms)
+        search_ms.append(tm["search_kernel_ms"])
+    barrier()
+    wall_dev = time.perf_counter() - t0
+    gpu_launches = fb.launch_count() - launches1
+    dev_total_ms = float(sum(pipeline_ms))
+
+    # ---- end-to-end arm: pinned host buffers through fin_search_batch32
+    h_seqs = torch.empty(n_bases, dtype=torch.uint8).pin_memory()
+    h_seqs.numpy()[:] = seqs
+    h_out = torch.empty((kmers_per_step, 2), dtype=torch.int32).pin_memory()
+    h_seqs_np, h_out_np = h_seqs.numpy(), h_out.numpy()
+    for _ in range(min(args.warmup, 2)):
+        ix.search_batch((h_seqs_np, offs), hit_bits=32, out=h_out_np)
+    barrier()
+    e2e_times = []
+    for _ in range(args.steps):
+        t1 = time.perf_counter()
+        _, c_e2e = ix.search_batch((h_seqs_np, offs), hit_bits=32, out=h_out_np)
+        e2e_times.append(time.perf_counter() - t1)
+    barrier()
+    clocks = None
+    sampler.stop_flag.set()
+    sampler.join(timeout=3)
+    clocks = sampler.summary()
+    e2e_total = float(sum(e2e_times))
+    assert c_e2e.positive == counts.positive
+
+    # ---- max over ranks
+    if world > 1:
+        t = torch.tensor([dev_total_ms, e2e_total, wall_dev], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_total_ms, e2e_total, wall_dev = (float(x) for x in t.cpu())
+    value = world * kmers_per_step * args.steps / (dev_total_ms / 1e3)
+    e2e_value = world * kmers_per_step * args.steps / e2e_total
+
+    if rank == 0:
+        # ---- roofline of the dominant kernel (search_reads_kernel): algorithmic bytes from the access counters
+        sample = min(n_reads, 1_000_000)
+        ix.set_counting(True)
+        ix.search_device(d_seqs.data_ptr(), d_offs.data_ptr(), sample, sample * args.read_len, sample * (args.read_len - args.k + 1),
+                         d_out.data_ptr(), 4)
+        acc = ix.access_counters()
+        ix.set_counting(False)
+        scale = n_reads / sample
+        bytes_per_launch = algorithmic_bytes({k_: v * scale for k_, v in acc.items()}, n_bases, kmers_per_step)
+        avg_search_s = float(np.mean(search_ms)) / 1e3
+        peak, peak_src = measured_peak()
+        achieved = bytes_per_launch / avg_search_s / 1e9
+        traffic = profiled_traffic()
+        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": traffic["dram_bytes_per_launch"] if traffic else None,
+                    "kernel": "search_reads_kernel", "kernel_ms": avg_search_s * 1e3, "kernel_share_of_step": float(np.sum(search_ms)) / dev_total_ms if world == 1 else None,
+                    "algorithmic_bytes_per_launch": bytes_per_launch, "algorithmic_bytes_per_kmer": bytes_per_launch / kmers_per_step,
+                    "peak_source": peak_src,
+                    "note": f"index is {info['device_bytes'] / 1e6:.1f} MB (L2-resident at this config): the sector model counts every access as HBM traffic"}
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            cpu = cpu_baseline(prefix, ds, args, all_threads=False, sample_reads=args.cpu_sample_reads)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": workload_name(args), "k": args.k, "t": 1, "type": "rarest", "reads_per_gpu_per_step": n_reads,
+                       "kmers_per_gpu_per_step": kmers_per_step, "found_fraction": counts.positive / counts.n_queries,
+                       "index_nodes": info["n_nodes"], "index_device_bytes": info["device_bytes"], "parallelism": f"reads sharded x{world}, index replicated, no collective",
+                       "l2": "per-step inputs+outputs (1.5 GB reads, 9.6 GB hits at the default size) exceed the 126 MB L2; the index itself is L2-resident by design of this config",
+                       "index_build_s": build_s},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n_bases + 8 * (n_reads + 1)),
+                    "d2h_bytes_per_step": int(kmers_per_step * 8), "ms_per_step": e2e_total / args.steps * 1e3,
+                    "api": "fin_search_batch32 (pinned host buffers, 3-stream sub-batch pipeline)"},
+            "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "wall_s_device_arm": wall_dev,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def reference_arm(args):
+    """The reference's own CPU implementation on this box's host cores; each step = a bounded sample."""
+    ds = dataset(args, 0)
+    prefix = os.path.join(ds["dir"], "index")
+    if not os.path.exists(prefix + ".FBV.sdsl"):
+        # the index files are inputs of the timed path; any builder that writes the reference's format will do
+        ref = reference_binary()
+        if ref:
+            r = subprocess.run([ref, "build-fmin", "-o", prefix, "-i", ds["sbwt"], "-u", ds["unitigs"]], capture_output=True, text=True)
+            if r.returncode != 0:
+                raise SystemExit("reference build-fmin failed: " + r.stderr[-500:])
+        else:
+            import helpers as H
+
+            H.oracle_build(ds["sbwt"], ds["unitigs"], prefix)
+    values, last = [], None
+    n_runs = args.warmup + args.steps
+    budget_s = 150.0 / max(1, n_runs)  # whole run within a few minutes
+    threads = cpu_threads()
+    sample = int(min(args.reads, max(2000, budget_s * 0.9e6 * threads / (args.read_len - args.k + 1))))
+    for i in range(n_runs):
+        last = cpu_baseline(prefix, ds, args, all_threads=True, sample_reads=sample)
+        if i >= args.warmup:
+            values.append(last["value"])
+    v = float(np.mean(values))
+    kmers = last["detail"]["kmers"]
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": kmers / v * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u64", "data": "synthetic",
+            "config": {"workload": workload_name(args), "k": args.k, "t": 1, "type": "rarest", "step": last["sample"]},
+            "cpu_baseline": {k_: last[k_] for k_ in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    line["cpu_baseline"]["value"] = v
+    print(json.dumps(line))
+
+
+if __name__ == "__main__":
+    main()

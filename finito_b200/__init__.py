@@ -45,6 +45,10 @@ class _Access(C.Structure):
                  "n_kmers")]
 
 
+class _Timing(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("pipeline_ms", "prepare_ms", "search_kernel_ms")]
+
+
 # every symbol include/finito_b200.h declares: name -> (restype, argtypes)
 _u64p = C.POINTER(C.c_uint64)
 ABI = {
@@ -64,6 +68,8 @@ ABI = {
     "fin_search_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p,
                                     C.c_int, C.POINTER(_Counts), C.POINTER(C.c_float)]),
     "fin_search_access_counters": (C.c_int, [C.c_void_p, C.POINTER(_Access)]),
+    "fin_search_set_counting": (C.c_int, [C.c_void_p, C.c_int]),
+    "fin_search_last_timing": (C.c_int, [C.c_void_p, C.POINTER(_Timing)]),
     "fin_launch_count": (C.c_uint64, []),
     "fin_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "fin_host_free": (None, [C.c_void_p]),
@@ -196,6 +202,14 @@ class FinimizerIndex:
         _check(lib().fin_search_device(self._h, d_seqs, d_offsets, n_reads, n_bases, total_kmers, d_out, hit_bytes,
                                        C.byref(c), C.byref(ms)))
         return SearchCounts(c.found_fwd, c.found_rc, c.positive, c.n_queries), float(ms.value)
+
+    def set_counting(self, enabled: bool) -> None:
+        _check(lib().fin_search_set_counting(self._h, int(enabled)))
+
+    def last_timing(self) -> dict:
+        t = _Timing()
+        _check(lib().fin_search_last_timing(self._h, C.byref(t)))
+        return {n: float(getattr(t, n)) for n, _ in _Timing._fields_}
 
     def access_counters(self) -> dict:
         a = _Access()

@@ -118,6 +118,20 @@ fin_status fin_search_access_counters(const fin_index* index, fin_access_counter
     });
 }
 
+fin_status fin_search_set_counting(fin_index* index, int enabled) {
+    return guarded([&] {
+        require(index != nullptr, "fin_search_set_counting: null argument");
+        index->dev->count_accesses = enabled != 0;
+    });
+}
+
+fin_status fin_search_last_timing(const fin_index* index, fin_search_timing* out) {
+    return guarded([&] {
+        require(index && out, "fin_search_last_timing: null argument");
+        *out = index->dev->last_timing;
+    });
+}
+
 uint64_t fin_launch_count(void) { return fin::g_launches; }
 
 fin_status fin_host_alloc(size_t bytes, void** out) {

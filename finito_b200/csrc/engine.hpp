@@ -68,6 +68,7 @@ class DeviceIndex {
                        uint64_t total_kmers, void* d_out, int hit_bytes, fin_search_counts* counts, float* kernel_ms);
     fin_access_counters last_access{};
     bool count_accesses = false;
+    fin_search_timing last_timing{};
 
    private:
     int device_;

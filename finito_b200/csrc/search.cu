@@ -118,7 +118,7 @@ static void launch_search_t(const IndexView& v, const uint64_t* packed, const ui
 static void launch_pipeline(const IndexView& v, const uint8_t* d_ascii, uint64_t n_bases, const uint64_t* d_offsets,
                             uint64_t n_reads, uint64_t* d_packed, uint64_t* d_out_offsets, void* d_scan_tmp,
                             size_t scan_tmp_bytes, void* d_out, int hit_bytes, SearchTotals* d_totals, bool count,
-                            int n_strands, cudaStream_t st) {
+                            int n_strands, cudaStream_t st, cudaEvent_t before_search = nullptr) {
     if (n_reads == 0) return;
     const uint64_t n_words = (n_bases + 31) / 32 + 1;
     {
@@ -133,6 +133,7 @@ static void launch_pipeline(const IndexView& v, const uint8_t* d_ascii, uint64_t
     }
     FIN_CUDA(cub::DeviceScan::ExclusiveSum(d_scan_tmp, scan_tmp_bytes, d_out_offsets, d_out_offsets, (int64_t)n_reads, st));
     g_launches += 2;
+    if (before_search) FIN_CUDA(cudaEventRecord(before_search, st));
     if (hit_bytes == 4) {
         if (count) launch_search_t<int32_t, true>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, n_strands, st);
         else launch_search_t<int32_t, false>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, n_strands, st);
@@ -188,20 +189,26 @@ void DeviceIndex::search_device(const void* d_seqs, const uint64_t* d_read_offse
     dev_scan_tmp_.ensure(tmp);
     dev_totals_.ensure(sizeof(SearchTotals));
     FIN_CUDA(cudaMemsetAsync(dev_totals_.p, 0, sizeof(SearchTotals), 0));
-    cudaEvent_t e0, e1;
+    cudaEvent_t e0, e1, em;
     FIN_CUDA(cudaEventCreate(&e0));
     FIN_CUDA(cudaEventCreate(&e1));
+    FIN_CUDA(cudaEventCreate(&em));
     FIN_CUDA(cudaEventRecord(e0, 0));
+    if (n_reads == 0) FIN_CUDA(cudaEventRecord(em, 0));
     launch_pipeline(view_, (const uint8_t*)d_seqs, n_bases, d_read_offsets, n_reads, dev_packed_.p, dev_out_offsets_.p,
-                    dev_scan_tmp_.p, tmp, d_out, hit_bytes, (SearchTotals*)dev_totals_.p, count_accesses, 2, 0);
+                    dev_scan_tmp_.p, tmp, d_out, hit_bytes, (SearchTotals*)dev_totals_.p, count_accesses, 2, 0, em);
     FIN_CUDA(cudaEventRecord(e1, 0));
     SearchTotals t;
     FIN_CUDA(cudaMemcpy(&t, dev_totals_.p, sizeof t, cudaMemcpyDeviceToHost));
     FIN_CUDA(cudaEventSynchronize(e1));
     float ms = 0;
     FIN_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    last_timing.pipeline_ms = ms;
+    FIN_CUDA(cudaEventElapsedTime(&last_timing.prepare_ms, e0, em));
+    FIN_CUDA(cudaEventElapsedTime(&last_timing.search_kernel_ms, em, e1));
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
+    cudaEventDestroy(em);
     if (kernel_ms) *kernel_ms = ms;
     check_flags(t.error_flags);
     fin_search_counts c{};

@@ -111,11 +111,20 @@ fin_status fin_search_device(fin_index* index, const void* d_seqs, const uint64_
                              fin_search_counts* counts, float* kernel_ms);
 
 /* Access counters of the last search call on this handle, the ones SURVEY.md section 8(d) builds the
- * algorithmic-bytes figure from (only filled by a library built with -DFIN_COUNTERS=1, else zeros). */
+ * algorithmic-bytes figure from.  They are only tallied while counting is enabled (fin_search_set_counting,
+ * or FIN_COUNTERS=1 in the environment at load time): the counting kernel variant is slower. */
 typedef struct fin_access_counters {
     int64_t n_rank, n_lcs_reads, n_ustart_reads, n_anchor, n_anchor_branch, n_walk_words, n_bases, n_kmers;
 } fin_access_counters;
 fin_status fin_search_access_counters(const fin_index* index, fin_access_counters* out);
+fin_status fin_search_set_counting(fin_index* index, int enabled);
+
+/* CUDA-event times of the last fin_search_device call: the whole pipeline, the preparation kernels
+ * (2-bit packing, k-mer counts, output offsets) and the streaming-search kernel alone. */
+typedef struct fin_search_timing {
+    float pipeline_ms, prepare_ms, search_kernel_ms;
+} fin_search_timing;
+fin_status fin_search_last_timing(const fin_index* index, fin_search_timing* out);
 
 /* Number of kernel launches issued by this library on this thread's handles since load (bench.py's
  * gpu_launches claim is read from here). */
