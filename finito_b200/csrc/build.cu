@@ -87,12 +87,9 @@ static void build_rarest(SbwtHost&& sbwt, PackedVec&& lcs_file, const SeqBatch& 
     if (lcs_file.size() != N) throw format_error("LCS length differs from the number of SBWT columns");
     check_unitigs(unitigs, k);
 
-    DevBuf<uint64_t> d_matrix = to_device(matrix_sectors(sbwt));
-    DevBuf<uint8_t> d_lcs = to_device(lcs_bytes(lcs_file));
+    DevBuf<uint64_t> d_lines = to_device(make_lines(sbwt, &lcs_file, nullptr, nullptr));
     IndexView ix{};
-    ix.matrix = reinterpret_cast<const ulonglong2*>(d_matrix.p);
-    ix.lcs = d_lcs.p;
-    for (int c = 0; c < 4; c++) ix.C[c] = (idx_t)sbwt.C[c];
+    ix.lines = reinterpret_cast<const uint4*>(d_lines.p);
     ix.n_nodes = (idx_t)N;
     ix.k = k;
 

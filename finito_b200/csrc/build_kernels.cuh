@@ -156,7 +156,7 @@ FIN_D void build_stream_chunk(const IndexView& ix, const uint64_t* __restrict__ 
                 // candidate ends are kept relative to the chunk so that they fit the 24-bit field
                 cur = cand_pack((int)(end - start + 1), I.l, (int)s);
                 start++;
-                I = drop_first_char<false>(ix, (int)(end - start + 1), I, dummy);
+                I = drop_first_char<(KCAP > 128), false>(ix, (int)(end - start + 1), I, dummy);
             } while (I.l == I.r);
             while (dq_n > 0 && (int64_t)ch.first_pos + cand_start(dq[dq_head]) < kmer) {
                 dq_head = (dq_head + 1) & (KCAP - 1);

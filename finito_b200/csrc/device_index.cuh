@@ -1,15 +1,22 @@
 // Device-resident layout of the FinimizerIndex and the device functions every kernel shares.
 //
 // Layout (all little-endian, all arrays padded so that position n itself is addressable):
-//   rank sectors — the unit is one 32-byte sector {u64 ones_before_block, u64 bits[3]} covering a block of
-//                  192 bit positions.  One rank = one sector + at most three masked popcounts.
-//       subset matrix : sector (4*block + c) for c in A,C,G,T, so the four rows of a block share one
-//                       128-byte line (replaces 4 x sdsl::bit_vector + 4 x rank_support_v5,
-//                       SBWT/include/sbwt/SubsetMatrixRank.hh:18-37, sdsl/rank_support_v5.hpp:116-134)
-//       Ustart, fmin  : sector (block)                 (FinimizerIndex.hh:111-115; rank rebuilt at load :219,:235)
-//       tstart        : sector (block) over TEXT positions, bit set at the first base of every unitig;
-//                       rank replaces std::upper_bound over unitigs.ends (PackedStrings.hh:91-100)
-//   lcs     — one byte per SBWT column (k <= 255)      (sdsl::int_vector<> LCS, FinimizerIndex.hh:109)
+//   lines   — one 128-byte line per 64 SBWT columns; everything the streaming search touches for a column
+//             interval lives in the line(s) of that interval, so one step of a chain costs one new line:
+//               bytes   0..63  four 16-byte rows, one per A,C,G,T:
+//                              {u64 bits of the row for these 64 columns,
+//                               u32 C[c] + ones of the row before the line,
+//                               u32 extra: row A/C = Ustart bits 0..31 / 32..63, row G/T = fmin bits 0..31 / 32..63}
+//               bytes 64..127  LCS of the 64 columns, one byte each (k <= 255)
+//             rank_c(p) and with it SBWT::update_sbwt_interval is ONE 16-byte load and a popcount
+//             (replaces 4 x sdsl::bit_vector + 4 x rank_support_v5 + the C array,
+//              SBWT/include/sbwt/SubsetMatrixRank.hh:18-37, sdsl/rank_support_v5.hpp:116-134, SBWT.hh:355-370;
+//              the LCS int_vector, FinimizerIndex.hh:109; the Ustart bit test of common.hh:167)
+//   rank sectors — one 32-byte sector {u64 ones_before_block, u64 bits[3]} per 192 bit positions, for the
+//             three rank queries of the (rare) anchor lookups:
+//       ustart, fmin : over SBWT columns            (FinimizerIndex.hh:111-115; rank rebuilt at load :219,:235)
+//       tstart       : over TEXT positions, bit set at the first base of every unitig; its rank replaces
+//                      std::upper_bound over unitigs.ends (PackedStrings.hh:91-100)
 //   offsets — u32 per finimizer, in column order       (global_offsets, FinimizerIndex.hh:113)
 //   ends    — u32 exclusive end of every unitig        (unitigs.ends, PackedStrings.hh:29)
 //   text    — 2 bits per base, 32 bases per u64, same bit order as sdsl::int_vector<2> (PackedStrings.hh:28)
@@ -30,17 +37,19 @@ namespace fin {
 typedef uint32_t idx_t;  // SBWT column / text position.  This build supports n_nodes, text_len < 2^32 - 256.
 
 constexpr int kRankBlockBits = 192;
+constexpr int kLineColumns = 64;   // columns per 128-byte line
+constexpr int kLineU4 = 8;         // uint4 per line
+constexpr int kLineU64 = 16;       // u64 per line
+constexpr int kLineLcsU64 = 8;     // first u64 of the LCS half of a line
 
 struct IndexView {
-    const ulonglong2* __restrict__ matrix;  // 2 x ulonglong2 per sector, 4 sectors per block
+    const uint4* __restrict__ lines;        // 8 x uint4 per line
     const ulonglong2* __restrict__ ustart;  // 2 x ulonglong2 per sector
     const ulonglong2* __restrict__ fmin;
     const ulonglong2* __restrict__ tstart;
-    const uint8_t* __restrict__ lcs;
     const uint32_t* __restrict__ offsets;
     const uint32_t* __restrict__ ends;
     const uint64_t* __restrict__ text;
-    idx_t C[4];
     idx_t n_nodes;
     idx_t text_len;
     uint32_t n_unitigs;
@@ -72,38 +81,37 @@ FIN_D uint32_t rank1(const ulonglong2* __restrict__ sectors, idx_t p) {
     return sector_count(a, b, q);
 }
 
-FIN_D bool bit1(const ulonglong2* __restrict__ sectors, idx_t p) {
-    const idx_t blk = p / kRankBlockBits;
-    const int q = (int)(p - blk * kRankBlockBits);
-    const uint64_t* w = reinterpret_cast<const uint64_t*>(sectors + 2 * (size_t)blk);
-    return (__ldg(w + 1 + (q >> 6)) >> (q & 63)) & 1ULL;
+// C[c] + rank_c(p): the column the edge labelled c out of the first column >= p leads to
+FIN_D idx_t step_c(const IndexView& ix, const idx_t p, const int c) {
+    const uint4 row = __ldg(ix.lines + (size_t)(p >> 6) * kLineU4 + c);
+    const uint64_t bits = (uint64_t)row.x | ((uint64_t)row.y << 32);
+    return row.z + (idx_t)__popcll(bits & ((1ULL << (p & 63)) - 1ULL));
 }
 
 // SBWT::update_sbwt_interval for one character (SBWT/include/sbwt/SBWT.hh:355-370):
-// I' = [C[c] + rank_c(l), C[c] + rank_c(r+1) - 1].  Both ranks come from one sector when l and r+1
-// share a 192-column block, which is the common case once the interval is narrow.
+// I' = [C[c] + rank_c(l), C[c] + rank_c(r+1) - 1].  Two 16-byte loads, the same 32-byte sector whenever l and
+// r+1 share a line, which is the common case once the interval is narrow.
 FIN_D Ival extend(const IndexView& ix, const Ival I, const int c) {
-    const idx_t lp = I.l, rp = I.r + 1;
-    const idx_t bl = lp / kRankBlockBits, br = rp / kRankBlockBits;
-    const ulonglong2* sl = ix.matrix + 2 * ((size_t)bl * 4 + c);
-    const ulonglong2 a = __ldg(sl), b = __ldg(sl + 1);
-    const uint32_t rl = sector_count(a, b, (int)(lp - bl * kRankBlockBits));
-    uint32_t rr;
-    if (br == bl) {
-        rr = sector_count(a, b, (int)(rp - br * kRankBlockBits));
-    } else {
-        const ulonglong2* sr = ix.matrix + 2 * ((size_t)br * 4 + c);
-        const ulonglong2 a2 = __ldg(sr), b2 = __ldg(sr + 1);
-        rr = sector_count(a2, b2, (int)(rp - br * kRankBlockBits));
-    }
     Ival J;
-    J.l = ix.C[c] + rl;
-    J.r = ix.C[c] + rr - 1;  // rr == rl gives r == l - 1: empty
+    J.l = step_c(ix, I.l, c);
+    J.r = step_c(ix, I.r + 1, c) - 1;  // equal ranks give r == l - 1: empty
     return J;
 }
 
 // C[c] >= 1 (SBWT.hh:279), so an empty result has l = r + 1 without wrap-around
 FIN_D bool is_empty(const Ival I) { return I.l > I.r; }
+
+// Ustart[p] (common.hh:167) from the line of p
+FIN_D bool ustart_bit(const IndexView& ix, const idx_t p) {
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(ix.lines + (size_t)(p >> 6) * kLineU4 + ((p >> 5) & 1));
+    return (__ldg(w + 3) >> (p & 31)) & 1u;
+}
+
+// LCS[p] from the line of p (build kernels; the search uses the word-parallel drop_step below)
+FIN_D int lcs_at(const IndexView& ix, const idx_t p) {
+    const uint8_t* b = reinterpret_cast<const uint8_t*>(ix.lines + (size_t)(p >> 6) * kLineU4);
+    return (int)__ldg(b + 64 + (p & 63));
+}
 
 #endif  // __CUDACC__ || FIN_EMU
 

@@ -75,8 +75,7 @@ class DeviceIndex {
     IndexView view_{};
     fin_index_info info_{};
     bool fits32_ = true;
-    DevBuf<uint64_t> matrix_, ustart_, fmin_, tstart_, text_;
-    DevBuf<uint8_t> lcs_;
+    DevBuf<uint64_t> lines_, ustart_, fmin_, tstart_, text_;
     DevBuf<uint32_t> offsets_, ends_;
     std::vector<std::unique_ptr<SearchSlot>> slots_;
     // scratch of search_device

@@ -75,22 +75,40 @@ inline void save_index_files(const IndexHost& ix, const std::string& prefix) {  
     if (fclose(f) != 0 || !ok) throw io_error("short write on " + path);
 }
 
-inline std::vector<uint64_t> matrix_sectors(const SbwtHost& s) {
-    const uint64_t* rows[4] = {s.bits[0].words.data(), s.bits[1].words.data(), s.bits[2].words.data(), s.bits[3].words.data()};
-    return make_rank_sectors(rows, 4, (uint64_t)s.n_nodes);
-}
-
-inline std::vector<uint8_t> lcs_bytes(const PackedVec& lcs) {
-    const uint64_t n = lcs.size();
-    std::vector<uint8_t> l(n + 64, 0);
-    for (uint64_t i = 0; i < n; i++) l[i] = (uint8_t)lcs.get(i);
-    return l;
+// The 128-byte lines of device_index.cuh: per 64 columns four rows {u64 bits, u32 C[c] + ones before, u32 extra}
+// followed by 64 LCS bytes.  lcs / ustart / fmin may be null (build-fmin streams before they exist): zeros then.
+// (N >> 6) + 2 lines, so that column N (rank of the whole vector, LCS pad = 0) is addressable.
+inline std::vector<uint64_t> make_lines(const SbwtHost& s, const PackedVec* lcs, const PackedVec* ustart, const PackedVec* fmin) {
+    const uint64_t N = (uint64_t)s.n_nodes;
+    const uint64_t n_lines = (N >> 6) + 2;
+    const uint64_t n_words = (N + 63) >> 6;
+    const uint64_t tail_bits = N & 63;
+    std::vector<uint64_t> L(n_lines * 16, 0);
+    uint64_t cum[4] = {(uint64_t)s.C[0], (uint64_t)s.C[1], (uint64_t)s.C[2], (uint64_t)s.C[3]};
+    for (uint64_t b = 0; b < n_lines; b++) {
+        uint64_t* line = &L[b * 16];
+        const uint64_t us = ustart && b < n_words ? ustart->words[b] : 0;
+        const uint64_t fm = fmin && b < n_words ? fmin->words[b] : 0;
+        const uint32_t extra[4] = {(uint32_t)us, (uint32_t)(us >> 32), (uint32_t)fm, (uint32_t)(fm >> 32)};
+        for (int c = 0; c < 4; c++) {
+            uint64_t x = b < n_words ? s.bits[c].words[b] : 0;
+            if (tail_bits && b == n_words - 1) x &= (1ULL << tail_bits) - 1;  // bits past the end never count
+            line[2 * c] = x;
+            line[2 * c + 1] = (cum[c] & 0xFFFFFFFFull) | ((uint64_t)extra[c] << 32);
+            cum[c] += (uint64_t)__builtin_popcountll(x);
+        }
+        if (lcs) {
+            uint8_t* lb = reinterpret_cast<uint8_t*>(line + 8);
+            const uint64_t i0 = b * 64, i1 = std::min(N, i0 + 64);
+            for (uint64_t i = i0; i < i1; i++) lb[i - i0] = (uint8_t)lcs->get(i);
+        }
+    }
+    return L;
 }
 
 // Arrays in exactly the form the kernels read them (see device_index.cuh for the meaning of each).
 struct HostLayout {
-    std::vector<uint64_t> matrix, ustart, fmin, tstart, text;
-    std::vector<uint8_t> lcs;
+    std::vector<uint64_t> lines, ustart, fmin, tstart, text;
     std::vector<uint32_t> offsets, ends;
     uint64_t n_nodes = 0, text_len = 0, n_unitigs = 0, n_fmin = 0, max_unitig_len = 0;
     int64_t C[4] = {0, 0, 0, 0};
@@ -107,7 +125,7 @@ inline HostLayout build_host_layout(const IndexHost& h) {
     L.n_nodes = N; L.text_len = T; L.n_unitigs = U; L.n_fmin = F;
     L.k = h.sbwt.k; L.n_kmers = h.sbwt.n_kmers;
     for (int c = 0; c < 4; c++) L.C[c] = h.sbwt.C[c];
-    L.matrix = matrix_sectors(h.sbwt);
+    L.lines = make_lines(h.sbwt, &h.lcs, &h.ustart, &h.fmin);
     {
         const uint64_t* r[1] = {h.ustart.words.data()};
         L.ustart = make_rank_sectors(r, 1, N);
@@ -131,7 +149,6 @@ inline HostLayout build_host_layout(const IndexHost& h) {
         const uint64_t* r[1] = {ts.data()};
         L.tstart = make_rank_sectors(r, 1, T);
     }
-    L.lcs = lcs_bytes(h.lcs);
     L.offsets.assign(F + 1, 0);
     for (uint64_t i = 0; i < F; i++) {
         const uint64_t v = h.offsets.get(i);

@@ -50,24 +50,21 @@ DeviceIndex::DeviceIndex(const IndexHost& h, int device) : device_(device) {
     FIN_CUDA(cudaSetDevice(device));
 
     const HostLayout L = build_host_layout(h);
-    matrix_ = upload(L.matrix.data(), L.matrix.size());
+    lines_ = upload(L.lines.data(), L.lines.size());
     ustart_ = upload(L.ustart.data(), L.ustart.size());
     fmin_ = upload(L.fmin.data(), L.fmin.size());
     tstart_ = upload(L.tstart.data(), L.tstart.size());
     text_ = upload(L.text.data(), L.text.size());
-    lcs_ = upload(L.lcs.data(), L.lcs.size());
     offsets_ = upload(L.offsets.data(), L.offsets.size());
     ends_ = upload(L.ends.data(), L.ends.size());
 
-    view_.matrix = reinterpret_cast<const ulonglong2*>(matrix_.p);
+    view_.lines = reinterpret_cast<const uint4*>(lines_.p);
     view_.ustart = reinterpret_cast<const ulonglong2*>(ustart_.p);
     view_.fmin = reinterpret_cast<const ulonglong2*>(fmin_.p);
     view_.tstart = reinterpret_cast<const ulonglong2*>(tstart_.p);
-    view_.lcs = lcs_.p;
     view_.offsets = offsets_.p;
     view_.ends = ends_.p;
     view_.text = text_.p;
-    for (int c = 0; c < 4; c++) view_.C[c] = (idx_t)L.C[c];
     view_.n_nodes = (idx_t)L.n_nodes;
     view_.text_len = (idx_t)L.text_len;
     view_.n_unitigs = (uint32_t)L.n_unitigs;
@@ -82,7 +79,7 @@ DeviceIndex::DeviceIndex(const IndexHost& h, int device) : device_(device) {
     info_.text_len = (int64_t)L.text_len;
     info_.n_finimizers = (int64_t)L.n_fmin;
     info_.device = device;
-    info_.device_bytes = (int64_t)(matrix_.bytes() + ustart_.bytes() + fmin_.bytes() + tstart_.bytes() + lcs_.bytes() +
+    info_.device_bytes = (int64_t)(lines_.bytes() + ustart_.bytes() + fmin_.bytes() + tstart_.bytes() +
                                    offsets_.bytes() + ends_.bytes() + text_.bytes());
     const char* e = getenv("FIN_COUNTERS");
     count_accesses = e && *e && *e != '0';
@@ -98,20 +95,38 @@ DeviceIndex::~DeviceIndex() {
 // -------------------------------------------------------------------------------------------------------
 static int window_capacity(int k) { return k <= 32 ? 32 : k <= 64 ? 64 : k <= 128 ? 128 : 256; }
 
+// persistent grid: as many blocks as are resident at once (148 SMs x blocks per SM), never more than the reads need
+template <int KCAP, class HitT, bool COUNT>
+static void launch_search_k(const IndexView& v, const uint64_t* packed, const uint64_t* offsets, uint64_t n_reads,
+                            const uint64_t* out_offsets, HitPair<HitT>* o, SearchTotals* totals, int n_strands, cudaStream_t st) {
+    const int threads = 128;
+    static thread_local int resident[64] = {0};  // per device
+    int dev = 0;
+    FIN_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) throw arg_error("CUDA device ordinal out of range");
+    if (!resident[dev]) {
+        int per_sm = 0, sms = 0;
+        FIN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, search_reads_kernel<KCAP, HitT, COUNT>, threads, 0));
+        FIN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        resident[dev] = std::max(1, per_sm) * std::max(1, sms);
+    }
+    const uint64_t need = (n_reads + threads - 1) / threads;
+    const unsigned blocks = (unsigned)std::min<uint64_t>(need, (uint64_t)resident[dev]);
+    search_reads_kernel<KCAP, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands);
+    g_launches++;
+    FIN_CUDA(cudaGetLastError());
+}
+
 template <class HitT, bool COUNT>
 static void launch_search_t(const IndexView& v, const uint64_t* packed, const uint64_t* offsets, uint64_t n_reads,
                             const uint64_t* out_offsets, void* out, SearchTotals* totals, int n_strands, cudaStream_t st) {
-    const unsigned threads = 128;
-    const unsigned blocks = (unsigned)((n_reads + threads - 1) / threads);
     HitPair<HitT>* o = reinterpret_cast<HitPair<HitT>*>(out);
     switch (window_capacity(v.k)) {
-        case 32: search_reads_kernel<32, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands); break;
-        case 64: search_reads_kernel<64, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands); break;
-        case 128: search_reads_kernel<128, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands); break;
-        default: search_reads_kernel<256, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands); break;
+        case 32: launch_search_k<32, HitT, COUNT>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands, st); break;
+        case 64: launch_search_k<64, HitT, COUNT>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands, st); break;
+        case 128: launch_search_k<128, HitT, COUNT>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands, st); break;
+        default: launch_search_k<256, HitT, COUNT>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands, st); break;
     }
-    g_launches++;
-    FIN_CUDA(cudaGetLastError());
 }
 
 // pack + k-mer counts + exclusive scan + search on one stream; every pointer is device memory

@@ -2,7 +2,9 @@
 //   pack_reads_kernel   : ASCII -> 2 bits per base + validation      (SBWT/include/sbwt/SeqIO.hh:232 upper-casing,
 //                                                                     common.hh:50-58 char_idx, :106-111 validation)
 //   kmer_counts_kernel  : k-mer positions per read                   (search_fmin.hh:69)
-//   search_reads_kernel : one thread streams one read, forward strand then reverse complement:
+//   search_reads_kernel : persistent warps; every lane runs one chain = one read, forward strand then reverse
+//                         complement, as a flattened state machine (struct Chain below) whose iteration is the
+//                         same instruction sequence for every lane whatever its phase:
 //                         rarest_fmin_streaming_search (common.hh:78-186) fused with the resolve loop of
 //                         FinimizerIndex::search (FinimizerIndex.hh:148-183), walk_in_unitigs (:47-102),
 //                         the dictionary lookups (common.hh:61-72), global_offset_to_local_offset
@@ -17,6 +19,7 @@ struct SearchTotals {  // device-side accumulators of one launch
     unsigned long long n_rank, n_lcs_reads, n_ustart_reads, n_anchor, n_anchor_branch, n_walk_words, n_bases, n_kmers;
     unsigned int error_flags;  // bit 0: non-ACGT base; bit 1: candidate window underflow; bit 2: lookup out of range
     unsigned int pad;
+    unsigned long long next_read;  // work counter of the persistent search kernel
 };
 
 enum : unsigned { kErrBadBase = 1u, kErrWindowUnderflow = 2u, kErrLookupRange = 4u, kErrReadTooLong = 8u };
@@ -79,29 +82,84 @@ static __global__ void kmer_counts_kernel(const uint64_t* __restrict__ read_offs
 
 #endif  // __CUDACC__
 
-// ---- drop_first_char (common.hh:38-48) ---------------------------------------------------------------------
-template <bool COUNT>
+
+// ---- drop_first_char (common.hh:38-48), word-parallel ------------------------------------------------------
+// The reference widens l downwards while LCS[l] >= new_len and r upwards while LCS[r+1] >= new_len, one element
+// per iteration.  Here one step inspects the aligned 8-byte LCS word that holds l (resp. r+1) with byte-parallel
+// compares and jumps to the terminating element; a side that runs off its word stays pending for another step.
+// LCS[0] = 0 and the LCS pad past n_nodes is 0, so both scans stop inside the array without bound checks
+// (new_len >= 1 here; new_len <= 0 is the "whole range" case handled by the callers).
+constexpr uint64_t kByteHigh = 0x8080808080808080ULL;
+
+// bit 7 of every byte whose value is < n (1 <= n <= 255).  WIDE = false needs all bytes and n below 129 (k <= 128).
+template <bool WIDE> FIN_D uint64_t bytes_below(const uint64_t x, const int n) {
+    const uint64_t n8 = (uint64_t)(uint32_t)n * 0x0101010101010101ULL;
+    if (!WIDE) {
+        return ~((x | kByteHigh) - n8) & kByteHigh;
+    } else {
+        const uint64_t t = ((x & ~kByteHigh) | kByteHigh) - (n8 & ~kByteHigh);  // bit 7: low 7 bits of x >= those of n
+        const uint64_t xh = x & kByteHigh, nh = n8 & kByteHigh;
+        const uint64_t ge = (xh & ~nh) | (~(xh ^ nh) & t);
+        return ~ge & kByteHigh;
+    }
+}
+
+enum : unsigned { kDropLeft = 1u, kDropRight = 2u };
+
+// One word step on the pending sides of I; returns the sides that are still pending.
+template <bool WIDE, bool COUNT>
+FIN_D unsigned drop_step(const IndexView& ix, Ival& I, const int new_len, const unsigned pend, unsigned& n_lcs) {
+    const uint64_t* __restrict__ lw = reinterpret_cast<const uint64_t*>(ix.lines);
+    unsigned still = 0;
+    if (pend & kDropLeft) {
+        const idx_t l = I.l;
+        const uint64_t w = __ldg(lw + (size_t)(l >> 6) * kLineU64 + kLineLcsU64 + ((l & 63) >> 3));
+        const int j = (int)(l & 7);
+        const uint64_t stop = bytes_below<WIDE>(w, new_len) & (~0ULL >> (8 * (7 - j)));
+        idx_t nl;
+        if (stop) {
+            nl = (l & ~7u) + (idx_t)((63 - __clzll((long long)stop)) >> 3);
+            if (COUNT) n_lcs += (l - nl) + (nl > 0 ? 1u : 0u);
+        } else {  // cannot happen in the word of column 0: LCS[0] = 0
+            nl = (l & ~7u) - 1;
+            if (COUNT) n_lcs += l - nl;
+            still |= kDropLeft;
+        }
+        I.l = nl;
+    }
+    if (pend & kDropRight) {
+        const idx_t rp = I.r + 1;
+        const uint64_t w = __ldg(lw + (size_t)(rp >> 6) * kLineU64 + kLineLcsU64 + ((rp & 63) >> 3));
+        const int j = (int)(rp & 7);
+        const uint64_t stop = bytes_below<WIDE>(w, new_len) & (~0ULL << (8 * j));
+        idx_t nr;
+        if (stop) {
+            nr = (rp & ~7u) + (idx_t)((__ffsll((long long)stop) - 1) >> 3) - 1;
+            if (COUNT) n_lcs += (nr - I.r) + (nr < ix.n_nodes - 1 ? 1u : 0u);
+        } else {
+            nr = (rp & ~7u) + 7;
+            if (COUNT) n_lcs += nr - I.r;
+            still |= kDropRight;
+        }
+        I.r = nr;
+    }
+    return still;
+}
+
+// the whole of drop_first_char, for the callers that are not state machines (build-fmin kernels)
+template <bool WIDE, bool COUNT>
 FIN_D Ival drop_first_char(const IndexView& ix, const int new_len, Ival I, unsigned& n_lcs) {
     if (new_len <= 0) {
         I.l = 0;
         I.r = ix.n_nodes - 1;
         return I;
     }
-    while (I.l > 0) {
-        if (COUNT) n_lcs++;
-        if ((int)__ldg(ix.lcs + I.l) >= new_len) I.l--;
-        else break;
-    }
-    const idx_t last = ix.n_nodes - 1;
-    while (I.r < last) {
-        if (COUNT) n_lcs++;
-        if ((int)__ldg(ix.lcs + I.r + 1) >= new_len) I.r++;
-        else break;
-    }
+    unsigned pend = kDropLeft | kDropRight;
+    while (pend) pend = drop_step<WIDE, COUNT>(ix, I, new_len, pend, n_lcs);
     return I;
 }
 
-template <class HitT> struct HitPair { HitT unitig, pos; };
+template <class HitT> struct alignas(2 * sizeof(HitT)) HitPair { HitT unitig, pos; };
 
 // Candidate finimizers are packed into one u64 so that the unsigned order equals the reference's tuple
 // order (freq, len, colex, end) with freq == 1 throughout (common.hh:84,147): len:8 | colex:32 | end:24.
@@ -115,236 +173,342 @@ FIN_D int cand_start(uint64_t c) { return cand_end(c) - cand_len(c) + 1; }
 
 constexpr int kMaxReadLen = (1 << 24) - 1;
 
-// One read, both strands.  KCAP: power of two >= k, capacity of the candidate window (see DESIGN.md
-// "candidate window": entries are expired eagerly, which is unobservable because candidate starts are
-// non-decreasing along the deque, so at most k live entries exist).
-template <int KCAP, class HitT, bool COUNT>
-FIN_D void search_one_read(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t b0, const uint64_t len64,
-                           HitPair<HitT>* __restrict__ o, ReadCounters& rc, const int n_strands = 2) {
-    unsigned (&found)[2] = rc.found;
-    unsigned &positive = rc.positive, &n_q = rc.n_q, &err = rc.err;
-    unsigned &c_rank = rc.c_rank, &c_lcs = rc.c_lcs, &c_ustart = rc.c_ustart, &c_anchor = rc.c_anchor, &c_branch = rc.c_branch,
-             &c_walk = rc.c_walk, &c_bases = rc.c_bases, &c_kmers = rc.c_kmers;
-    {
-        const int k = ix.k;
-        const idx_t N = ix.n_nodes;
+// ---- one chain = one read, both strands, as a flattened state machine ------------------------------------------
+// The reference's loop nest (per character: contract-and-retry loops for the finimizer interval and the k-mer
+// interval, the shrink loop, the widening loops inside drop_first_char) has data-dependent trip counts: bursts of
+// ~20 contractions after every read error, one or two per character on the strand that does not match.  With one
+// read per lane and the loops as written, a warp waits for its slowest lane at every character (measured: 6.8 of
+// 32 lanes active per instruction).  Here every iteration of ONE loop does, for every lane, the same four things
+//   A  extend        : ranks for I and I_kmer with the current character        (common.hh:114, :133)
+//   B  decide        : Ustart test, set up the shrink drop and the window drop  (:145-154, :167, :170, :181)
+//   F  drop          : one word step of every pending drop_first_char           (common.hh:38-48)
+//   D/E shrink check, candidate window, emission, resolve, next character       (:155-164, :173-182, FinimizerIndex.hh:148-183)
+// and a lane that needs another contraction or another drop word simply spends its next iteration on it while its
+// neighbours move on to their next character: lanes drift apart in position instead of waiting for each other.
+// In the matching region a character costs one iteration.
+enum : int { ST_EXT = 0, ST_EXTK = 1, ST_POST = 2, ST_SHRINK = 3, ST_EMIT = 4, ST_IDLE = 5 };
+
+template <int KCAP, class HitT, bool COUNT> struct Chain {
+    static constexpr bool WIDE = KCAP > 128;
+    // the read
+    uint64_t b0 = 0;
+    HitPair<HitT>* o = nullptr;
+    int len = 0, nk = 0, strand = 0;
+    // stream state (common.hh:80-103)
+    int st = ST_IDLE, end = 0, c = 0;
+    int start = 0, kmer_start = 0;
+    Ival I{0, 0}, Ik{0, 0};
+    uint64_t qword = 0;
+    unsigned pendI = 0, pendK = 0;  // sides of the pending drops
+    int lenI = 0, lenK = 0;         // their new_len
+    bool emit = false;              // a complete k-mer window ends at `end`
+    uint64_t cur = 0;               // the candidate being shrunk
+    int dq_head = 0, dq_n = 0;
+    int bestU_pos = -1;
+    idx_t bestU_col = 0;
+    // walk state (walk_in_unitigs): the last answered k-mer ends at text position walk_g
+    bool walking = false;
+    idx_t walk_g = 0, walk_ustart = 0, walk_uend = 0;
+    uint32_t walk_uid = 0;
+    uint64_t tword = 0;
+    int walk_j = 0;
+    uint64_t dq[KCAP];
+
+    FIN_D void begin_strand(const IndexView& ix, const uint64_t* __restrict__ packed) {
+        start = kmer_start = 0;
+        I.l = 0; I.r = ix.n_nodes - 1;
+        Ik = I;
+        dq_head = dq_n = 0;
+        bestU_pos = -1;
+        walking = false;
+        pendI = pendK = 0;
+        end = 0;
+        fetch_base(packed);
+        st = ST_EXT;
+    }
+
+    FIN_D void fetch_base(const uint64_t* __restrict__ packed) {
+        if (strand == 0) {
+            const uint64_t b = b0 + (uint64_t)end;
+            if (end == 0 || (b & 31) == 0) qword = __ldg(packed + (b >> 5));
+            c = (int)((qword >> (2 * (b & 31))) & 3);
+        } else {
+            const uint64_t b = b0 + (uint64_t)(len - 1 - end);
+            if (end == 0 || (b & 31) == 31) qword = __ldg(packed + (b >> 5));
+            c = 3 - (int)((qword >> (2 * (b & 31))) & 3);
+        }
+    }
+
+    // takes a new read; returns false (and stays idle) when the read has no k-mer
+    FIN_D bool begin_read(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t base, const uint64_t len64,
+                          HitPair<HitT>* out, ReadCounters& rc) {
+        st = ST_IDLE;
         if (len64 > (uint64_t)kMaxReadLen) {
-            err |= kErrReadTooLong;
-        } else if (len64 >= (uint64_t)k) {
-            const int len = (int)len64;
-            const int nk = len - k + 1;
-            n_q = (unsigned)nk;
-            uint64_t dq[KCAP];
+            rc.err |= kErrReadTooLong;
+            return false;
+        }
+        if (len64 < (uint64_t)ix.k) return false;
+        b0 = base;
+        len = (int)len64;
+        nk = len - ix.k + 1;
+        rc.n_q += (unsigned)nk;
+        o = out;
+        strand = 0;
+        begin_strand(ix, packed);
+        return true;
+    }
 
-            for (int strand = 0; strand < n_strands; strand++) {
-                int start = 0, kmer_start = 0;
-                Ival I{0, N - 1}, Ik{0, N - 1};
-                int dq_head = 0, dq_n = 0;
-                int bestU_pos = -1;
-                idx_t bestU_col = 0;
-                // walk state (walk_in_unitigs): last answered k-mer ends at text position walk_g
-                bool walking = false;
-                idx_t walk_g = 0, walk_ustart = 0, walk_uend = 0;
-                uint32_t walk_uid = 0;
-                uint64_t tword = 0, qword = 0;
-                int walk_j = 0;  // bases compared since the anchor (access counters only)
+    FIN_D void set_drop_I(const IndexView& ix, const int new_len) {
+        if (new_len <= 0) { I.l = 0; I.r = ix.n_nodes - 1; }
+        else { lenI = new_len; pendI = kDropLeft | kDropRight; }
+    }
+    FIN_D void set_drop_K(const IndexView& ix, const int new_len) {
+        if (new_len <= 0) { Ik.l = 0; Ik.r = ix.n_nodes - 1; }
+        else { lenK = new_len; pendK = kDropLeft | kDropRight; }
+    }
 
-                for (int end = 0; end < len; end++) {
-                    // ---- next base of this strand
-                    int c;
-                    if (strand == 0) {
-                        const uint64_t b = b0 + (uint64_t)end;
-                        if (end == 0 || (b & 31) == 0) qword = __ldg(packed + (b >> 5));
-                        c = (int)((qword >> (2 * (b & 31))) & 3);
-                    } else {
-                        const uint64_t b = b0 + (uint64_t)(len - 1 - end);
-                        if (end == 0 || (b & 31) == 31) qword = __ldg(packed + (b >> 5));
-                        c = 3 - (int)((qword >> (2 * (b & 31))) & 3);
-                    }
-                    if (COUNT) c_bases++;
+    FIN_D void step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc, const int n_strands);
+};
 
-                    // ---- (1) finimizer interval: extend, contracting from the left while absent (common.hh:114-126)
-                    Ival In = extend(ix, I, c);
-                    if (COUNT) c_rank += 2;
-                    while (is_empty(In)) {
-                        kmer_start = ++start;
-                        if (start > end) {
-                            In.l = 0;
-                            In.r = N - 1;
-                            Ik = In;
-                            break;
-                        }
-                        I = drop_first_char<COUNT>(ix, end - start, I, c_lcs);
-                        In = extend(ix, I, c);
-                        if (COUNT) c_rank += 2;
-                        Ik = In;
-                    }
-                    I = In;
-                    // ---- (2) k-mer interval (common.hh:132-143)
-                    if (start != kmer_start) {
-                        Ival J = extend(ix, Ik, c);
-                        if (COUNT) c_rank += 2;
-                        while (is_empty(J)) {
-                            kmer_start++;
-                            Ik = drop_first_char<COUNT>(ix, end - kmer_start, Ik, c_lcs);
-                            J = extend(ix, Ik, c);
-                            if (COUNT) c_rank += 2;
-                        }
-                        Ik = J;
-                    } else {
-                        Ik = I;
-                    }
-                    // ---- (3) unique: shrink to the shortest unique suffix and record it (common.hh:145-164)
-                    if (I.l == I.r) {
-                        uint64_t cur;
-                        do {
-                            cur = cand_pack(end - start + 1, I.l, end);
-                            start++;
-                            I = drop_first_char<COUNT>(ix, end - start + 1, I, c_lcs);
-                        } while (I.l == I.r);
-                        while (dq_n > 0 && cand_start(dq[dq_head]) < kmer_start) {  // eager expiry
-                            dq_head = (dq_head + 1) & (KCAP - 1);
-                            dq_n--;
-                        }
-                        while (dq_n > 0 && dq[(dq_head + dq_n - 1) & (KCAP - 1)] > cur) dq_n--;
-                        if (dq_n == KCAP) {  // cannot happen for live entries; keeps memory safe out of domain
-                            err |= kErrWindowUnderflow;
-                            dq_n--;
-                        }
-                        dq[(dq_head + dq_n) & (KCAP - 1)] = cur;
-                        dq_n++;
-                    }
-                    // ---- (4) rightmost unitig start among the singleton k-mer intervals (common.hh:167)
-                    if (Ik.l == Ik.r) {
-                        if (COUNT) c_ustart++;
-                        if (bit1(ix.ustart, Ik.l)) {
-                            bestU_pos = end;
-                            bestU_col = Ik.l;
-                        }
-                    }
-                    // ---- (5) a complete k-mer ends here (common.hh:170-182)
-                    bool present = false;
-                    uint64_t w = 0;
-                    idx_t kmer_col = 0;
-                    if (end - kmer_start + 1 == k) {
-                        while (dq_n > 0 && cand_start(dq[dq_head]) < kmer_start) {
-                            dq_head = (dq_head + 1) & (KCAP - 1);
-                            dq_n--;
-                        }
-                        present = true;
-                        kmer_col = Ik.l;
-                        if (dq_n > 0) {
-                            w = dq[dq_head];
-                        } else {  // the reference would read a stale slot here (BoundedDeque.hh:28-34)
-                            err |= kErrWindowUnderflow;
-                            present = false;
-                        }
-                        kmer_start++;
-                        Ik = drop_first_char<COUNT>(ix, k - 1, Ik, c_lcs);
-                    }
-                    (void)kmer_col;
+template <int KCAP, class HitT, bool COUNT>
+FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc,
+                                          const int n_strands) {
+    const int k = ix.k;
+    const idx_t N = ix.n_nodes;
 
-                    // ---- resolve (FinimizerIndex.hh:148-183), in step with the stream
-                    if (end >= k - 1) {
-                        if (COUNT) c_kmers++;
-                        HitT hit_u = (HitT)-1, hit_p = (HitT)-1;
-                        bool hit = false;
-                        if (walking) {  // walk_in_unitigs: next query base against the next text base
-                            const idx_t tp = walk_g + 1;
-                            bool match = false;
-                            if (tp < walk_uend) {
-                                if ((tp & 31) == 0) tword = __ldg(ix.text + (tp >> 5));
-                                if (COUNT && (walk_j & 31) == 0) c_walk++;  // one 32-base compare of the reference (:72-100)
-                                match = (int)((tword >> (2 * (tp & 31))) & 3) == c;
-                            }
-                            if (match) {
-                                walk_g = tp;
-                                walk_j++;
-                                hit = true;
-                            } else {
-                                walking = false;
-                            }
-                        }
-                        if (!hit && present) {
-                            if (COUNT) c_anchor++;
-                            idx_t g;
-                            bool ok = true;
-                            if (bestU_pos >= cand_end(w)) {  // lookup_from_branch_dictionary (common.hh:61-67)
-                                if (COUNT) c_branch++;
-                                const uint32_t u = rank1(ix.ustart, bestU_col);
-                                const idx_t us = u > 0 ? __ldg(ix.ends + (u - 1 < ix.n_unitigs ? u - 1 : ix.n_unitigs - 1)) : 0;
-                                g = us + (idx_t)(k - 1) + (idx_t)(end - bestU_pos);
-                            } else {  // lookup_from_finimizer_dictionary (common.hh:69-72)
-                                const uint32_t id = rank1(ix.fmin, cand_colex(w));
-                                if (id >= ix.n_fmin) {
-                                    ok = false;
-                                    g = 0;
-                                } else {
-                                    g = __ldg(ix.offsets + id) + (idx_t)(end - cand_end(w));
-                                }
-                            }
-                            const idx_t gs = g - (idx_t)(k - 1);
-                            if (!ok || g < (idx_t)(k - 1) || gs >= ix.text_len) {
-                                err |= kErrLookupRange;
-                            } else {  // global_offset_to_local_offset (PackedStrings.hh:91-100)
-                                walk_uid = rank1(ix.tstart, gs + 1) - 1;
-                                walk_ustart = walk_uid > 0 ? __ldg(ix.ends + walk_uid - 1) : 0;
-                                walk_uend = __ldg(ix.ends + walk_uid);
-                                walk_g = g;
-                                hit = true;
-                                walking = g < walk_uend;
-                                walk_j = 0;
-                                if (walking && g + 1 < walk_uend) tword = __ldg(ix.text + ((g + 1) >> 5));
-                            }
-                        }
-                        if (hit) {
-                            hit_u = (HitT)walk_uid;
-                            hit_p = (HitT)(walk_g - (idx_t)(k - 1) - walk_ustart);
-                            found[strand]++;
-                        }
-                        const int j = end - (k - 1);
-                        if (strand == 0) {
-                            o[j].unitig = hit_u;
-                            o[j].pos = hit_p;
-                            if (hit) positive++;
-                        } else if (hit) {  // merge: the forward answer wins (search_fmin.hh:54-60)
-                            const int i = nk - 1 - j;
-                            if (o[i].unitig == (HitT)-1) {
-                                o[i].unitig = hit_u;
-                                o[i].pos = hit_p;
-                                positive++;
-                            }
-                        }
-                    }
+    // ---- A: extend both intervals with the current character (common.hh:114-143).  ST_EXTK = the finimizer
+    //         interval is already extended, only the k-mer interval is being contracted and retried.
+    if ((pendI | pendK) == 0 && st <= ST_EXTK) {
+        const bool both = st == ST_EXT;
+        Ival JI = I;
+        if (both) {
+            JI = extend(ix, I, c);
+            if (COUNT) rc.c_rank += 2;
+        }
+        const Ival JK = extend(ix, Ik, c);  // speculative in ST_EXT: unused when the k-mer interval follows I
+        if (both && is_empty(JI)) {         // :116-126 contract the finimizer interval from the left and retry
+            kmer_start = ++start;
+            if (start > end) {
+                I.l = 0;
+                I.r = N - 1;
+                Ik = I;
+                emit = false;
+                st = ST_EMIT;
+            } else {
+                set_drop_I(ix, end - start);
+            }
+        } else {
+            if (both) I = JI;
+            if (both && start == kmer_start) {  // :141-143
+                Ik = I;
+                st = ST_POST;
+            } else {                            // :132-140
+                if (COUNT) rc.c_rank += 2;
+                if (is_empty(JK)) {
+                    kmer_start++;
+                    set_drop_K(ix, end - kmer_start);
+                    st = ST_EXTK;
+                } else {
+                    Ik = JK;
+                    st = ST_POST;
                 }
             }
+        }
+    }
+
+    // ---- B: both intervals stand for this character
+    if (st == ST_POST) {
+        if (Ik.l == Ik.r) {  // :167 rightmost unitig start among the singleton k-mer intervals
+            if (COUNT) rc.c_ustart++;
+            if (ustart_bit(ix, Ik.l)) {
+                bestU_pos = end;
+                bestU_col = Ik.l;
+            }
+        }
+        emit = end - kmer_start + 1 == k;  // :170
+        if (emit) set_drop_K(ix, k - 1);   // :181, independent of the shrink below
+        if (I.l == I.r) {                  // :145-154 shrink to the shortest unique suffix
+            cur = cand_pack(end - start + 1, I.l, end);
+            start++;
+            set_drop_I(ix, end - start + 1);
+            st = ST_SHRINK;
+        } else {
+            st = ST_EMIT;
+        }
+    }
+
+    // ---- F: one word step of every pending drop_first_char
+    if (pendI) pendI = drop_step<WIDE, COUNT>(ix, I, lenI, pendI, rc.c_lcs);
+    if (pendK) pendK = drop_step<WIDE, COUNT>(ix, Ik, lenK, pendK, rc.c_lcs);
+
+    // ---- D: shrink loop condition (:154) and the candidate window (:155-164)
+    if (st == ST_SHRINK && pendI == 0) {
+        if (I.l == I.r) {
+            cur = cand_pack(end - start + 1, I.l, end);
+            start++;
+            set_drop_I(ix, end - start + 1);
+        } else {
+            while (dq_n > 0 && cand_start(dq[dq_head]) < kmer_start) {  // eager expiry
+                dq_head = (dq_head + 1) & (KCAP - 1);
+                dq_n--;
+            }
+            while (dq_n > 0 && dq[(dq_head + dq_n - 1) & (KCAP - 1)] > cur) dq_n--;
+            if (dq_n == KCAP) {  // cannot happen for live entries; keeps memory safe out of domain
+                rc.err |= kErrWindowUnderflow;
+                dq_n--;
+            }
+            dq[(dq_head + dq_n) & (KCAP - 1)] = cur;
+            dq_n++;
+            st = ST_EMIT;
+        }
+    }
+
+    // ---- E: emission (:170-182), resolve (FinimizerIndex.hh:148-183), next character
+    if (st == ST_EMIT && (pendI | pendK) == 0) {
+        if (COUNT) rc.c_bases++;
+        bool present = false;
+        uint64_t w = 0;
+        if (emit) {
+            while (dq_n > 0 && cand_start(dq[dq_head]) < kmer_start) {
+                dq_head = (dq_head + 1) & (KCAP - 1);
+                dq_n--;
+            }
+            present = true;
+            if (dq_n > 0) {
+                w = dq[dq_head];
+            } else {  // the reference would read a stale slot here (BoundedDeque.hh:28-34)
+                rc.err |= kErrWindowUnderflow;
+                present = false;
+            }
+            kmer_start++;
+        }
+        if (end >= k - 1) {
+            if (COUNT) rc.c_kmers++;
+            bool hit = false;
+            if (walking) {  // walk_in_unitigs: next query base against the next text base
+                const idx_t tp = walk_g + 1;
+                bool match = false;
+                if (tp < walk_uend) {
+                    if ((tp & 31) == 0) tword = __ldg(ix.text + (tp >> 5));
+                    if (COUNT && (walk_j & 31) == 0) rc.c_walk++;  // one 32-base compare of the reference (:72-100)
+                    match = (int)((tword >> (2 * (tp & 31))) & 3) == c;
+                }
+                if (match) {
+                    walk_g = tp;
+                    walk_j++;
+                    hit = true;
+                } else {
+                    walking = false;
+                }
+            }
+            if (!hit && present) {
+                if (COUNT) rc.c_anchor++;
+                idx_t g;
+                bool ok = true;
+                if (bestU_pos >= cand_end(w)) {  // lookup_from_branch_dictionary (common.hh:61-67)
+                    if (COUNT) rc.c_branch++;
+                    const uint32_t u = rank1(ix.ustart, bestU_col);
+                    const idx_t us = u > 0 ? __ldg(ix.ends + (u - 1 < ix.n_unitigs ? u - 1 : ix.n_unitigs - 1)) : 0;
+                    g = us + (idx_t)(k - 1) + (idx_t)(end - bestU_pos);
+                } else {  // lookup_from_finimizer_dictionary (common.hh:69-72)
+                    const uint32_t id = rank1(ix.fmin, cand_colex(w));
+                    if (id >= ix.n_fmin) {
+                        ok = false;
+                        g = 0;
+                    } else {
+                        g = __ldg(ix.offsets + id) + (idx_t)(end - cand_end(w));
+                    }
+                }
+                const idx_t gs = g - (idx_t)(k - 1);
+                if (!ok || g < (idx_t)(k - 1) || gs >= ix.text_len) {
+                    rc.err |= kErrLookupRange;
+                } else {  // global_offset_to_local_offset (PackedStrings.hh:91-100)
+                    walk_uid = rank1(ix.tstart, gs + 1) - 1;
+                    walk_ustart = walk_uid > 0 ? __ldg(ix.ends + walk_uid - 1) : 0;
+                    walk_uend = __ldg(ix.ends + walk_uid);
+                    walk_g = g;
+                    hit = true;
+                    walking = g < walk_uend;
+                    walk_j = 0;
+                    if (walking && g + 1 < walk_uend) tword = __ldg(ix.text + ((g + 1) >> 5));
+                }
+            }
+            const int j = end - (k - 1);
+            if (strand == 0) {
+                HitPair<HitT> h;
+                h.unitig = hit ? (HitT)walk_uid : (HitT)-1;
+                h.pos = hit ? (HitT)(walk_g - (idx_t)(k - 1) - walk_ustart) : (HitT)-1;
+                o[j] = h;
+                if (hit) {
+                    rc.found[0]++;
+                    rc.positive++;
+                }
+            } else if (hit) {  // merge: the forward answer wins (search_fmin.hh:54-60)
+                rc.found[1]++;
+                const int i = nk - 1 - j;
+                if (o[i].unitig == (HitT)-1) {
+                    HitPair<HitT> h;
+                    h.unitig = (HitT)walk_uid;
+                    h.pos = (HitT)(walk_g - (idx_t)(k - 1) - walk_ustart);
+                    o[i] = h;
+                    rc.positive++;
+                }
+            }
+        }
+        end++;
+        if (end == len) {
+            strand++;
+            if (strand < n_strands) begin_strand(ix, packed);
+            else st = ST_IDLE;
+        } else {
+            fetch_base(packed);
+            st = ST_EXT;
         }
     }
 }
 
 #ifdef __CUDACC__
+// Persistent warps: a lane that finishes its read takes the next one from a global counter (one atomic per
+// group of lanes that run dry in the same iteration), so no lane idles while reads remain.
 template <int KCAP, class HitT, bool COUNT>
 __global__ void __launch_bounds__(128) search_reads_kernel(const IndexView ix, const uint64_t* __restrict__ packed,
                                                            const uint64_t* __restrict__ read_offsets, const uint64_t n_reads,
                                                            const uint64_t* __restrict__ out_offsets,
                                                            HitPair<HitT>* __restrict__ out, SearchTotals* __restrict__ totals,
                                                            const int n_strands) {
-    const uint64_t rid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned full = 0xFFFFFFFFu;
+    const unsigned lane = threadIdx.x & 31u;
+    Chain<KCAP, HitT, COUNT> ch;
     ReadCounters rc;
-    if (rid < n_reads) {
-        const uint64_t b0 = __ldg(read_offsets + rid);
-        const uint64_t len64 = __ldg(read_offsets + rid + 1) - b0;
-        search_one_read<KCAP, HitT, COUNT>(ix, packed, b0, len64, out + __ldg(out_offsets + rid), rc, n_strands);
+    bool dry = false;  // the counter ran past the last read
+    while (true) {
+        const bool want = ch.st == ST_IDLE && !dry;
+        const unsigned m = __ballot_sync(full, want);
+        if (m) {
+            const int leader = __ffs((int)m) - 1;
+            unsigned long long base = 0;
+            if ((int)lane == leader) base = atomicAdd(&totals->next_read, (unsigned long long)__popc(m));
+            base = __shfl_sync(full, base, leader);
+            if (want) {
+                const uint64_t rid = base + (uint64_t)__popc(m & ((1u << lane) - 1u));
+                if (rid < n_reads) {
+                    const uint64_t b0 = __ldg(read_offsets + rid);
+                    const uint64_t len64 = __ldg(read_offsets + rid + 1) - b0;
+                    ch.begin_read(ix, packed, b0, len64, out + __ldg(out_offsets + rid), rc);
+                } else {
+                    dry = true;
+                }
+            }
+        }
+        if (__all_sync(full, ch.st == ST_IDLE)) {
+            if (__all_sync(full, dry)) break;
+            continue;
+        }
+        ch.step(ix, packed, rc, n_strands);
     }
-    const unsigned err = rc.err;
-    const unsigned c_rank = rc.c_rank, c_lcs = rc.c_lcs, c_ustart = rc.c_ustart, c_anchor = rc.c_anchor, c_branch = rc.c_branch,
-                   c_walk = rc.c_walk, c_bases = rc.c_bases, c_kmers = rc.c_kmers;
-    const unsigned* found = rc.found;
-    const unsigned positive = rc.positive, n_q = rc.n_q;
 
     // ---- per-warp reduction of the counters, one atomic per warp and counter
-    const unsigned full = 0xFFFFFFFFu;
-    unsigned long long v_ff = found[0], v_fr = found[1], v_pos = positive, v_q = n_q;
+    unsigned long long v_ff = rc.found[0], v_fr = rc.found[1], v_pos = rc.positive, v_q = rc.n_q;
 #pragma unroll
     for (int s = 16; s > 0; s >>= 1) {
         v_ff += __shfl_down_sync(full, v_ff, s);
@@ -352,8 +516,8 @@ __global__ void __launch_bounds__(128) search_reads_kernel(const IndexView ix, c
         v_pos += __shfl_down_sync(full, v_pos, s);
         v_q += __shfl_down_sync(full, v_q, s);
     }
-    const unsigned any_err = __reduce_or_sync(full, err);
-    if ((threadIdx.x & 31) == 0) {
+    const unsigned any_err = __reduce_or_sync(full, rc.err);
+    if (lane == 0) {
         if (v_ff) atomicAdd(&totals->found_fwd, v_ff);
         if (v_fr) atomicAdd(&totals->found_rc, v_fr);
         if (v_pos) atomicAdd(&totals->positive, v_pos);
@@ -361,14 +525,14 @@ __global__ void __launch_bounds__(128) search_reads_kernel(const IndexView ix, c
         if (any_err) atomicOr(&totals->error_flags, any_err);
     }
     if (COUNT) {
-        unsigned long long cs[8] = {c_rank, c_lcs, c_ustart, c_anchor, c_branch, c_walk, c_bases, c_kmers};
+        unsigned long long cs[8] = {rc.c_rank, rc.c_lcs, rc.c_ustart, rc.c_anchor, rc.c_branch, rc.c_walk, rc.c_bases, rc.c_kmers};
         unsigned long long* dst = &totals->n_rank;
 #pragma unroll
         for (int i = 0; i < 8; i++) {
             unsigned long long v = cs[i];
 #pragma unroll
             for (int s = 16; s > 0; s >>= 1) v += __shfl_down_sync(full, v, s);
-            if ((threadIdx.x & 31) == 0 && v) atomicAdd(dst + i, v);
+            if (lane == 0 && v) atomicAdd(dst + i, v);
         }
     }
 }

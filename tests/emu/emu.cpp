@@ -12,6 +12,8 @@ struct ulonglong2 { unsigned long long x, y; };
 struct uint4 { unsigned int x, y, z, w; };
 template <class T> static inline T __ldg(const T* p) { return *p; }
 static inline int __popcll(unsigned long long x) { return __builtin_popcountll(x); }
+static inline int __clzll(long long x) { return x ? __builtin_clzll((unsigned long long)x) : 64; }
+static inline int __ffsll(long long x) { return __builtin_ffsll(x); }
 using std::max;
 using std::min;
 
@@ -27,15 +29,13 @@ template <class F> static int guarded(F f) {
 
 static IndexView view_of(const HostLayout& L) {
     IndexView v{};
-    v.matrix = reinterpret_cast<const ulonglong2*>(L.matrix.data());
+    v.lines = reinterpret_cast<const uint4*>(L.lines.data());
     v.ustart = reinterpret_cast<const ulonglong2*>(L.ustart.data());
     v.fmin = reinterpret_cast<const ulonglong2*>(L.fmin.data());
     v.tstart = reinterpret_cast<const ulonglong2*>(L.tstart.data());
-    v.lcs = L.lcs.data();
     v.offsets = L.offsets.data();
     v.ends = L.ends.data();
     v.text = L.text.data();
-    for (int c = 0; c < 4; c++) v.C[c] = (idx_t)L.C[c];
     v.n_nodes = (idx_t)L.n_nodes;
     v.text_len = (idx_t)L.text_len;
     v.n_unitigs = (uint32_t)L.n_unitigs;
@@ -44,14 +44,22 @@ static IndexView view_of(const HostLayout& L) {
     return v;
 }
 
+template <int KCAP, class HitT, bool COUNT>
+static void run_chain(const IndexView& v, const uint64_t* packed, uint64_t b0, uint64_t len, HitPair<HitT>* o, ReadCounters& rc,
+                      int n_strands) {
+    Chain<KCAP, HitT, COUNT> ch;
+    if (!ch.begin_read(v, packed, b0, len, o, rc)) return;
+    while (ch.st != ST_IDLE) ch.step(v, packed, rc, n_strands);
+}
+
 template <class HitT, bool COUNT>
 static void run_read(const IndexView& v, const uint64_t* packed, uint64_t b0, uint64_t len, HitPair<HitT>* o, ReadCounters& rc,
                      int n_strands) {
     const int k = v.k;
-    if (k <= 32) search_one_read<32, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
-    else if (k <= 64) search_one_read<64, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
-    else if (k <= 128) search_one_read<128, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
-    else search_one_read<256, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
+    if (k <= 32) run_chain<32, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
+    else if (k <= 64) run_chain<64, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
+    else if (k <= 128) run_chain<128, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
+    else run_chain<256, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
 }
 
 static std::vector<uint8_t> emu_lcs_bytes(const SbwtHost& s) {
@@ -140,12 +148,9 @@ int emu_build(const char* sbwt_path, const char* unitig_path, const char* out_pr
         append_sequences(files[0], unitigs);
         check_unitigs(unitigs, k);
         const uint64_t U = unitigs.size();
-        std::vector<uint64_t> matrix = matrix_sectors(sbwt);
-        std::vector<uint8_t> lb = lcs_bytes(lcs_file);
+        std::vector<uint64_t> lines = make_lines(sbwt, &lcs_file, nullptr, nullptr);
         IndexView ix{};
-        ix.matrix = reinterpret_cast<const ulonglong2*>(matrix.data());
-        ix.lcs = lb.data();
-        for (int c = 0; c < 4; c++) ix.C[c] = (idx_t)sbwt.C[c];
+        ix.lines = reinterpret_cast<const uint4*>(lines.data());
         ix.n_nodes = (idx_t)N;
         ix.k = k;
         std::vector<uint64_t> order(U), starts;
