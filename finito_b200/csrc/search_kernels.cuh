@@ -212,7 +212,7 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
     uint32_t walk_uid = 0;
     uint64_t tword = 0;
     int walk_j = 0;
-    uint64_t dq[KCAP];
+    uint64_t fr = 0, bk = 0;  // front and back of the candidate window, cached in registers
 
     FIN_D void begin_strand(const IndexView& ix, const uint64_t* __restrict__ packed) {
         start = kmer_start = 0;
@@ -267,12 +267,13 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
         else { lenK = new_len; pendK = kDropLeft | kDropRight; }
     }
 
-    FIN_D void step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc, const int n_strands);
+    // dq: the KCAP slots of the candidate window, a separate array so that the scalar state stays in registers
+    FIN_D void step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc, const int n_strands, uint64_t* dq);
 };
 
 template <int KCAP, class HitT, bool COUNT>
 FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc,
-                                          const int n_strands) {
+                                          const int n_strands, uint64_t* dq) {
     const int k = ix.k;
     const idx_t N = ix.n_nodes;
 
@@ -348,17 +349,27 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
             start++;
             set_drop_I(ix, end - start + 1);
         } else {
-            while (dq_n > 0 && cand_start(dq[dq_head]) < kmer_start) {  // eager expiry
-                dq_head = (dq_head + 1) & (KCAP - 1);
+            // monotone window: drop the candidates that are larger than the new one, then append it.  Front and
+            // back live in registers, so only a pop touches the slots.
+            while (dq_n > 0 && bk > cur) {
                 dq_n--;
+                if (dq_n > 0) bk = dq[(dq_head + dq_n - 1) & (KCAP - 1)];
             }
-            while (dq_n > 0 && dq[(dq_head + dq_n - 1) & (KCAP - 1)] > cur) dq_n--;
-            if (dq_n == KCAP) {  // cannot happen for live entries; keeps memory safe out of domain
-                rc.err |= kErrWindowUnderflow;
-                dq_n--;
+            if (dq_n == KCAP) {  // only entries that left the window can fill the ring: expire them now
+                while (dq_n > 0 && cand_start(fr) < kmer_start) {
+                    dq_head = (dq_head + 1) & (KCAP - 1);
+                    dq_n--;
+                    if (dq_n > 0) fr = dq[dq_head];
+                }
+                if (dq_n == KCAP) {  // cannot happen for live entries; keeps memory safe out of domain
+                    rc.err |= kErrWindowUnderflow;
+                    dq_n--;
+                }
             }
             dq[(dq_head + dq_n) & (KCAP - 1)] = cur;
             dq_n++;
+            bk = cur;
+            if (dq_n == 1) fr = cur;
             st = ST_EMIT;
         }
     }
@@ -368,14 +379,17 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         if (COUNT) rc.c_bases++;
         bool present = false;
         uint64_t w = 0;
+        // candidates that begin before the window are gone for good (kmer_start never decreases); the reference pops
+        // them at its next emission (:173-176), popping them at every character is unobservable
+        while (dq_n > 0 && cand_start(fr) < kmer_start) {
+            dq_head = (dq_head + 1) & (KCAP - 1);
+            dq_n--;
+            if (dq_n > 0) fr = dq[dq_head];
+        }
         if (emit) {
-            while (dq_n > 0 && cand_start(dq[dq_head]) < kmer_start) {
-                dq_head = (dq_head + 1) & (KCAP - 1);
-                dq_n--;
-            }
             present = true;
             if (dq_n > 0) {
-                w = dq[dq_head];
+                w = fr;
             } else {  // the reference would read a stale slot here (BoundedDeque.hh:28-34)
                 rc.err |= kErrWindowUnderflow;
                 present = false;
@@ -479,6 +493,7 @@ __global__ void __launch_bounds__(128) search_reads_kernel(const IndexView ix, c
     const unsigned full = 0xFFFFFFFFu;
     const unsigned lane = threadIdx.x & 31u;
     Chain<KCAP, HitT, COUNT> ch;
+    uint64_t dq[KCAP];
     ReadCounters rc;
     bool dry = false;  // the counter ran past the last read
     while (true) {
@@ -504,7 +519,7 @@ __global__ void __launch_bounds__(128) search_reads_kernel(const IndexView ix, c
             if (__all_sync(full, dry)) break;
             continue;
         }
-        ch.step(ix, packed, rc, n_strands);
+        ch.step(ix, packed, rc, n_strands, dq);
     }
 
     // ---- per-warp reduction of the counters, one atomic per warp and counter

@@ -48,8 +48,9 @@ template <int KCAP, class HitT, bool COUNT>
 static void run_chain(const IndexView& v, const uint64_t* packed, uint64_t b0, uint64_t len, HitPair<HitT>* o, ReadCounters& rc,
                       int n_strands) {
     Chain<KCAP, HitT, COUNT> ch;
+    uint64_t dq[KCAP];
     if (!ch.begin_read(v, packed, b0, len, o, rc)) return;
-    while (ch.st != ST_IDLE) ch.step(v, packed, rc, n_strands);
+    while (ch.st != ST_IDLE) ch.step(v, packed, rc, n_strands, dq);
 }
 
 template <class HitT, bool COUNT>
