@@ -186,6 +186,15 @@ constexpr int kMaxReadLen = (1 << 24) - 1;
 // and a lane that needs another contraction or another drop word simply spends its next iteration on it while its
 // neighbours move on to their next character: lanes drift apart in position instead of waiting for each other.
 // In the matching region a character costs one iteration.
+// Every lane of the warp calls step() in every iteration, so the phases can be fenced with warp barriers: they keep
+// the compiler from threading a phase into the branches of the one before it (which would execute it once per
+// incoming path, each time for a few lanes).
+#ifdef FIN_EMU
+#define FIN_PHASE_FENCE() do {} while (0)
+#else
+#define FIN_PHASE_FENCE() __syncwarp()
+#endif
+
 enum : int { ST_EXT = 0, ST_EXTK = 1, ST_POST = 2, ST_SHRINK = 3, ST_EMIT = 4, ST_IDLE = 5 };
 
 template <int KCAP, class HitT, bool COUNT> struct Chain {
@@ -317,6 +326,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         }
     }
 
+    FIN_PHASE_FENCE();
     // ---- B: both intervals stand for this character
     if (st == ST_POST) {
         if (Ik.l == Ik.r) {  // :167 rightmost unitig start among the singleton k-mer intervals
@@ -338,9 +348,12 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         }
     }
 
+    FIN_PHASE_FENCE();
     // ---- F: one word step of every pending drop_first_char
     if (pendI) pendI = drop_step<WIDE, COUNT>(ix, I, lenI, pendI, rc.c_lcs);
+    FIN_PHASE_FENCE();
     if (pendK) pendK = drop_step<WIDE, COUNT>(ix, Ik, lenK, pendK, rc.c_lcs);
+    FIN_PHASE_FENCE();
 
     // ---- D: shrink loop condition (:154) and the candidate window (:155-164)
     if (st == ST_SHRINK && pendI == 0) {
@@ -374,6 +387,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         }
     }
 
+    FIN_PHASE_FENCE();
     // ---- E: emission (:170-182), resolve (FinimizerIndex.hh:148-183), next character
     if (st == ST_EMIT && (pendI | pendK) == 0) {
         if (COUNT) rc.c_bases++;
