@@ -83,7 +83,7 @@ FIN_D uint32_t rank1(const ulonglong2* __restrict__ sectors, idx_t p) {
 
 // C[c] + rank_c(p): the column the edge labelled c out of the first column >= p leads to
 FIN_D idx_t step_c(const IndexView& ix, const idx_t p, const int c) {
-    const uint4 row = __ldg(ix.lines + (size_t)(p >> 6) * kLineU4 + c);
+    const uint4 row = __ldg(ix.lines + (((p >> 6) << 3) | (uint32_t)c));  // 32-bit index: n_nodes / 8 < 2^29
     const uint64_t bits = (uint64_t)row.x | ((uint64_t)row.y << 32);
     return row.z + (idx_t)__popcll(bits & ((1ULL << (p & 63)) - 1ULL));
 }
@@ -103,14 +103,14 @@ FIN_D bool is_empty(const Ival I) { return I.l > I.r; }
 
 // Ustart[p] (common.hh:167) from the line of p
 FIN_D bool ustart_bit(const IndexView& ix, const idx_t p) {
-    const uint32_t* w = reinterpret_cast<const uint32_t*>(ix.lines + (size_t)(p >> 6) * kLineU4 + ((p >> 5) & 1));
-    return (__ldg(w + 3) >> (p & 31)) & 1u;
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(ix.lines);
+    return (__ldg(w + (((p >> 6) << 5) | ((p >> 3) & 4u) | 3u)) >> (p & 31)) & 1u;
 }
 
 // LCS[p] from the line of p (build kernels; the search uses the word-parallel drop_step below)
 FIN_D int lcs_at(const IndexView& ix, const idx_t p) {
-    const uint8_t* b = reinterpret_cast<const uint8_t*>(ix.lines + (size_t)(p >> 6) * kLineU4);
-    return (int)__ldg(b + 64 + (p & 63));
+    const uint8_t* b = reinterpret_cast<const uint8_t*>(ix.lines);
+    return (int)__ldg(b + (((size_t)(p >> 6) << 7) | 64u | (p & 63u)));
 }
 
 #endif  // __CUDACC__ || FIN_EMU

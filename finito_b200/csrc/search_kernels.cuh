@@ -106,44 +106,42 @@ template <bool WIDE> FIN_D uint64_t bytes_below(const uint64_t x, const int n) {
 
 enum : unsigned { kDropLeft = 1u, kDropRight = 2u };
 
+// u64 index of the aligned 8-byte LCS word of column p inside the lines array (< n_nodes / 4: fits 32 bits)
+FIN_D uint32_t lcs_word_index(const idx_t p) { return ((p >> 6) << 4) | 8u | ((p >> 3) & 7u); }
+
+// Left end: w = the LCS word of column I.l.  Clears kDropLeft in pend unless the scan runs off the word.
+template <bool WIDE, bool COUNT>
+FIN_D void drop_left(const uint64_t w, Ival& I, const int new_len, unsigned& pend, unsigned& n_lcs) {
+    const idx_t l = I.l;
+    const uint32_t j = l & 7u;
+    const uint64_t stop = bytes_below<WIDE>(w, new_len) << (8u * (7u - j));  // bytes above l shifted out
+    const bool found = stop != 0;  // always true in the word of column 0: LCS[0] = 0
+    const idx_t nl = found ? l - (idx_t)(__clzll((long long)stop) >> 3) : l - j - 1u;
+    if (COUNT) n_lcs += (l - nl) + (found && nl > 0 ? 1u : 0u);
+    if (found) pend &= ~kDropLeft;
+    I.l = nl;
+}
+
+// Right end: w = the LCS word of column I.r + 1.
+template <bool WIDE, bool COUNT>
+FIN_D void drop_right(const uint64_t w, Ival& I, const int new_len, unsigned& pend, const idx_t n_nodes, unsigned& n_lcs) {
+    const idx_t rp = I.r + 1;
+    const uint32_t j = rp & 7u;
+    const uint64_t stop = bytes_below<WIDE>(w, new_len) >> (8u * j);  // bytes below r+1 shifted out
+    const bool found = stop != 0;
+    const idx_t nr = found ? I.r + (idx_t)((__ffsll((long long)stop) - 1) >> 3) : (rp | 7u);
+    if (COUNT) n_lcs += (nr - I.r) + (found && nr < n_nodes - 1 ? 1u : 0u);
+    if (found) pend &= ~kDropRight;
+    I.r = nr;
+}
+
 // One word step on the pending sides of I; returns the sides that are still pending.
 template <bool WIDE, bool COUNT>
-FIN_D unsigned drop_step(const IndexView& ix, Ival& I, const int new_len, const unsigned pend, unsigned& n_lcs) {
+FIN_D unsigned drop_step(const IndexView& ix, Ival& I, const int new_len, unsigned pend, unsigned& n_lcs) {
     const uint64_t* __restrict__ lw = reinterpret_cast<const uint64_t*>(ix.lines);
-    unsigned still = 0;
-    if (pend & kDropLeft) {
-        const idx_t l = I.l;
-        const uint64_t w = __ldg(lw + (size_t)(l >> 6) * kLineU64 + kLineLcsU64 + ((l & 63) >> 3));
-        const int j = (int)(l & 7);
-        const uint64_t stop = bytes_below<WIDE>(w, new_len) & (~0ULL >> (8 * (7 - j)));
-        idx_t nl;
-        if (stop) {
-            nl = (l & ~7u) + (idx_t)((63 - __clzll((long long)stop)) >> 3);
-            if (COUNT) n_lcs += (l - nl) + (nl > 0 ? 1u : 0u);
-        } else {  // cannot happen in the word of column 0: LCS[0] = 0
-            nl = (l & ~7u) - 1;
-            if (COUNT) n_lcs += l - nl;
-            still |= kDropLeft;
-        }
-        I.l = nl;
-    }
-    if (pend & kDropRight) {
-        const idx_t rp = I.r + 1;
-        const uint64_t w = __ldg(lw + (size_t)(rp >> 6) * kLineU64 + kLineLcsU64 + ((rp & 63) >> 3));
-        const int j = (int)(rp & 7);
-        const uint64_t stop = bytes_below<WIDE>(w, new_len) & (~0ULL << (8 * j));
-        idx_t nr;
-        if (stop) {
-            nr = (rp & ~7u) + (idx_t)((__ffsll((long long)stop) - 1) >> 3) - 1;
-            if (COUNT) n_lcs += (nr - I.r) + (nr < ix.n_nodes - 1 ? 1u : 0u);
-        } else {
-            nr = (rp & ~7u) + 7;
-            if (COUNT) n_lcs += nr - I.r;
-            still |= kDropRight;
-        }
-        I.r = nr;
-    }
-    return still;
+    if (pend & kDropLeft) drop_left<WIDE, COUNT>(__ldg(lw + lcs_word_index(I.l)), I, new_len, pend, n_lcs);
+    if (pend & kDropRight) drop_right<WIDE, COUNT>(__ldg(lw + lcs_word_index(I.r + 1)), I, new_len, pend, ix.n_nodes, n_lcs);
+    return pend;
 }
 
 // the whole of drop_first_char, for the callers that are not state machines (build-fmin kernels)
@@ -207,10 +205,10 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
     int st = ST_IDLE, end = 0, c = 0;
     int start = 0, kmer_start = 0;
     Ival I{0, 0}, Ik{0, 0};
-    uint64_t qword = 0;
     unsigned pendI = 0, pendK = 0;  // sides of the pending drops
     int lenI = 0, lenK = 0;         // their new_len
     bool emit = false;              // a complete k-mer window ends at `end`
+    bool fresh = false;             // the character at `end` has not been fetched yet
     uint64_t cur = 0;               // the candidate being shrunk
     int dq_head = 0, dq_n = 0;
     int bestU_pos = -1;
@@ -232,20 +230,15 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
         walking = false;
         pendI = pendK = 0;
         end = 0;
-        fetch_base(packed);
+        fresh = true;
         st = ST_EXT;
     }
 
+    // 2-bit code of the character at `end` of the current strand (reverse complement: read backwards, complemented)
     FIN_D void fetch_base(const uint64_t* __restrict__ packed) {
-        if (strand == 0) {
-            const uint64_t b = b0 + (uint64_t)end;
-            if (end == 0 || (b & 31) == 0) qword = __ldg(packed + (b >> 5));
-            c = (int)((qword >> (2 * (b & 31))) & 3);
-        } else {
-            const uint64_t b = b0 + (uint64_t)(len - 1 - end);
-            if (end == 0 || (b & 31) == 31) qword = __ldg(packed + (b >> 5));
-            c = 3 - (int)((qword >> (2 * (b & 31))) & 3);
-        }
+        const uint64_t b = b0 + (uint64_t)(strand ? len - 1 - end : end);
+        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(packed) + (b >> 4));
+        c = (int)((w >> (2 * (b & 15))) & 3u) ^ (strand ? 3 : 0);
     }
 
     // takes a new read; returns false (and stays idle) when the read has no k-mer
@@ -267,14 +260,8 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
         return true;
     }
 
-    FIN_D void set_drop_I(const IndexView& ix, const int new_len) {
-        if (new_len <= 0) { I.l = 0; I.r = ix.n_nodes - 1; }
-        else { lenI = new_len; pendI = kDropLeft | kDropRight; }
-    }
-    FIN_D void set_drop_K(const IndexView& ix, const int new_len) {
-        if (new_len <= 0) { Ik.l = 0; Ik.r = ix.n_nodes - 1; }
-        else { lenK = new_len; pendK = kDropLeft | kDropRight; }
-    }
+    FIN_D void set_drop_I(const int new_len) { lenI = new_len; pendI = kDropLeft | kDropRight; }
+    FIN_D void set_drop_K(const int new_len) { lenK = new_len; pendK = kDropLeft | kDropRight; }
 
     // dq: the KCAP slots of the candidate window, a separate array so that the scalar state stays in registers
     FIN_D void step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc, const int n_strands, uint64_t* dq);
@@ -289,13 +276,15 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
     // ---- A: extend both intervals with the current character (common.hh:114-143).  ST_EXTK = the finimizer
     //         interval is already extended, only the k-mer interval is being contracted and retried.
     if ((pendI | pendK) == 0 && st <= ST_EXTK) {
-        const bool both = st == ST_EXT;
-        Ival JI = I;
-        if (both) {
-            JI = extend(ix, I, c);
-            if (COUNT) rc.c_rank += 2;
+        if (fresh) {
+            fetch_base(packed);
+            fresh = false;
         }
-        const Ival JK = extend(ix, Ik, c);  // speculative in ST_EXT: unused when the k-mer interval follows I
+        const bool both = st == ST_EXT;
+        // all four ranks at once (the k-mer interval speculatively: unused when it follows I)
+        const Ival JI = extend(ix, I, c);
+        const Ival JK = extend(ix, Ik, c);
+        if (COUNT && both) rc.c_rank += 2;
         if (both && is_empty(JI)) {         // :116-126 contract the finimizer interval from the left and retry
             kmer_start = ++start;
             if (start > end) {
@@ -305,7 +294,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                 emit = false;
                 st = ST_EMIT;
             } else {
-                set_drop_I(ix, end - start);
+                set_drop_I(end - start);
             }
         } else {
             if (both) I = JI;
@@ -316,7 +305,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                 if (COUNT) rc.c_rank += 2;
                 if (is_empty(JK)) {
                     kmer_start++;
-                    set_drop_K(ix, end - kmer_start);
+                    set_drop_K(end - kmer_start);
                     st = ST_EXTK;
                 } else {
                     Ik = JK;
@@ -327,32 +316,57 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
     }
 
     FIN_PHASE_FENCE();
-    // ---- B: both intervals stand for this character
-    if (st == ST_POST) {
-        if (Ik.l == Ik.r) {  // :167 rightmost unitig start among the singleton k-mer intervals
-            if (COUNT) rc.c_ustart++;
-            if (ustart_bit(ix, Ik.l)) {
-                bestU_pos = end;
-                bestU_col = Ik.l;
-            }
-        }
+    // ---- B: both intervals stand for this character.  Decisions first (pure arithmetic), then every load of this
+    //         phase and of the drops in one batch, so that the chain waits for memory once, not five times.
+    const bool post = st == ST_POST;
+    const bool single = post && Ik.l == Ik.r;  // :167 rightmost unitig start among the singleton k-mer intervals
+    const idx_t ucol = Ik.l;
+    if (post) {
         emit = end - kmer_start + 1 == k;  // :170
-        if (emit) set_drop_K(ix, k - 1);   // :181, independent of the shrink below
+        if (emit) set_drop_K(k - 1);       // :181, independent of the shrink below
         if (I.l == I.r) {                  // :145-154 shrink to the shortest unique suffix
             cur = cand_pack(end - start + 1, I.l, end);
             start++;
-            set_drop_I(ix, end - start + 1);
+            set_drop_I(end - start + 1);
             st = ST_SHRINK;
         } else {
             st = ST_EMIT;
         }
     }
-
-    FIN_PHASE_FENCE();
-    // ---- F: one word step of every pending drop_first_char
-    if (pendI) pendI = drop_step<WIDE, COUNT>(ix, I, lenI, pendI, rc.c_lcs);
-    FIN_PHASE_FENCE();
-    if (pendK) pendK = drop_step<WIDE, COUNT>(ix, Ik, lenK, pendK, rc.c_lcs);
+    // ---- F: one word step of every pending drop_first_char (common.hh:38-48)
+    if (pendI && lenI <= 0) {  // :39-41 nothing left of the string: the whole range
+        I.l = 0;
+        I.r = N - 1;
+        pendI = 0;
+    }
+    if (pendK && lenK <= 0) {
+        Ik.l = 0;
+        Ik.r = N - 1;
+        pendK = 0;
+    }
+    {
+        const uint64_t* __restrict__ lw = reinterpret_cast<const uint64_t*>(ix.lines);
+        const uint32_t* __restrict__ l32 = reinterpret_cast<const uint32_t*>(ix.lines);
+        const idx_t il = I.l, ir = I.r + 1, kl = Ik.l, kr = Ik.r + 1;
+        uint32_t uw = 0;
+        uint64_t w_il = 0, w_ir = 0, w_kl = 0, w_kr = 0;
+        if (single) uw = __ldg(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
+        if (pendI & kDropLeft) w_il = __ldg(lw + lcs_word_index(il));
+        if (pendI & kDropRight) w_ir = __ldg(lw + lcs_word_index(ir));
+        if (pendK & kDropLeft) w_kl = __ldg(lw + lcs_word_index(kl));
+        if (pendK & kDropRight) w_kr = __ldg(lw + lcs_word_index(kr));
+        if (single) {
+            if (COUNT) rc.c_ustart++;
+            if ((uw >> (ucol & 31)) & 1u) {
+                bestU_pos = end;
+                bestU_col = ucol;
+            }
+        }
+        if (pendI & kDropLeft) drop_left<WIDE, COUNT>(w_il, I, lenI, pendI, rc.c_lcs);
+        if (pendI & kDropRight) drop_right<WIDE, COUNT>(w_ir, I, lenI, pendI, N, rc.c_lcs);
+        if (pendK & kDropLeft) drop_left<WIDE, COUNT>(w_kl, Ik, lenK, pendK, rc.c_lcs);
+        if (pendK & kDropRight) drop_right<WIDE, COUNT>(w_kr, Ik, lenK, pendK, N, rc.c_lcs);
+    }
     FIN_PHASE_FENCE();
 
     // ---- D: shrink loop condition (:154) and the candidate window (:155-164)
@@ -360,7 +374,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         if (I.l == I.r) {
             cur = cand_pack(end - start + 1, I.l, end);
             start++;
-            set_drop_I(ix, end - start + 1);
+            set_drop_I(end - start + 1);
         } else {
             // monotone window: drop the candidates that are larger than the new one, then append it.  Front and
             // back live in registers, so only a pop touches the slots.
@@ -489,7 +503,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
             if (strand < n_strands) begin_strand(ix, packed);
             else st = ST_IDLE;
         } else {
-            fetch_base(packed);
+            fresh = true;
             st = ST_EXT;
         }
     }
