@@ -1,6 +1,7 @@
 // build-fmin on the device: host driver around the kernels of build_kernels.cuh.  Reproduces
 // FinimizerIndexBuilder's constructor (include/FinimizerIndex.hh:273-319), the build_fmin driver
 // (include/build_fmin.hh:302-401) and FinimizerIndex::serialize (:187-207).
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_select.cuh>
 
@@ -174,6 +175,110 @@ static void build_rarest(SbwtHost&& sbwt, PackedVec&& lcs_file, const SeqBatch& 
     save_index_files(out, out_prefix);
 }
 
+// ---- B5 / B6: --type shortest | verify, statistics only (build_fmin.hh:95-214,252-267) ---------------------------
+// Unitigs stay in FILE order here (no permutation): the shared fmin_found bit vector of B5 makes the result depend on it.
+static std::string build_stats(const SbwtHost& sbwt, const PackedVec& lcs_file, const SeqBatch& unitigs, const std::string& type,
+                               int64_t t) {
+    const int k = (int)sbwt.k;
+    const uint64_t N = (uint64_t)sbwt.n_nodes, U = unitigs.size();
+    if (lcs_file.size() != N) throw format_error("LCS length differs from the number of SBWT columns");
+    check_unitigs(unitigs, k);
+    check_stats_t(t, sbwt.n_nodes);
+
+    DevBuf<uint64_t> d_lines = to_device(make_lines(sbwt, &lcs_file, nullptr, nullptr));
+    IndexView ix{};
+    ix.lines = reinterpret_cast<const uint4*>(d_lines.p);
+    ix.n_nodes = (idx_t)N;
+    ix.k = k;
+    std::vector<uint64_t> order(U), starts;
+    std::iota(order.begin(), order.end(), 0);
+    PackedVec text;
+    pack_unitigs(unitigs, order, text, starts);
+    const PackedVec ends = unitig_ends(unitigs, order, starts);
+    const uint64_t T = text.size();
+    DevBuf<uint64_t> d_text = to_device(text.words, 2);
+    DevBuf<unsigned int> d_err(1);
+    FIN_CUDA(cudaMemset(d_err.p, 0, 4));
+
+    DevBuf<uint64_t> d_keys;
+    uint64_t n_keys = 0;
+    if (type == "shortest") {
+        const std::vector<BuildChunk> chunks = plan_build_chunks(starts, ends, k, 0);
+        const uint32_t nc = (uint32_t)chunks.size();
+        DevBuf<BuildChunk> d_chunks = to_device(chunks);
+        DevBuf<uint32_t> d_first(N), d_runs((size_t)nc + 1);
+        FIN_CUDA(cudaMemset(d_first.p, 0xFF, d_first.bytes()));
+        FIN_CUDA(cudaMemset(d_runs.p, 0, d_runs.bytes()));
+        const unsigned blocks = (nc + 127) / 128;
+        auto launch = [&](auto pass) {
+            constexpr int P = decltype(pass)::value;
+            switch (window_capacity(k)) {
+                case 32: shortest_stream_kernel<32, P><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, (uint32_t)t, d_first.p, d_runs.p, d_keys.p, d_err.p); break;
+                case 64: shortest_stream_kernel<64, P><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, (uint32_t)t, d_first.p, d_runs.p, d_keys.p, d_err.p); break;
+                case 128: shortest_stream_kernel<128, P><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, (uint32_t)t, d_first.p, d_runs.p, d_keys.p, d_err.p); break;
+                default: shortest_stream_kernel<256, P><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, (uint32_t)t, d_first.p, d_runs.p, d_keys.p, d_err.p); break;
+            }
+            g_launches++;
+            FIN_CUDA(cudaGetLastError());
+        };
+        launch(std::integral_constant<int, 0>());
+        {  // run counts -> offsets; the element past the last chunk becomes the total
+            size_t tb = 0;
+            cub::DeviceScan::ExclusiveSum(nullptr, tb, d_runs.p, d_runs.p, (int64_t)nc + 1);
+            DevBuf<uint8_t> tmp(tb + 256);
+            FIN_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tb, d_runs.p, d_runs.p, (int64_t)nc + 1));
+            g_launches += 2;
+        }
+        uint32_t total = 0;
+        FIN_CUDA(cudaMemcpy(&total, d_runs.p + nc, 4, cudaMemcpyDeviceToHost));
+        n_keys = total;
+        d_keys.alloc(n_keys + 1);
+        launch(std::integral_constant<int, 1>());
+    } else {  // verify
+        std::vector<uint32_t> ends32(U);
+        for (uint64_t u = 0; u < U; u++) ends32[u] = (uint32_t)ends.words[u];
+        DevBuf<uint32_t> d_ends = to_device(ends32);
+        DevBuf<uint64_t> d_rec(T + 1);
+        n_keys = T;
+        d_keys.alloc(T + 1);
+        const unsigned blocks = (unsigned)((T + 255) / 256);
+        rare_prefix_kernel<<<blocks, 256>>>(ix, d_text.p, d_ends.p, (uint32_t)U, (uint32_t)T, (uint32_t)t, d_rec.p, d_err.p);
+        verify_window_kernel<<<blocks, 256>>>(d_rec.p, d_ends.p, (uint32_t)U, (uint32_t)T, k, d_keys.p, d_err.p);
+        g_launches += 2;
+        FIN_CUDA(cudaGetLastError());
+    }
+    unsigned err = 0;
+    FIN_CUDA(cudaMemcpy(&err, d_err.p, 4, cudaMemcpyDeviceToHost));
+    if (err)
+        throw domain_error("the unitigs are not a disjoint spectrum-preserving string set of this SBWT "
+                           "(a unitig k-mer is missing from the SBWT or a window has no substring with at most t occurrences)");
+
+    // the std::set of the reference: sort, unique, sum
+    unsigned long long sums[3] = {0, 0, 0};
+    if (n_keys) {
+        DevBuf<uint64_t> d_sorted(n_keys), d_unique(n_keys);
+        DevBuf<uint64_t> d_nuniq(1);
+        size_t tb1 = 0, tb2 = 0;
+        cub::DeviceRadixSort::SortKeys(nullptr, tb1, d_keys.p, d_sorted.p, (int64_t)n_keys);
+        cub::DeviceSelect::Unique(nullptr, tb2, d_sorted.p, d_unique.p, d_nuniq.p, (int64_t)n_keys);
+        DevBuf<uint8_t> tmp(std::max(tb1, tb2) + 256);
+        FIN_CUDA(cub::DeviceRadixSort::SortKeys(tmp.p, tb1, d_keys.p, d_sorted.p, (int64_t)n_keys));
+        FIN_CUDA(cub::DeviceSelect::Unique(tmp.p, tb2, d_sorted.p, d_unique.p, d_nuniq.p, (int64_t)n_keys));
+        g_launches += 10;
+        uint64_t n_unique = 0;
+        FIN_CUDA(cudaMemcpy(&n_unique, d_nuniq.p, 8, cudaMemcpyDeviceToHost));
+        DevBuf<unsigned long long> d_sums(3);
+        FIN_CUDA(cudaMemset(d_sums.p, 0, 24));
+        if (n_unique) {
+            stat_sum_kernel<<<(unsigned)((n_unique + 255) / 256), 256>>>(d_unique.p, n_unique, d_sums.p);
+            g_launches++;
+            FIN_CUDA(cudaGetLastError());
+        }
+        FIN_CUDA(cudaMemcpy(sums, d_sums.p, 24, cudaMemcpyDeviceToHost));
+    }
+    return stats_string(sums[0], sums[1], sums[2], sbwt.n_kmers);
+}
+
 std::string build_fmin_device(const std::string& sbwt_path, const std::string& unitig_path, const std::string& out_prefix,
                               const std::string& type, int64_t t_arg, const std::string& lcs_path, int device) {
     const signed char t = (signed char)t_arg;  // build_fmin.hh:333 narrows to char
@@ -200,7 +305,7 @@ std::string build_fmin_device(const std::string& sbwt_path, const std::string& u
         if (t != 1) throw domain_error("t != 1 does not make sense with rarest type");  // :245-247
         build_rarest(std::move(sbwt), std::move(lcs), unitigs, out_prefix);
     } else {
-        throw arg_error("--type " + type + ": the stats-only modes are not built yet in this library");
+        result = build_stats(sbwt, lcs, unitigs, type, t);
     }
     append_stats_line(out_prefix, (int)t, result);
     return result;

@@ -145,6 +145,21 @@ inline PackedVec pack_offsets(const std::vector<uint32_t>& offs) {
     return p;
 }
 
+// print_finimizer_stats (common.hh:188-197): "<#finimizers>,<sum freq>,<mean freq>,<mean len>,<#k-mers>", the means in
+// float and printed by std::to_string(float)
+inline std::string stats_string(uint64_t n_fmin, uint64_t sum_freq, uint64_t sum_len, int64_t n_kmers) {
+    return std::to_string((int64_t)n_fmin) + "," + std::to_string((int64_t)sum_freq) + "," +
+           std::to_string(static_cast<float>((int64_t)sum_freq) / static_cast<float>((int64_t)n_fmin)) + "," +
+           std::to_string(static_cast<float>((int64_t)sum_len) / static_cast<float>((int64_t)n_fmin)) + "," + std::to_string(n_kmers);
+}
+
+// the parity domain of the statistics modes: 1 <= t <= 127 (the reference narrows t to char, build_fmin.hh:333)
+// and t < n_nodes (with t >= n_nodes its shrink loop never ends, build_fmin.hh:155-166)
+inline void check_stats_t(int64_t t, int64_t n_nodes) {
+    if (t < 1 || t > 127) throw domain_error("-t outside 1..127 (the reference narrows it to char)");
+    if (t >= n_nodes) throw domain_error("-t is not smaller than the number of SBWT columns (the reference does not terminate)");
+}
+
 inline void append_stats_line(const std::string& out_prefix, int t, const std::string& result) {  // build_fmin.hh:386-395
     const std::string stats_path = out_prefix + "_stats.txt";
     FILE* sf = fopen(stats_path.c_str(), "ab");

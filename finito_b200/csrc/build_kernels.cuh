@@ -194,6 +194,141 @@ FIN_D void build_stream_chunk(const IndexView& ix, const uint64_t* __restrict__ 
     if (err) fin_atomic_or(error_flags, err);
 }
 
+// =====================================================================================================
+// B5  build_shortest_streaming_search (include/build_fmin.hh:134-200) over chunks — statistics only
+// =====================================================================================================
+// Candidates are triggered by freq <= t instead of freq == 1 and ordered by (len, freq, colex, end) (:161).  Packed
+// so that the unsigned order is that tuple order: len:8 | freq:8 | colex:32 | end:16 (end relative to the chunk,
+// < 2^16 by the chunk plan; freq <= t <= 127 because the reference narrows t to char, :333).  The reference's
+// clear()/pop_back()/pop_front() dance (:168-176, :192-195) is a monotone window minimum whenever every window
+// holds a candidate, which is the case for unitigs of the SBWT (DESIGN.md "stats modes").
+FIN_D uint64_t scand_pack(int len, uint32_t freq, idx_t colex, uint32_t end_rel) {
+    return ((uint64_t)(uint32_t)len << 56) | ((uint64_t)freq << 48) | ((uint64_t)colex << 16) | (uint64_t)end_rel;
+}
+FIN_D int scand_len(uint64_t c) { return (int)(c >> 56); }
+FIN_D idx_t scand_colex(uint64_t c) { return (idx_t)(c >> 16); }
+FIN_D int scand_end(uint64_t c) { return (int)(c & 0xFFFFu); }
+FIN_D int scand_start(uint64_t c) { return scand_end(c) - scand_len(c) + 1; }
+// the (len, freq, colex) tuple of the statistics set (:183), as one sortable key
+FIN_D uint64_t stat_key(uint64_t c) { return c >> 16; }
+constexpr uint64_t kNoStatKey = ~0ULL;
+
+// The insertion rule (:182-187) depends on the order of the windows: (len,freq,colex) is inserted while
+// fmin_found[colex] is unset, and fmin_found[colex] is set by the first window whose finimizer ends at or after
+// position k-1 of its unitig.  Closed form: with order(window) = global text position of the window in FILE order,
+// a window inserts its tuple iff order <= first_flag[colex] = min order over the flagged windows of that colex.
+//   PASS 0: first_flag[colex] = atomicMin(order) over flagged windows; runs per chunk counted
+//   PASS 1: one key per run of equal window minima: the tuple if it is inserted, kNoStatKey otherwise
+// Returns the number of runs of the chunk.
+#ifdef FIN_EMU
+inline void fin_atomic_min(uint32_t* p, uint32_t v) { if (*p > v) *p = v; }
+#else
+FIN_D void fin_atomic_min(uint32_t* p, uint32_t v) { atomicMin(p, v); }
+#endif
+
+template <int KCAP, int PASS>
+FIN_D uint32_t shortest_stream_chunk(const IndexView& ix, const uint64_t* __restrict__ text, const BuildChunk ch, const uint32_t t,
+                                     uint32_t* __restrict__ first_flag, uint64_t* __restrict__ out_keys,
+                                     unsigned int* __restrict__ error_flags) {
+    const int k = ix.k;
+    const idx_t N = ix.n_nodes;
+    uint64_t dq[KCAP];
+    int dq_head = 0, dq_n = 0;
+    unsigned dummy = 0, err = 0;
+    Ival I{0, N - 1};
+    int64_t start = ch.first_pos;
+    uint64_t last_w = kNoStatKey, word = 0;
+    uint32_t n_runs = 0;
+    for (uint32_t s = 0; s < ch.n_stream; s++) {
+        const uint64_t tp = (uint64_t)ch.text_begin + s;
+        if (s == 0 || (tp & 31) == 0) word = __ldg(text + (tp >> 5));
+        const int c = (int)((word >> (2 * (tp & 31))) & 3);
+        const int64_t end = (int64_t)ch.first_pos + s;
+        I = extend(ix, I, c);  // :150
+        if (is_empty(I)) {
+            err |= kErrLookupRange;
+            break;
+        }
+        const int64_t kmer = end - (k - 1);
+        if (I.r - I.l < t) {  // freq <= t (:154)
+            uint64_t cur;
+            do {              // :155-166 shrink to the shortest suffix that is still rare enough
+                cur = scand_pack((int)(end - start + 1), I.r - I.l + 1, I.l, s);
+                start++;
+                I = drop_first_char<(KCAP > 128), false>(ix, (int)(end - start + 1), I, dummy);
+            } while (I.r - I.l < t);
+            while (dq_n > 0 && (int64_t)ch.first_pos + scand_start(dq[dq_head]) < kmer) {
+                dq_head = (dq_head + 1) & (KCAP - 1);
+                dq_n--;
+            }
+            while (dq_n > 0 && dq[(dq_head + dq_n - 1) & (KCAP - 1)] > cur) dq_n--;
+            if (dq_n == KCAP) {
+                err |= kErrWindowUnderflow;
+                dq_n--;
+            }
+            dq[(dq_head + dq_n) & (KCAP - 1)] = cur;
+            dq_n++;
+        }
+        if (end >= (int64_t)ch.first_emit) {  // :181
+            while (dq_n > 0 && (int64_t)ch.first_pos + scand_start(dq[dq_head]) < kmer) {
+                dq_head = (dq_head + 1) & (KCAP - 1);
+                dq_n--;
+            }
+            if (dq_n == 0) {  // the reference would index fmin_found with its sentinel n_nodes here
+                err |= kErrWindowUnderflow;
+            } else {
+                const uint64_t w = dq[dq_head];
+                if (w != last_w) {
+                    last_w = w;
+                    const uint32_t order = ch.unitig_start + (uint32_t)kmer;
+                    const idx_t colex = scand_colex(w);
+                    if (PASS == 0) {
+                        const bool flagged = ch.first_pos + (uint32_t)scand_end(w) >= (uint32_t)(k - 1);  // :184
+                        if (flagged) fin_atomic_min(first_flag + colex, order);
+                    } else {
+                        out_keys[n_runs] = order <= first_flag[colex] ? stat_key(w) : kNoStatKey;
+                    }
+                    n_runs++;
+                }
+            }
+        }
+    }
+    if (err) fin_atomic_or(error_flags, err);
+    return n_runs;
+}
+
+// =====================================================================================================
+// B6  verify_shortest_streaming_search (include/build_fmin.hh:95-132) — statistics only
+// =====================================================================================================
+// The reference tries all k(k+1)/2 substrings of every window.  For a fixed start the tuple (len, freq, colex, end)
+// grows with the end, so only the SHORTEST prefix with freq <= t of every start can win, and that prefix does not
+// depend on the window: step 1 computes it once per text position, step 2 takes, per window, the minimum over its k
+// starts of those that end inside the window.  The set only keeps (len, freq, colex), so ties on `end` are moot.
+// rec = stat key of the shortest prefix of text[p ..) with freq <= t, at most `limit` long; kNoStatKey if none.
+FIN_D uint64_t shortest_rare_prefix(const IndexView& ix, const uint64_t* __restrict__ text, const uint64_t p, const int limit,
+                                    const uint32_t t, unsigned& err) {
+    Ival I{0, ix.n_nodes - 1};
+    for (int j = 0; j < limit; j++) {
+        I = extend(ix, I, text_base(text, p + (uint64_t)j));
+        if (is_empty(I)) {  // the reference would continue with {-1,-1} and freq 1: a unitig that is not in the SBWT
+            err |= kErrLookupRange;
+            return kNoStatKey;
+        }
+        if (I.r - I.l < t) return stat_key(scand_pack(j + 1, I.r - I.l + 1, I.l, 0));
+    }
+    return kNoStatKey;
+}
+
+// window [p, p+k): min over its starts s of rec[s] with s + len(rec[s]) <= p + k
+FIN_D uint64_t verify_window_min(const uint64_t* __restrict__ rec, const uint64_t p, const int k) {
+    uint64_t best = kNoStatKey;
+    for (int j = 0; j < k; j++) {
+        const uint64_t r = rec[p + (uint64_t)j];
+        if (r != kNoStatKey && j + (int)(r >> 40) <= k && r < best) best = r;
+    }
+    return best;
+}
+
 #ifdef __CUDACC__
 // ones per 64-column word of each row -> (after an exclusive scan) destination of the word's first edge
 static __global__ void row_popcount_kernel(const uint64_t* __restrict__ rows, uint64_t n_words, uint32_t* __restrict__ counts) {
@@ -238,6 +373,70 @@ static __global__ void fmin_bits_kernel(const unsigned long long* __restrict__ t
     const unsigned mask = __ballot_sync(0xFFFFFFFFu, key != 0ULL);
     if ((threadIdx.x & 31) == 0 && i < ((n + 31) / 32) * 32) bits32[i >> 5] = mask;
     if (i < n) offs_or_sentinel[i] = key ? fmin_key_offset(key) : 0xFFFFFFFFu;
+}
+
+// ---- statistics modes (B5, B6) ------------------------------------------------------------------------------
+template <int KCAP, int PASS>
+__global__ void __launch_bounds__(128) shortest_stream_kernel(const IndexView ix, const uint64_t* __restrict__ text,
+                                                              const BuildChunk* __restrict__ chunks, uint32_t n_chunks, uint32_t t,
+                                                              uint32_t* __restrict__ first_flag, uint32_t* __restrict__ runs,
+                                                              uint64_t* __restrict__ out_keys, unsigned int* __restrict__ error_flags) {
+    const uint32_t cid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cid >= n_chunks) return;
+    if (PASS == 0) runs[cid] = shortest_stream_chunk<KCAP, 0>(ix, text, chunks[cid], t, first_flag, nullptr, error_flags);
+    else shortest_stream_chunk<KCAP, 1>(ix, text, chunks[cid], t, first_flag, out_keys + runs[cid], error_flags);  // runs = offsets now
+}
+
+// index of the unitig that holds text position p: first u with ends[u] > p
+FIN_D uint32_t unitig_of(const uint32_t* __restrict__ ends, uint32_t n_unitigs, uint32_t p) {
+    uint32_t lo = 0, hi = n_unitigs;
+    while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(ends + mid) > p) hi = mid;
+        else lo = mid + 1;
+    }
+    return lo;
+}
+
+static __global__ void rare_prefix_kernel(const IndexView ix, const uint64_t* __restrict__ text, const uint32_t* __restrict__ ends,
+                                          uint32_t n_unitigs, uint32_t text_len, uint32_t t, uint64_t* __restrict__ rec,
+                                          unsigned int* __restrict__ error_flags) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= text_len) return;
+    const uint32_t e = __ldg(ends + unitig_of(ends, n_unitigs, (uint32_t)p));
+    unsigned err = 0;
+    rec[p] = shortest_rare_prefix(ix, text, p, (int)min((uint32_t)ix.k, e - (uint32_t)p), t, err);
+    if (err) atomicOr(error_flags, err);
+}
+
+static __global__ void verify_window_kernel(const uint64_t* __restrict__ rec, const uint32_t* __restrict__ ends, uint32_t n_unitigs,
+                                            uint32_t text_len, int k, uint64_t* __restrict__ keys,
+                                            unsigned int* __restrict__ error_flags) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= text_len) return;
+    const uint32_t e = __ldg(ends + unitig_of(ends, n_unitigs, (uint32_t)p));
+    uint64_t key = kNoStatKey;
+    if (p + (uint64_t)k <= e) {
+        key = verify_window_min(rec, p, k);
+        if (key == kNoStatKey) atomicOr(error_flags, kErrWindowUnderflow);  // the reference inserts its sentinel (k+1, N, N)
+    }
+    keys[p] = key;
+}
+
+// sums[0] += valid keys, sums[1] += their freq, sums[2] += their len   (print_finimizer_stats, common.hh:188-197)
+static __global__ void stat_sum_kernel(const uint64_t* __restrict__ keys, uint64_t n, unsigned long long* __restrict__ sums) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t key = i < n ? keys[i] : kNoStatKey;
+    const bool valid = key != kNoStatKey;
+    unsigned cnt = valid ? 1u : 0u, fr = valid ? (unsigned)((key >> 32) & 0xFFu) : 0u, ln = valid ? (unsigned)(key >> 40) : 0u;
+    cnt = __reduce_add_sync(0xFFFFFFFFu, cnt);
+    fr = __reduce_add_sync(0xFFFFFFFFu, fr);
+    ln = __reduce_add_sync(0xFFFFFFFFu, ln);
+    if ((threadIdx.x & 31) == 0 && cnt) {
+        atomicAdd(sums, (unsigned long long)cnt);
+        atomicAdd(sums + 1, (unsigned long long)fr);
+        atomicAdd(sums + 2, (unsigned long long)ln);
+    }
 }
 
 struct NotSentinel {

@@ -196,4 +196,82 @@ int emu_build(const char* sbwt_path, const char* unitig_path, const char* out_pr
     });
 }
 
+
+// build-fmin --type shortest|verify with the kernel bodies (one "thread" after the other); result = the stats string
+int emu_stats(const char* sbwt_path, const char* unitig_path, const char* type_c, int64_t t, uint64_t per_chunk, char* result,
+              uint64_t cap) {
+    return guarded([&] {
+        const std::string type = type_c;
+        const std::vector<std::string> files = unitig_file_list(unitig_path);
+        SbwtHost sbwt = load_sbwt_file(sbwt_path, true);
+        check_sbwt_limits(sbwt);
+        const uint64_t N = (uint64_t)sbwt.n_nodes;
+        const int k = (int)sbwt.k;
+        check_stats_t(t, sbwt.n_nodes);
+        PackedVec lcs_file = lcs_bytes_to_packed(emu_lcs_bytes(sbwt), N, k);
+        SeqBatch unitigs;
+        append_sequences(files[0], unitigs);
+        check_unitigs(unitigs, k);
+        const uint64_t U = unitigs.size();
+        std::vector<uint64_t> lines = make_lines(sbwt, &lcs_file, nullptr, nullptr);
+        IndexView ix{};
+        ix.lines = reinterpret_cast<const uint4*>(lines.data());
+        ix.n_nodes = (idx_t)N;
+        ix.k = k;
+        std::vector<uint64_t> order(U), starts;
+        for (uint64_t u = 0; u < U; u++) order[u] = u;
+        PackedVec text;
+        pack_unitigs(unitigs, order, text, starts);
+        text.words.resize(text.words.size() + 2, 0);
+        PackedVec ends = unitig_ends(unitigs, order, starts);
+        const uint64_t T = text.size();
+        unsigned err = 0;
+        std::vector<uint64_t> keys;
+        if (type == "shortest") {
+            std::vector<BuildChunk> chunks = plan_build_chunks(starts, ends, k, per_chunk);
+            std::vector<uint32_t> first(N, 0xFFFFFFFFu), runs(chunks.size() + 1, 0);
+            auto run = [&](auto pass, size_t c, uint64_t* out) -> uint32_t {
+                constexpr int P = decltype(pass)::value;
+                if (k <= 32) return shortest_stream_chunk<32, P>(ix, text.words.data(), chunks[c], (uint32_t)t, first.data(), out, &err);
+                if (k <= 64) return shortest_stream_chunk<64, P>(ix, text.words.data(), chunks[c], (uint32_t)t, first.data(), out, &err);
+                if (k <= 128) return shortest_stream_chunk<128, P>(ix, text.words.data(), chunks[c], (uint32_t)t, first.data(), out, &err);
+                return shortest_stream_chunk<256, P>(ix, text.words.data(), chunks[c], (uint32_t)t, first.data(), out, &err);
+            };
+            // the chunks in REVERSE order: the result must not depend on the order the "threads" run in
+            uint64_t total = 0;
+            for (size_t c = chunks.size(); c-- > 0;) runs[c] = run(std::integral_constant<int, 0>(), c, nullptr);
+            for (size_t c = 0; c < chunks.size(); c++) { const uint32_t n = runs[c]; runs[c] = (uint32_t)total; total += n; }
+            keys.assign(total + 1, kNoStatKey);
+            for (size_t c = chunks.size(); c-- > 0;) run(std::integral_constant<int, 1>(), c, keys.data() + runs[c]);
+        } else if (type == "verify") {
+            std::vector<uint64_t> rec(T + 1, kNoStatKey);
+            uint64_t u = 0;
+            for (uint64_t p = 0; p < T; p++) {
+                while (ends.words[u] <= p) u++;
+                rec[p] = shortest_rare_prefix(ix, text.words.data(), p, (int)std::min<uint64_t>((uint64_t)k, ends.words[u] - p), (uint32_t)t, err);
+            }
+            u = 0;
+            for (uint64_t p = 0; p < T; p++) {
+                while (ends.words[u] <= p) u++;
+                if (p + (uint64_t)k <= ends.words[u]) {
+                    const uint64_t key = verify_window_min(rec.data(), p, k);
+                    if (key == kNoStatKey) err |= kErrWindowUnderflow;
+                    keys.push_back(key);
+                }
+            }
+        } else {
+            throw arg_error("emu_stats: type");
+        }
+        if (err) throw domain_error("emu: stats stream error flags " + std::to_string(err));
+        std::sort(keys.begin(), keys.end());
+        keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
+        uint64_t n = 0, sf = 0, sl = 0;
+        for (uint64_t key : keys)
+            if (key != kNoStatKey) { n++; sf += (key >> 32) & 0xFF; sl += key >> 40; }
+        const std::string r = stats_string(n, sf, sl, sbwt.n_kmers);
+        if (r.size() + 1 > cap) throw arg_error("buffer too small");
+        memcpy(result, r.c_str(), r.size() + 1);
+    });
+}
+
 }  // extern "C"

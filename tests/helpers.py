@@ -131,6 +131,7 @@ def emu_lib() -> C.CDLL:
                                C.c_void_p, C.c_int]
     lib.emu_lcs.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_uint64]
     lib.emu_build.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]
+    lib.emu_stats.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_uint64, C.c_char_p, C.c_uint64]
     return lib
 
 
@@ -156,6 +157,14 @@ def emu_build(sbwt, unitigs, prefix, per_chunk=0):
     lib = emu_lib()
     if lib.emu_build(os.fsencode(sbwt), os.fsencode(unitigs), os.fsencode(prefix), per_chunk):
         raise RuntimeError("emu: " + lib.emu_last_error().decode())
+
+
+def emu_stats(sbwt, unitigs, type, t, per_chunk=0) -> str:
+    lib = emu_lib()
+    buf = C.create_string_buffer(512)
+    if lib.emu_stats(os.fsencode(sbwt), os.fsencode(unitigs), type.encode(), t, per_chunk, buf, 512):
+        raise RuntimeError("emu: " + lib.emu_last_error().decode())
+    return buf.value.decode()
 
 
 def sbwt_header(path, with_variant=True) -> dict:

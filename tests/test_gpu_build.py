@@ -63,3 +63,37 @@ def test_build_with_given_lcs_and_error_paths(gpu_lib, tmp_path):
     with pytest.raises(fb.FinitoError) as e:  # the index member has no variant header
         fb.build_fmin(os.path.join(d, "ref.sbwt"), os.path.join(d, "unitigs.fna"), prefix)
     assert e.value.status == fb.FIN_ERR_FORMAT
+
+
+@pytest.mark.parametrize("case", golden_cases())
+def test_golden_stats_modes(case, gpu_lib, tmp_path):
+    """BASELINE.json configs[2]: --type shortest|verify -t T print statistics only (build_fmin.hh:95-214)."""
+    import json
+
+    fb = gpu_lib
+    d = os.path.join(H.GOLDEN, case)
+    for mode, line in json.load(open(os.path.join(H.GOLDEN, "stats_modes.json")))[case].items():
+        typ, t = mode.split(":")
+        prefix = str(tmp_path / f"gpu_{typ}_{t}")
+        got = fb.build_fmin(os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), prefix, type=typ, t=int(t))
+        assert f"{t},{got}\n" == line, (case, mode)
+        assert open(prefix + "_stats.txt").read() == line
+        assert os.path.exists(prefix + ".LCS.sdsl") and not os.path.exists(prefix + ".FBV.sdsl")
+
+
+@pytest.mark.parametrize("k,genome_len,t", [(31, 1_000_000, 4), (63, 300_000, 2), (20, 200_000, 16)])
+def test_synthetic_stats_modes_match_oracle(k, genome_len, t, gpu_lib, tmp_path):
+    fb = gpu_lib
+    ds = make_dataset("gpub", genome_len=genome_len, k=k, n_reads=2000, read_len=150, seed=100 + k)
+    for typ in ("shortest", "verify"):
+        want = H.oracle_build(ds["sbwt"], ds["unitigs"], str(tmp_path / f"orc_{typ}"), type=typ, t=t)
+        assert fb.build_fmin(ds["sbwt"], ds["unitigs"], str(tmp_path / f"gpu_{typ}"), type=typ, t=t) == want, typ
+
+
+def test_stats_modes_reject_out_of_domain_t(gpu_lib, tmp_path):
+    fb = gpu_lib
+    d = os.path.join(H.GOLDEN, "kat_paper_example")
+    for t in (0, 128, 18):  # 18 columns: with t >= n_nodes the reference's shrink loop never terminates
+        with pytest.raises(fb.FinitoError) as e:
+            fb.build_fmin(os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), str(tmp_path / "x"), type="shortest", t=t)
+        assert e.value.status == fb.FIN_ERR_DOMAIN

@@ -53,3 +53,30 @@ def test_search_and_build_bodies_match_oracle_on_synthetic(k, genome_len, tmp_pa
     for name in ("n_rank", "n_lcs_reads", "n_ustart_reads", "n_anchor", "n_anchor_branch", "n_walk_words", "n_bases", "n_kmers"):
         assert acc[name] == oc[name], name
     assert 0.5 < wc[2] / wc[3] < 0.95  # most k-mers of 1 %-error reads are found
+
+
+def stats_modes():
+    import json
+
+    return json.load(open(os.path.join(H.GOLDEN, "stats_modes.json")))
+
+
+@pytest.mark.parametrize("case", golden_cases())
+@pytest.mark.parametrize("per_chunk", [0, 1, 7])
+def test_stats_mode_bodies_match_reference(case, per_chunk):
+    """--type shortest|verify -t T (build_fmin.hh:95-214): the stats line the reference binary wrote."""
+    d = os.path.join(H.GOLDEN, case)
+    for mode, line in stats_modes()[case].items():
+        typ, t = mode.split(":")
+        if typ == "verify" and per_chunk:
+            continue
+        got = H.emu_stats(os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), typ, int(t), per_chunk)
+        assert f"{t},{got}\n" == line, (case, mode)
+
+
+@pytest.mark.parametrize("k,genome_len,t", [(31, 150_000, 4), (63, 60_000, 2), (17, 40_000, 9)])
+def test_stats_mode_bodies_match_oracle_on_synthetic(k, genome_len, t, tmp_path):
+    ds = make_dataset("cpu", genome_len=genome_len, k=k, n_reads=400, read_len=150, seed=k)
+    for typ in ("shortest", "verify"):
+        want = H.oracle_build(ds["sbwt"], ds["unitigs"], str(tmp_path / f"orc_{typ}"), type=typ, t=t)
+        assert H.emu_stats(ds["sbwt"], ds["unitigs"], typ, t) == want, typ

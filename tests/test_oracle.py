@@ -70,3 +70,15 @@ def test_reference_own_tests_pass(tmp_path):
 
     r = subprocess.run([os.path.join(H.REF_DIR, "finito_ref_tests")], cwd=tmp_path, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-2000:]
+
+
+@pytest.mark.parametrize("case", golden_cases())
+def test_oracle_stats_modes_match_reference(case, tmp_path):
+    """--type shortest|verify -t T: the `<t>,<stats>` line written by the unmodified reference binary."""
+    import json
+
+    d = os.path.join(H.GOLDEN, case)
+    for mode, line in json.load(open(os.path.join(H.GOLDEN, "stats_modes.json")))[case].items():
+        typ, t = mode.split(":")
+        got = H.oracle_build(os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), str(tmp_path / "x"), type=typ, t=int(t))
+        assert f"{t},{got}\n" == line, (case, mode)
