@@ -49,6 +49,12 @@ class _Timing(C.Structure):
     _fields_ = [(n, C.c_float) for n in ("pipeline_ms", "prepare_ms", "search_kernel_ms")]
 
 
+class _BuilderInfo(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("n_nodes", "slice_columns", "slice_words", "text_len", "n_unitigs", "n_chunks",
+                                         "chunk_begin", "chunk_end", "bases_streamed")] + \
+               [("rank", C.c_int32), ("world", C.c_int32), ("stream_ms", C.c_float)]
+
+
 # every symbol include/finito_b200.h declares: name -> (restype, argtypes)
 _u64p = C.POINTER(C.c_uint64)
 ABI = {
@@ -76,6 +82,15 @@ ABI = {
     "fin_build": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int, C.c_char_p,
                             C.c_size_t]),
     "fin_lcs": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, _u64p]),
+    "fin_builder_open": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int,
+                                   C.POINTER(C.c_void_p)]),
+    "fin_builder_free": (None, [C.c_void_p]),
+    "fin_builder_info_get": (C.c_int, [C.c_void_p, C.POINTER(_BuilderInfo)]),
+    "fin_builder_stream": (C.c_int, [C.c_void_p, _u64p]),
+    "fin_builder_export": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
+    "fin_builder_merge": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, _u64p]),
+    "fin_builder_slice": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fin_builder_finish": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_char_p]),
 }
 
 _lib = None
@@ -224,6 +239,64 @@ def build_fmin(sbwt_path: str, unitig_path: str, out_prefix: str, type: str = "r
     _check(lib().fin_build(os.fsencode(sbwt_path), os.fsencode(unitig_path), os.fsencode(out_prefix), type.encode(), t,
                            os.fsencode(lcs_path) if lcs_path else None, device, buf, len(buf)))
     return buf.value.decode()
+
+
+class ShardedBuilder:
+    """One rank of build-fmin --type rarest sharded over GPUs (fin_builder_* in include/finito_b200.h; the stages of
+    FinimizerIndexBuilder, include/FinimizerIndex.hh:273-389).  All buffers are raw DEVICE pointers except the
+    per-rank counts and what finish() takes; finito_b200/distributed.py drives it with torch.distributed."""
+
+    memory = "cuda"  # where export/merge/slice buffers live
+
+    def __init__(self, sbwt_path: str, unitig_path: str, out_prefix: str, rank: int, world: int, device: int = 0,
+                 lcs_path: str | None = None):
+        out = C.c_void_p()
+        _check(lib().fin_builder_open(os.fsencode(sbwt_path), os.fsencode(unitig_path),
+                                      os.fsencode(lcs_path) if lcs_path else None, os.fsencode(out_prefix), device, rank, world,
+                                      C.byref(out)))
+        self._h = C.c_void_p(out.value)
+        self.out_prefix = out_prefix
+
+    def close(self) -> None:
+        if self._h:
+            lib().fin_builder_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def info(self) -> dict:
+        i = _BuilderInfo()
+        _check(lib().fin_builder_info_get(self._h, C.byref(i)))
+        return {n: getattr(i, n) for n, _ in _BuilderInfo._fields_}
+
+    def stream(self) -> int:
+        n = C.c_uint64()
+        _check(lib().fin_builder_stream(self._h, C.byref(n)))
+        return int(n.value)
+
+    def export(self, tuples_ptr: int, capacity: int, world: int) -> np.ndarray:
+        counts = np.zeros(world, dtype=np.uint64)
+        _check(lib().fin_builder_export(self._h, tuples_ptr, capacity, counts.ctypes.data))
+        return counts
+
+    def merge(self, tuples_ptr: int, n: int) -> int:
+        out = C.c_uint64()
+        _check(lib().fin_builder_merge(self._h, tuples_ptr, n, C.byref(out)))
+        return int(out.value)
+
+    def slice(self, bits_ptr: int, offsets_ptr: int) -> None:
+        _check(lib().fin_builder_slice(self._h, bits_ptr, offsets_ptr))
+
+    def finish(self, bits_all: np.ndarray, offsets_all: np.ndarray) -> None:
+        bits_all = np.ascontiguousarray(bits_all, dtype=np.uint64)
+        offsets_all = np.ascontiguousarray(offsets_all, dtype=np.uint32)
+        _check(lib().fin_builder_finish(self._h, bits_all.ctypes.data, bits_all.size, offsets_all.ctypes.data, offsets_all.size,
+                                        os.fsencode(self.out_prefix)))
 
 
 def lcs_array(sbwt_path: str, with_variant_header: bool = True, device: int = 0) -> np.ndarray:

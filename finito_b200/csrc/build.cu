@@ -4,6 +4,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_select.cuh>
+#include <cub/iterator/counting_input_iterator.cuh>
 
 #include "build_host.hpp"
 #include "engine.hpp"
@@ -81,98 +82,272 @@ std::vector<uint8_t> lcs_device(const SbwtHost& s, int device) {
 
 static int window_capacity(int k) { return k <= 32 ? 32 : k <= 64 ? 64 : k <= 128 ? 128 : 256; }
 
-// ---- B2-B4: FinimizerIndexBuilder -------------------------------------------------------------------------
-static void build_rarest(SbwtHost&& sbwt, PackedVec&& lcs_file, const SeqBatch& unitigs, const std::string& out_prefix) {
-    const int k = (int)sbwt.k;
-    const uint64_t N = (uint64_t)sbwt.n_nodes, U = unitigs.size();
-    if (lcs_file.size() != N) throw format_error("LCS length differs from the number of SBWT columns");
-    check_unitigs(unitigs, k);
+// ---- B2-B4: FinimizerIndexBuilder, staged so that the stream can be sharded over GPUs ----------------------------
+// world == 1: open -> stream -> merge (nothing to fold) -> finish.
+// world  > 1: every rank opens the same inputs; stream() covers this rank's chunks, export_tuples() hands out the
+// (colex, key) pairs sorted by colex with the number that belongs to every owner, the caller moves them with ONE
+// all-to-all (finito_b200/distributed.py: torch.distributed over NCCL), merge() folds what arrived into this rank's
+// column slice, slice() returns the slice's fmin words and offsets in column order, and rank 0 — after gathering the
+// slices — writes the files in finish().
+struct TableNonZero {
+    const unsigned long long* table;
+    __device__ bool operator()(const uint32_t& i) const { return table[i] != 0ULL; }
+};
 
-    DevBuf<uint64_t> d_lines = to_device(make_lines(sbwt, &lcs_file, nullptr, nullptr));
-    IndexView ix{};
-    ix.lines = reinterpret_cast<const uint4*>(d_lines.p);
-    ix.n_nodes = (idx_t)N;
-    ix.k = k;
+static __global__ void tuple_gather_kernel(const unsigned long long* __restrict__ table, const uint32_t* __restrict__ idx, uint64_t n,
+                                           uint64_t* __restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t colex = idx[i];
+    reinterpret_cast<ulonglong2*>(out)[i] = make_ulonglong2((unsigned long long)colex, table[colex]);
+}
 
-    // first k-mer columns on the file-order text, then the permuted text
-    std::vector<uint64_t> order(U), starts;
-    std::iota(order.begin(), order.end(), 0);
-    PackedVec text;
-    pack_unitigs(unitigs, order, text, starts);
-    DevBuf<uint64_t> d_text = to_device(text.words, 2);
-    DevBuf<uint64_t> d_starts = to_device(starts);
-    DevBuf<uint32_t> d_cols(U);
-    first_kmer_kernel<<<(unsigned)((U + 127) / 128), 128>>>(ix, d_text.p, d_starts.p, (uint32_t)U, d_cols.p);
-    g_launches++;
-    FIN_CUDA(cudaGetLastError());
-    std::vector<uint32_t> cols(U);
-    FIN_CUDA(cudaMemcpy(cols.data(), d_cols.p, U * 4, cudaMemcpyDeviceToHost));
+// bounds[g] = first tuple whose colex >= g * slice_cols (idx ascending), g = 0 .. world
+static __global__ void owner_bounds_kernel(const uint32_t* __restrict__ idx, uint64_t n, uint64_t slice_cols, int world,
+                                           uint64_t* __restrict__ bounds) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g > world) return;
+    const uint64_t want = (uint64_t)g * slice_cols;
+    uint64_t lo = 0, hi = n;
+    while (lo < hi) {
+        const uint64_t mid = (lo + hi) >> 1;
+        if ((uint64_t)idx[mid] >= want) hi = mid;
+        else lo = mid + 1;
+    }
+    bounds[g] = g == world ? n : lo;
+}
 
-    PackedVec ustart;
-    order = unitig_order(cols, N, ustart);
-    pack_unitigs(unitigs, order, text, starts);
-    FIN_CUDA(cudaMemcpy(d_text.p, text.words.data(), text.words.size() * 8, cudaMemcpyHostToDevice));
-    PackedVec ends = unitig_ends(unitigs, order, starts);
+static __global__ void tuple_merge_kernel(const uint64_t* __restrict__ tuples, uint64_t n, uint64_t slice_begin, uint64_t slice_cols,
+                                          unsigned long long* __restrict__ slice_table, unsigned int* __restrict__ error_flags) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const ulonglong2 t = reinterpret_cast<const ulonglong2*>(tuples)[i];
+    const uint64_t local = t.x - slice_begin;
+    if (t.x < slice_begin || local >= slice_cols) {
+        atomicOr(error_flags, kErrLookupRange);
+        return;
+    }
+    atomicMax(slice_table + local, t.y);
+}
 
-    // add_sequence over chunks; overwrite rule as a max over table[colex]
-    const std::vector<BuildChunk> chunks = plan_build_chunks(starts, ends, k, 0);
-    DevBuf<BuildChunk> d_chunks = to_device(chunks);
-    DevBuf<unsigned long long> d_table(N);
-    FIN_CUDA(cudaMemset(d_table.p, 0, d_table.bytes()));
-    DevBuf<unsigned int> d_err(1);
-    FIN_CUDA(cudaMemset(d_err.p, 0, 4));
-    {
-        const unsigned blocks = (unsigned)((chunks.size() + 127) / 128);
-        const uint32_t nc = (uint32_t)chunks.size();
-        switch (window_capacity(k)) {
-            case 32: build_stream_kernel<32><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, d_table.p, d_err.p); break;
-            case 64: build_stream_kernel<64><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, d_table.p, d_err.p); break;
-            case 128: build_stream_kernel<128><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, d_table.p, d_err.p); break;
-            default: build_stream_kernel<256><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, d_table.p, d_err.p); break;
-        }
+class RarestBuilder {
+   public:
+    RarestBuilder(SbwtHost&& sbwt, PackedVec&& lcs_file, const SeqBatch& unitigs, int rank, int world)
+        : sbwt_(std::move(sbwt)), lcs_file_(std::move(lcs_file)), rank_(rank), world_(world) {
+        if (world < 1 || rank < 0 || rank >= world) throw arg_error("build: rank / world out of range");
+        k_ = (int)sbwt_.k;
+        N_ = (uint64_t)sbwt_.n_nodes;
+        const uint64_t U = unitigs.size();
+        if (lcs_file_.size() != N_) throw format_error("LCS length differs from the number of SBWT columns");
+        check_unitigs(unitigs, k_);
+        d_lines_ = to_device(make_lines(sbwt_, &lcs_file_, nullptr, nullptr));
+        ix_.lines = reinterpret_cast<const uint4*>(d_lines_.p);
+        ix_.n_nodes = (idx_t)N_;
+        ix_.k = k_;
+
+        // first k-mer columns on the file-order text, then the permuted text (B2)
+        std::vector<uint64_t> order(U), starts;
+        std::iota(order.begin(), order.end(), 0);
+        pack_unitigs(unitigs, order, text_, starts);
+        d_text_ = to_device(text_.words, 2);
+        DevBuf<uint64_t> d_starts = to_device(starts);
+        DevBuf<uint32_t> d_cols(U);
+        first_kmer_kernel<<<(unsigned)((U + 127) / 128), 128>>>(ix_, d_text_.p, d_starts.p, (uint32_t)U, d_cols.p);
         g_launches++;
         FIN_CUDA(cudaGetLastError());
-    }
-    unsigned err = 0;
-    FIN_CUDA(cudaMemcpy(&err, d_err.p, 4, cudaMemcpyDeviceToHost));
-    if (err)
-        throw domain_error("the unitigs are not a disjoint spectrum-preserving string set of this SBWT "
-                           "(a unitig k-mer is missing from the SBWT or a window has no unique substring)");
+        std::vector<uint32_t> cols(U);
+        FIN_CUDA(cudaMemcpy(cols.data(), d_cols.p, U * 4, cudaMemcpyDeviceToHost));
+        order = unitig_order(cols, N_, ustart_);
+        pack_unitigs(unitigs, order, text_, starts);
+        FIN_CUDA(cudaMemcpy(d_text_.p, text_.words.data(), text_.words.size() * 8, cudaMemcpyHostToDevice));
+        ends_ = unitig_ends(unitigs, order, starts);
 
-    // fmin bit vector and offsets in column order (FinimizerIndex.hh:301-306)
-    const uint64_t n_words32 = (N + 31) / 32;
-    DevBuf<uint32_t> d_bits(n_words32 + 2), d_offs(N), d_sel(N);
-    DevBuf<uint64_t> d_nsel(1);
-    FIN_CUDA(cudaMemset(d_bits.p, 0, d_bits.bytes()));
-    fmin_bits_kernel<<<(unsigned)((n_words32 * 32 + 255) / 256), 256>>>(d_table.p, N, d_bits.p, d_offs.p);
-    g_launches++;
-    FIN_CUDA(cudaGetLastError());
-    {
-        size_t tmp_bytes = 0;
-        cub::DeviceSelect::If(nullptr, tmp_bytes, d_offs.p, d_sel.p, d_nsel.p, (int64_t)N, NotSentinel());
-        DevBuf<uint8_t> tmp(tmp_bytes + 256);
-        FIN_CUDA(cub::DeviceSelect::If(tmp.p, tmp_bytes, d_offs.p, d_sel.p, d_nsel.p, (int64_t)N, NotSentinel()));
-        g_launches += 2;
+        chunks_ = plan_build_chunks(starts, ends_, k_, 0);
+        const std::pair<size_t, size_t> mine = shard_chunks(chunks_, rank, world);
+        chunk_begin_ = mine.first;
+        chunk_end_ = mine.second;
+        slice_cols_ = world == 1 ? N_ : slice_columns(N_, world);
+        slice_begin_ = (uint64_t)rank * slice_cols_;
+        for (size_t c = chunk_begin_; c < chunk_end_; c++) bases_streamed_ += chunks_[c].n_stream;
+        d_err_.alloc(1);
+        FIN_CUDA(cudaMemset(d_err_.p, 0, 4));
     }
-    uint64_t n_fmin = 0;
-    FIN_CUDA(cudaMemcpy(&n_fmin, d_nsel.p, 8, cudaMemcpyDeviceToHost));
-    std::vector<uint32_t> offs(n_fmin);
-    if (n_fmin) FIN_CUDA(cudaMemcpy(offs.data(), d_sel.p, n_fmin * 4, cudaMemcpyDeviceToHost));
 
-    IndexHost out;
-    out.fmin.assign(N, 1);
-    {
-        std::vector<uint32_t> b32(n_words32 + 2, 0);
-        FIN_CUDA(cudaMemcpy(b32.data(), d_bits.p, n_words32 * 4, cudaMemcpyDeviceToHost));
-        memcpy(out.fmin.words.data(), b32.data(), std::min<size_t>(n_words32 * 4, out.fmin.words.size() * 8));
+    uint64_t n_nodes() const { return N_; }
+    uint64_t slice_cols() const { return slice_cols_; }
+    uint64_t text_len() const { return text_.size(); }
+    uint64_t n_unitigs() const { return ends_.size(); }
+    uint64_t n_chunks() const { return chunks_.size(); }
+    uint64_t chunk_begin() const { return chunk_begin_; }
+    uint64_t chunk_end() const { return chunk_end_; }
+    uint64_t bases_streamed() const { return bases_streamed_; }
+    int world() const { return world_; }
+    int rank() const { return rank_; }
+    float stream_ms() const { return stream_ms_; }
+
+    // add_sequence over this rank's chunks; overwrite rule as a max over table[colex] (B3)
+    uint64_t stream() {
+        const size_t nc = chunk_end_ - chunk_begin_;
+        d_table_.alloc(N_);
+        FIN_CUDA(cudaMemset(d_table_.p, 0, d_table_.bytes()));
+        cudaEvent_t e0, e1;
+        FIN_CUDA(cudaEventCreate(&e0));
+        FIN_CUDA(cudaEventCreate(&e1));
+        FIN_CUDA(cudaEventRecord(e0));
+        if (nc) {
+            DevBuf<BuildChunk> d_chunks(nc);
+            FIN_CUDA(cudaMemcpy(d_chunks.p, chunks_.data() + chunk_begin_, nc * sizeof(BuildChunk), cudaMemcpyHostToDevice));
+            const unsigned blocks = (unsigned)((nc + 127) / 128);
+            const uint32_t n32 = (uint32_t)nc;
+            switch (window_capacity(k_)) {
+                case 32: build_stream_kernel<32><<<blocks, 128>>>(ix_, d_text_.p, d_chunks.p, n32, d_table_.p, d_err_.p); break;
+                case 64: build_stream_kernel<64><<<blocks, 128>>>(ix_, d_text_.p, d_chunks.p, n32, d_table_.p, d_err_.p); break;
+                case 128: build_stream_kernel<128><<<blocks, 128>>>(ix_, d_text_.p, d_chunks.p, n32, d_table_.p, d_err_.p); break;
+                default: build_stream_kernel<256><<<blocks, 128>>>(ix_, d_text_.p, d_chunks.p, n32, d_table_.p, d_err_.p); break;
+            }
+            g_launches++;
+            FIN_CUDA(cudaGetLastError());
+            FIN_CUDA(cudaEventRecord(e1));
+            FIN_CUDA(cudaEventSynchronize(e1));
+            FIN_CUDA(cudaEventElapsedTime(&stream_ms_, e0, e1));
+        }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        check_errors();
+        n_tuples_ = 0;
+        if (world_ > 1) {  // the columns this rank has something to say about, ascending
+            d_idx_.alloc(N_);
+            DevBuf<uint64_t> d_n(1);
+            cub::CountingInputIterator<uint32_t> first(0);
+            size_t tb = 0;
+            cub::DeviceSelect::If(nullptr, tb, first, d_idx_.p, d_n.p, (int64_t)N_, TableNonZero{d_table_.p});
+            DevBuf<uint8_t> tmp(tb + 256);
+            FIN_CUDA(cub::DeviceSelect::If(tmp.p, tb, first, d_idx_.p, d_n.p, (int64_t)N_, TableNonZero{d_table_.p}));
+            g_launches += 2;
+            FIN_CUDA(cudaMemcpy(&n_tuples_, d_n.p, 8, cudaMemcpyDeviceToHost));
+        }
+        streamed_ = true;
+        return n_tuples_;
     }
-    out.offsets = pack_offsets(offs);
-    out.sbwt = std::move(sbwt);
-    out.lcs = std::move(lcs_file);
-    out.text = std::move(text);
-    out.ends = std::move(ends);
-    out.ustart = std::move(ustart);
-    save_index_files(out, out_prefix);
+
+    // {u64 colex, u64 key} per tuple into d_out (device), counts[g] = tuples owned by rank g (host, world entries)
+    void export_tuples(uint64_t* d_out, uint64_t capacity, uint64_t* counts) {
+        if (!streamed_) throw arg_error("build: export before stream");
+        if (capacity < n_tuples_) throw arg_error("build: tuple buffer too small");
+        if (world_ == 1) {
+            counts[0] = 0;
+            return;
+        }
+        if (n_tuples_) {
+            tuple_gather_kernel<<<(unsigned)((n_tuples_ + 255) / 256), 256>>>(d_table_.p, d_idx_.p, n_tuples_, d_out);
+            g_launches++;
+        }
+        DevBuf<uint64_t> d_bounds((size_t)world_ + 1);
+        owner_bounds_kernel<<<(unsigned)((world_ + 1 + 63) / 64), 64>>>(d_idx_.p, n_tuples_, slice_cols_, world_, d_bounds.p);
+        g_launches++;
+        FIN_CUDA(cudaGetLastError());
+        std::vector<uint64_t> bounds((size_t)world_ + 1);
+        FIN_CUDA(cudaMemcpy(bounds.data(), d_bounds.p, bounds.size() * 8, cudaMemcpyDeviceToHost));
+        for (int g = 0; g < world_; g++) counts[g] = bounds[(size_t)g + 1] - bounds[(size_t)g];
+    }
+
+    // fold the tuples that arrived for this rank's slice; then fmin bits and offsets of the slice in column order
+    // (FinimizerIndex.hh:301-306).  Returns the number of finimizers in the slice.
+    uint64_t merge(const uint64_t* d_tuples, uint64_t n) {
+        if (!streamed_) throw arg_error("build: merge before stream");
+        const unsigned long long* slice_table = d_table_.p;
+        DevBuf<unsigned long long> d_slice;
+        if (world_ > 1) {
+            d_slice.alloc(slice_cols_);
+            FIN_CUDA(cudaMemset(d_slice.p, 0, d_slice.bytes()));
+            if (n) {
+                tuple_merge_kernel<<<(unsigned)((n + 255) / 256), 256>>>(d_tuples, n, slice_begin_, slice_cols_, d_slice.p, d_err_.p);
+                g_launches++;
+                FIN_CUDA(cudaGetLastError());
+            }
+            check_errors();
+            slice_table = d_slice.p;
+            d_table_.release();
+            d_idx_.release();
+        }
+        const uint64_t n_valid = slice_begin_ >= N_ ? 0 : std::min<uint64_t>(slice_cols_, N_ - slice_begin_);
+        const uint64_t n_words32 = (slice_cols_ + 31) / 32;
+        d_bits_.alloc(n_words32 + 2);
+        FIN_CUDA(cudaMemset(d_bits_.p, 0, d_bits_.bytes()));
+        n_slice_fmin_ = 0;
+        if (n_valid) {
+            DevBuf<uint32_t> d_offs(n_valid);
+            d_sel_.alloc(n_valid);
+            DevBuf<uint64_t> d_nsel(1);
+            fmin_bits_kernel<<<(unsigned)((((n_valid + 31) / 32) * 32 + 255) / 256), 256>>>(slice_table, n_valid, d_bits_.p, d_offs.p);
+            g_launches++;
+            FIN_CUDA(cudaGetLastError());
+            size_t tb = 0;
+            cub::DeviceSelect::If(nullptr, tb, d_offs.p, d_sel_.p, d_nsel.p, (int64_t)n_valid, NotSentinel());
+            DevBuf<uint8_t> tmp(tb + 256);
+            FIN_CUDA(cub::DeviceSelect::If(tmp.p, tb, d_offs.p, d_sel_.p, d_nsel.p, (int64_t)n_valid, NotSentinel()));
+            g_launches += 2;
+            FIN_CUDA(cudaMemcpy(&n_slice_fmin_, d_nsel.p, 8, cudaMemcpyDeviceToHost));
+        }
+        merged_ = true;
+        return n_slice_fmin_;
+    }
+
+    uint64_t slice_words() const { return (slice_cols_ + 63) / 64; }
+
+    // device -> caller's DEVICE buffers: slice_words() u64 of fmin bits, n_slice_fmin u32 offsets
+    void slice(uint64_t* d_bits_out, uint32_t* d_offsets_out) const {
+        if (!merged_) throw arg_error("build: slice before merge");
+        FIN_CUDA(cudaMemcpy(d_bits_out, d_bits_.p, slice_words() * 8, cudaMemcpyDeviceToDevice));
+        if (n_slice_fmin_) FIN_CUDA(cudaMemcpy(d_offsets_out, d_sel_.p, n_slice_fmin_ * 4, cudaMemcpyDeviceToDevice));
+    }
+    void slice_to_host(std::vector<uint64_t>& bits, std::vector<uint32_t>& offs) const {
+        if (!merged_) throw arg_error("build: slice before merge");
+        bits.assign(slice_words(), 0);
+        offs.resize(n_slice_fmin_);
+        // d_bits_ holds 32-bit words; an odd count leaves the upper half of the last u64 zero (allocated + 2, zeroed)
+        FIN_CUDA(cudaMemcpy(bits.data(), d_bits_.p, slice_words() * 8, cudaMemcpyDeviceToHost));
+        if (n_slice_fmin_) FIN_CUDA(cudaMemcpy(offs.data(), d_sel_.p, n_slice_fmin_ * 4, cudaMemcpyDeviceToHost));
+    }
+
+    // all slices in rank order (HOST): world * slice_words() u64 of fmin bits, the offsets back to back
+    void finish(const uint64_t* bits_all, uint64_t n_bit_words, const uint32_t* offsets_all, uint64_t n_offsets, const std::string& out_prefix) {
+        save_index_from_slices(std::move(sbwt_), std::move(lcs_file_), std::move(text_), std::move(ends_), std::move(ustart_), bits_all,
+                               n_bit_words, offsets_all, n_offsets, out_prefix);
+    }
+
+   private:
+    void check_errors() {
+        unsigned err = 0;
+        FIN_CUDA(cudaMemcpy(&err, d_err_.p, 4, cudaMemcpyDeviceToHost));
+        if (err)
+            throw domain_error("the unitigs are not a disjoint spectrum-preserving string set of this SBWT "
+                               "(a unitig k-mer is missing from the SBWT or a window has no unique substring)");
+    }
+
+    SbwtHost sbwt_;
+    PackedVec lcs_file_, text_, ends_, ustart_;
+    int rank_, world_, k_ = 0;
+    uint64_t N_ = 0, slice_cols_ = 0, slice_begin_ = 0, bases_streamed_ = 0, n_tuples_ = 0, n_slice_fmin_ = 0;
+    size_t chunk_begin_ = 0, chunk_end_ = 0;
+    float stream_ms_ = 0.f;
+    bool streamed_ = false, merged_ = false;
+    std::vector<BuildChunk> chunks_;
+    IndexView ix_{};
+    DevBuf<uint64_t> d_lines_, d_text_;
+    DevBuf<unsigned long long> d_table_;
+    DevBuf<uint32_t> d_idx_, d_bits_, d_sel_;
+    DevBuf<unsigned int> d_err_;
+};
+
+static void build_rarest(SbwtHost&& sbwt, PackedVec&& lcs_file, const SeqBatch& unitigs, const std::string& out_prefix) {
+    RarestBuilder b(std::move(sbwt), std::move(lcs_file), unitigs, 0, 1);
+    b.stream();
+    b.merge(nullptr, 0);
+    std::vector<uint64_t> bits;
+    std::vector<uint32_t> offs;
+    b.slice_to_host(bits, offs);
+    b.finish(bits.data(), bits.size(), offs.data(), offs.size(), out_prefix);
 }
 
 // ---- B5 / B6: --type shortest | verify, statistics only (build_fmin.hh:95-214,252-267) ---------------------------
@@ -277,6 +452,56 @@ static std::string build_stats(const SbwtHost& sbwt, const PackedVec& lcs_file, 
         FIN_CUDA(cudaMemcpy(sums, d_sums.p, 24, cudaMemcpyDeviceToHost));
     }
     return stats_string(sums[0], sums[1], sums[2], sbwt.n_kmers);
+}
+
+// ---- staged builder behind the fin_builder_* entry points ---------------------------------------------------------
+static PackedVec lcs_for_build(const SbwtHost& sbwt, const std::string& lcs_path, const std::string& out_prefix, bool write_file) {
+    if (!lcs_path.empty()) return load_packed_file(lcs_path, 0);
+    // build_fmin.hh:373-380: compute and save; the reference then loads the file back, which yields the same vector
+    DevBuf<uint8_t> d = lcs_on_device(sbwt);
+    std::vector<uint8_t> h((size_t)sbwt.n_nodes);
+    FIN_CUDA(cudaMemcpy(h.data(), d.p, h.size(), cudaMemcpyDeviceToHost));
+    PackedVec lcs = lcs_bytes_to_packed(h, h.size(), sbwt.k);
+    if (write_file) save_packed_file(out_prefix + ".LCS.sdsl", lcs, true);
+    return lcs;
+}
+
+RarestBuilder* builder_open(const std::string& sbwt_path, const std::string& unitig_path, const std::string& lcs_path,
+                            const std::string& out_prefix, int device, int rank, int world) {
+    const std::vector<std::string> files = unitig_file_list(unitig_path);
+    SbwtHost sbwt = load_sbwt_file(sbwt_path, true);
+    select_device(device);
+    check_sbwt_limits(sbwt);
+    PackedVec lcs = lcs_for_build(sbwt, lcs_path, out_prefix, rank == 0);
+    SeqBatch unitigs;
+    append_sequences(files[0], unitigs);
+    return new RarestBuilder(std::move(sbwt), std::move(lcs), unitigs, rank, world);
+}
+void builder_free(RarestBuilder* b) { delete b; }
+fin_builder_info builder_info(const RarestBuilder& b) {
+    fin_builder_info i{};
+    i.n_nodes = (int64_t)b.n_nodes();
+    i.slice_columns = (int64_t)b.slice_cols();
+    i.slice_words = (int64_t)b.slice_words();
+    i.text_len = (int64_t)b.text_len();
+    i.n_unitigs = (int64_t)b.n_unitigs();
+    i.n_chunks = (int64_t)b.n_chunks();
+    i.chunk_begin = (int64_t)b.chunk_begin();
+    i.chunk_end = (int64_t)b.chunk_end();
+    i.bases_streamed = (int64_t)b.bases_streamed();
+    i.rank = b.rank();
+    i.world = b.world();
+    i.stream_ms = b.stream_ms();
+    return i;
+}
+uint64_t builder_stream(RarestBuilder& b) { return b.stream(); }
+void builder_export(RarestBuilder& b, uint64_t* d_out, uint64_t capacity, uint64_t* counts) { b.export_tuples(d_out, capacity, counts); }
+uint64_t builder_merge(RarestBuilder& b, const uint64_t* d_tuples, uint64_t n) { return b.merge(d_tuples, n); }
+void builder_slice(const RarestBuilder& b, uint64_t* d_bits, uint32_t* d_offsets) { b.slice(d_bits, d_offsets); }
+void builder_finish(RarestBuilder& b, const uint64_t* bits_all, uint64_t n_bit_words, const uint32_t* offsets_all, uint64_t n_offsets,
+                    const std::string& out_prefix) {
+    b.finish(bits_all, n_bit_words, offsets_all, n_offsets, out_prefix);
+    append_stats_line(out_prefix, 1, "");
 }
 
 std::string build_fmin_device(const std::string& sbwt_path, const std::string& unitig_path, const std::string& out_prefix,

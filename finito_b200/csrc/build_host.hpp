@@ -131,6 +131,43 @@ inline std::vector<BuildChunk> plan_build_chunks(const std::vector<uint64_t>& st
     return chunks;
 }
 
+// ---- build-fmin sharded over GPUs -------------------------------------------------------
+// Every rank knows the whole plan (SBWT, LCS, permutation, chunk list are replicated: they are cheap next to the
+// stream).  Rank r streams the chunks [first, last) below — contiguous in permuted-unitig order, balanced by streamed
+// bases — and OWNS the SBWT columns [r * S, (r + 1) * S), S a multiple of 64 so that the fmin words of the slices
+// concatenate.  The (colex, key) tuples a rank produced for columns it does not own travel to their owner in one
+// all-to-all; the owner folds them into its slice with the same max as the single-GPU table.
+inline uint64_t slice_columns(uint64_t n_nodes, int world) {
+    const uint64_t per = (n_nodes + (uint64_t)world - 1) / (uint64_t)world;
+    return std::max<uint64_t>(64, (per + 63) / 64 * 64);
+}
+
+inline std::pair<size_t, size_t> shard_chunks(const std::vector<BuildChunk>& chunks, int rank, int world) {
+    uint64_t total = 0;
+    for (const BuildChunk& c : chunks) total += c.n_stream;
+    auto boundary = [&](int r) -> size_t {  // first chunk whose prefix sum reaches r/world of the work
+        if (r <= 0) return 0;
+        if (r >= world) return chunks.size();
+        const uint64_t want = total / (uint64_t)world * (uint64_t)r;
+        uint64_t acc = 0;
+        size_t i = 0;
+        while (i < chunks.size() && acc < want) acc += chunks[i++].n_stream;
+        return i;
+    };
+    return {boundary(rank), boundary(rank + 1)};
+}
+
+// tuples sorted by colex -> how many go to each owner
+inline std::vector<uint64_t> tuples_per_owner(const uint64_t* tuples /* {colex, key} pairs */, uint64_t n, uint64_t slice_cols, int world) {
+    std::vector<uint64_t> counts((size_t)world, 0);
+    for (uint64_t i = 0; i < n; i++) {
+        const uint64_t owner = tuples[2 * i] / slice_cols;
+        if (owner >= (uint64_t)world) throw arg_error("internal: tuple beyond the last slice");
+        counts[owner]++;
+    }
+    return counts;
+}
+
 // global_offsets of the marked columns, packed at the width of the largest one (FinimizerIndex.hh:301-306)
 inline PackedVec pack_offsets(const std::vector<uint32_t>& offs) {
     uint64_t max_off = 0;
@@ -158,6 +195,27 @@ inline std::string stats_string(uint64_t n_fmin, uint64_t sum_freq, uint64_t sum
 inline void check_stats_t(int64_t t, int64_t n_nodes) {
     if (t < 1 || t > 127) throw domain_error("-t outside 1..127 (the reference narrows it to char)");
     if (t >= n_nodes) throw domain_error("-t is not smaller than the number of SBWT columns (the reference does not terminate)");
+}
+
+// all column slices in rank order -> the seven index files (FinimizerIndex.hh:301-306, :187-207)
+inline void save_index_from_slices(SbwtHost&& sbwt, PackedVec&& lcs, PackedVec&& text, PackedVec&& ends, PackedVec&& ustart,
+                                   const uint64_t* bits_all, uint64_t n_bit_words, const uint32_t* offsets_all, uint64_t n_offsets,
+                                   const std::string& out_prefix) {
+    IndexHost out;
+    out.fmin.assign((uint64_t)sbwt.n_nodes, 1);
+    const uint64_t need = out.fmin.disk_words();
+    if (n_bit_words < need) throw arg_error("build: fmin words missing");
+    memcpy(out.fmin.words.data(), bits_all, need * 8);
+    uint64_t ones = 0;
+    for (uint64_t w = 0; w < need; w++) ones += (uint64_t)__builtin_popcountll(out.fmin.words[w]);
+    if (ones != n_offsets) throw arg_error("build: the slices disagree on the number of finimizers");
+    out.offsets = pack_offsets(std::vector<uint32_t>(offsets_all, offsets_all + n_offsets));
+    out.sbwt = std::move(sbwt);
+    out.lcs = std::move(lcs);
+    out.text = std::move(text);
+    out.ends = std::move(ends);
+    out.ustart = std::move(ustart);
+    save_index_files(out, out_prefix);
 }
 
 inline void append_stats_line(const std::string& out_prefix, int t, const std::string& result) {  // build_fmin.hh:386-395

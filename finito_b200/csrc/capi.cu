@@ -8,6 +8,11 @@ struct fin_index {
     std::unique_ptr<fin::DeviceIndex> dev;
 };
 
+struct fin_builder {
+    fin::RarestBuilder* b = nullptr;
+    ~fin_builder() { fin::builder_free(b); }
+};
+
 namespace {
 
 thread_local std::string g_error;
@@ -168,6 +173,62 @@ fin_status fin_lcs(const char* sbwt_path, int with_variant_header, int device, u
         require((uint64_t)s.n_nodes <= out_capacity, "fin_lcs: output buffer too small");
         std::vector<uint8_t> l = fin::lcs_device(s, device);
         memcpy(out, l.data(), (size_t)s.n_nodes);
+    });
+}
+
+fin_status fin_builder_open(const char* sbwt_path, const char* unitig_path, const char* lcs_path, const char* out_prefix,
+                            int device, int rank, int world, fin_builder** out) {
+    return guarded([&] {
+        require(sbwt_path && unitig_path && out_prefix && out, "fin_builder_open: null argument");
+        *out = nullptr;
+        std::unique_ptr<fin_builder> h(new fin_builder());
+        h->b = fin::builder_open(sbwt_path, unitig_path, lcs_path ? lcs_path : "", out_prefix, device, rank, world);
+        *out = h.release();
+    });
+}
+
+void fin_builder_free(fin_builder* b) { delete b; }
+
+fin_status fin_builder_info_get(const fin_builder* b, fin_builder_info* out) {
+    return guarded([&] {
+        require(b && out, "fin_builder_info_get: null argument");
+        *out = fin::builder_info(*b->b);
+    });
+}
+
+fin_status fin_builder_stream(fin_builder* b, uint64_t* n_tuples) {
+    return guarded([&] {
+        require(b && n_tuples, "fin_builder_stream: null argument");
+        *n_tuples = fin::builder_stream(*b->b);
+    });
+}
+
+fin_status fin_builder_export(fin_builder* b, void* d_tuples, uint64_t capacity_tuples, uint64_t* counts_per_rank) {
+    return guarded([&] {
+        require(b && counts_per_rank && (d_tuples || capacity_tuples == 0), "fin_builder_export: null argument");
+        fin::builder_export(*b->b, static_cast<uint64_t*>(d_tuples), capacity_tuples, counts_per_rank);
+    });
+}
+
+fin_status fin_builder_merge(fin_builder* b, const void* d_tuples, uint64_t n_tuples, uint64_t* n_slice_fmin) {
+    return guarded([&] {
+        require(b && n_slice_fmin && (d_tuples || n_tuples == 0), "fin_builder_merge: null argument");
+        *n_slice_fmin = fin::builder_merge(*b->b, static_cast<const uint64_t*>(d_tuples), n_tuples);
+    });
+}
+
+fin_status fin_builder_slice(const fin_builder* b, void* d_bits, void* d_offsets) {
+    return guarded([&] {
+        require(b && d_bits, "fin_builder_slice: null argument");
+        fin::builder_slice(*b->b, static_cast<uint64_t*>(d_bits), static_cast<uint32_t*>(d_offsets));
+    });
+}
+
+fin_status fin_builder_finish(fin_builder* b, const uint64_t* bits_all, uint64_t n_bit_words, const uint32_t* offsets_all,
+                              uint64_t n_offsets, const char* out_prefix) {
+    return guarded([&] {
+        require(b && bits_all && out_prefix && (offsets_all || n_offsets == 0), "fin_builder_finish: null argument");
+        fin::builder_finish(*b->b, bits_all, n_bit_words, offsets_all, n_offsets, out_prefix);
     });
 }
 

@@ -89,4 +89,17 @@ std::string build_fmin_device(const std::string& sbwt_path, const std::string& u
                               const std::string& type, int64_t t, const std::string& lcs_path, int device);
 std::vector<uint8_t> lcs_device(const SbwtHost& sbwt, int device);
 
+// staged build-fmin --type rarest, shardable over GPUs (build.cu)
+class RarestBuilder;
+RarestBuilder* builder_open(const std::string& sbwt_path, const std::string& unitig_path, const std::string& lcs_path,
+                            const std::string& out_prefix, int device, int rank, int world);
+void builder_free(RarestBuilder* b);
+fin_builder_info builder_info(const RarestBuilder& b);
+uint64_t builder_stream(RarestBuilder& b);
+void builder_export(RarestBuilder& b, uint64_t* d_out, uint64_t capacity, uint64_t* counts);
+uint64_t builder_merge(RarestBuilder& b, const uint64_t* d_tuples, uint64_t n);
+void builder_slice(const RarestBuilder& b, uint64_t* d_bits, uint32_t* d_offsets);
+void builder_finish(RarestBuilder& b, const uint64_t* bits_all, uint64_t n_bit_words, const uint32_t* offsets_all, uint64_t n_offsets,
+                    const std::string& out_prefix);
+
 }  // namespace fin

@@ -156,6 +156,47 @@ fin_status fin_build(const char* sbwt_path, const char* unitig_path, const char*
 fin_status fin_lcs(const char* sbwt_path, int with_variant_header, int device, uint8_t* out, uint64_t out_capacity,
                    uint64_t* n_nodes);
 
+/* ------------------------------------------------------------------------------------------------
+ * build-fmin --type rarest sharded over GPUs: one process (or thread) per GPU, every rank opens the same
+ * inputs.  Replaces the single loop over the permuted unitigs of FinimizerIndexBuilder's constructor
+ * (include/FinimizerIndex.hh:292-299) by `world` partial streams whose (finimizer column, overwrite-rule key)
+ * tuples meet at the owner of the column.  Call order on every rank:
+ *   fin_builder_open   -> loads, LCS (computed on the device when lcs_path is NULL/""; rank 0 writes the file),
+ *                         unitig permutation + Ustart (replicated), chunk plan, this rank's share
+ *   fin_builder_stream -> add_sequence (FinimizerIndex.hh:321-389) over this rank's chunks; *n_tuples = number of
+ *                         columns this rank produced a key for
+ *   fin_builder_export -> d_tuples (DEVICE, n_tuples x {u64 column, u64 key}, ascending by column);
+ *                         counts_per_rank (HOST, world entries): how many of them rank g owns, in order
+ *   ... the caller exchanges the tuples: ONE all-to-all (torch.distributed / NCCL in finito_b200/distributed.py) ...
+ *   fin_builder_merge  -> folds the received tuples (DEVICE) into this rank's slice of columns
+ *                         [rank * slice_columns, (rank+1) * slice_columns); *n_slice_fmin = finimizers in the slice
+ *   fin_builder_slice  -> d_bits (DEVICE, slice_words u64: fmin bits of the slice), d_offsets (DEVICE,
+ *                         n_slice_fmin u32: global_offsets of the slice in column order, FinimizerIndex.hh:301-306)
+ *   ... the caller gathers the slices on rank 0 ...
+ *   fin_builder_finish -> rank 0 only: all slices in rank order (HOST) -> the seven index files + the stats line
+ * With world == 1 export/exchange are skipped: open, stream, merge(NULL, 0), slice, finish  (what fin_build does).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct fin_builder fin_builder;
+
+typedef struct fin_builder_info {
+    int64_t n_nodes, slice_columns, slice_words, text_len, n_unitigs;
+    int64_t n_chunks, chunk_begin, chunk_end; /* the chunk plan and this rank's share [begin, end) */
+    int64_t bases_streamed;                   /* bases this rank's share streams (incl. the 2k warm-up per chunk) */
+    int32_t rank, world;
+    float stream_ms;                          /* CUDA-event time of build_stream_kernel (after fin_builder_stream) */
+} fin_builder_info;
+
+fin_status fin_builder_open(const char* sbwt_path, const char* unitig_path, const char* lcs_path, const char* out_prefix,
+                            int device, int rank, int world, fin_builder** out);
+void fin_builder_free(fin_builder* b);
+fin_status fin_builder_info_get(const fin_builder* b, fin_builder_info* out);
+fin_status fin_builder_stream(fin_builder* b, uint64_t* n_tuples);
+fin_status fin_builder_export(fin_builder* b, void* d_tuples, uint64_t capacity_tuples, uint64_t* counts_per_rank);
+fin_status fin_builder_merge(fin_builder* b, const void* d_tuples, uint64_t n_tuples, uint64_t* n_slice_fmin);
+fin_status fin_builder_slice(const fin_builder* b, void* d_bits, void* d_offsets);
+fin_status fin_builder_finish(fin_builder* b, const uint64_t* bits_all, uint64_t n_bit_words, const uint32_t* offsets_all,
+                              uint64_t n_offsets, const char* out_prefix);
+
 #ifdef __cplusplus
 }
 #endif

@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cstdint>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -271,6 +272,141 @@ int emu_stats(const char* sbwt_path, const char* unitig_path, const char* type_c
         const std::string r = stats_string(n, sf, sl, sbwt.n_kmers);
         if (r.size() + 1 > cap) throw arg_error("buffer too small");
         memcpy(result, r.c_str(), r.size() + 1);
+    });
+}
+
+// ---- one rank of the sharded build over HOST memory: same stages as fin_builder_* (include/finito_b200.h), the stream
+//      run by the kernel bodies.  Lets the gloo world_size-2 tests drive finito_b200/distributed.py without a GPU.
+struct EmuBuilder {
+    SbwtHost sbwt;
+    PackedVec lcs_file, text, ends, ustart;
+    std::vector<uint64_t> lines;
+    IndexView ix{};
+    std::vector<BuildChunk> chunks;
+    size_t c0 = 0, c1 = 0;
+    int rank = 0, world = 1, k = 0;
+    uint64_t N = 0, S = 0, bases = 0;
+    std::vector<unsigned long long> table, slice_table;
+    std::vector<uint64_t> tuples;   // {colex, key}
+    std::vector<uint64_t> bits;
+    std::vector<uint32_t> offs;
+    std::string prefix;
+};
+
+void* emu_builder_open(const char* sbwt_path, const char* unitig_path, const char* out_prefix, int rank, int world) {
+    EmuBuilder* b = nullptr;
+    const int rc = guarded([&] {
+        std::unique_ptr<EmuBuilder> e(new EmuBuilder());
+        const std::vector<std::string> files = unitig_file_list(unitig_path);
+        e->sbwt = load_sbwt_file(sbwt_path, true);
+        check_sbwt_limits(e->sbwt);
+        e->N = (uint64_t)e->sbwt.n_nodes;
+        e->k = (int)e->sbwt.k;
+        e->rank = rank; e->world = world; e->prefix = out_prefix;
+        e->lcs_file = lcs_bytes_to_packed(emu_lcs_bytes(e->sbwt), e->N, e->k);
+        if (rank == 0) save_packed_file(e->prefix + ".LCS.sdsl", e->lcs_file, true);
+        SeqBatch unitigs;
+        append_sequences(files[0], unitigs);
+        check_unitigs(unitigs, e->k);
+        const uint64_t U = unitigs.size();
+        e->lines = make_lines(e->sbwt, &e->lcs_file, nullptr, nullptr);
+        e->ix.lines = reinterpret_cast<const uint4*>(e->lines.data());
+        e->ix.n_nodes = (idx_t)e->N;
+        e->ix.k = e->k;
+        std::vector<uint64_t> order(U), starts;
+        for (uint64_t u = 0; u < U; u++) order[u] = u;
+        pack_unitigs(unitigs, order, e->text, starts);
+        e->text.words.resize(e->text.words.size() + 2, 0);
+        std::vector<uint32_t> cols(U);
+        for (uint64_t u = 0; u < U; u++) cols[u] = first_kmer_column(e->ix, e->text.words.data(), starts[u]);
+        order = unitig_order(cols, e->N, e->ustart);
+        pack_unitigs(unitigs, order, e->text, starts);
+        e->text.words.resize(e->text.words.size() + 2, 0);
+        e->ends = unitig_ends(unitigs, order, starts);
+        e->chunks = plan_build_chunks(starts, e->ends, e->k, 0);
+        const std::pair<size_t, size_t> mine = shard_chunks(e->chunks, rank, world);
+        e->c0 = mine.first; e->c1 = mine.second;
+        e->S = world == 1 ? e->N : slice_columns(e->N, world);
+        for (size_t c = e->c0; c < e->c1; c++) e->bases += e->chunks[c].n_stream;
+        b = e.release();
+    });
+    return rc ? nullptr : b;
+}
+void emu_builder_free(void* h) { delete static_cast<EmuBuilder*>(h); }
+// info9: n_nodes, slice_columns, slice_words, text_len, n_unitigs, n_chunks, chunk_begin, chunk_end, bases_streamed
+void emu_builder_info(void* h, int64_t* info9) {
+    EmuBuilder& e = *static_cast<EmuBuilder*>(h);
+    const int64_t v[9] = {(int64_t)e.N, (int64_t)e.S, (int64_t)((e.S + 63) / 64), (int64_t)e.text.size(), (int64_t)e.ends.size(),
+                          (int64_t)e.chunks.size(), (int64_t)e.c0, (int64_t)e.c1, (int64_t)e.bases};
+    memcpy(info9, v, sizeof v);
+}
+int emu_builder_stream(void* h, uint64_t* n_tuples) {
+    return guarded([&] {
+        EmuBuilder& e = *static_cast<EmuBuilder*>(h);
+        e.table.assign(e.N, 0);
+        unsigned err = 0;
+        for (size_t c = e.c0; c < e.c1; c++) {
+            const BuildChunk& ch = e.chunks[c];
+            if (e.k <= 32) build_stream_chunk<32>(e.ix, e.text.words.data(), ch, e.table.data(), &err);
+            else if (e.k <= 64) build_stream_chunk<64>(e.ix, e.text.words.data(), ch, e.table.data(), &err);
+            else if (e.k <= 128) build_stream_chunk<128>(e.ix, e.text.words.data(), ch, e.table.data(), &err);
+            else build_stream_chunk<256>(e.ix, e.text.words.data(), ch, e.table.data(), &err);
+        }
+        if (err) throw domain_error("emu: build stream error flags " + std::to_string(err));
+        e.tuples.clear();
+        if (e.world > 1)
+            for (uint64_t i = 0; i < e.N; i++)
+                if (e.table[i]) { e.tuples.push_back(i); e.tuples.push_back(e.table[i]); }
+        *n_tuples = e.tuples.size() / 2;
+    });
+}
+int emu_builder_export(void* h, uint64_t* out, uint64_t capacity, uint64_t* counts) {
+    return guarded([&] {
+        EmuBuilder& e = *static_cast<EmuBuilder*>(h);
+        const uint64_t n = e.tuples.size() / 2;
+        if (capacity < n) throw arg_error("tuple buffer too small");
+        if (n) memcpy(out, e.tuples.data(), n * 16);
+        const std::vector<uint64_t> c = tuples_per_owner(e.tuples.data(), n, e.S, e.world);
+        for (int g = 0; g < e.world; g++) counts[g] = e.world == 1 ? 0 : c[(size_t)g];
+    });
+}
+int emu_builder_merge(void* h, const uint64_t* tuples, uint64_t n, uint64_t* n_slice) {
+    return guarded([&] {
+        EmuBuilder& e = *static_cast<EmuBuilder*>(h);
+        const uint64_t begin = (uint64_t)e.rank * e.S;
+        if (e.world == 1) {
+            e.slice_table = e.table;
+        } else {
+            e.slice_table.assign(e.S, 0);
+            for (uint64_t i = 0; i < n; i++) {
+                const uint64_t local = tuples[2 * i] - begin;
+                if (tuples[2 * i] < begin || local >= e.S) throw arg_error("tuple outside the slice");
+                fin_atomic_max(&e.slice_table[local], tuples[2 * i + 1]);
+            }
+        }
+        const uint64_t n_valid = begin >= e.N ? 0 : std::min<uint64_t>(e.S, e.N - begin);
+        e.bits.assign((e.S + 63) / 64, 0);
+        e.offs.clear();
+        for (uint64_t i = 0; i < n_valid; i++)
+            if (e.slice_table[i]) {
+                e.bits[i >> 6] |= 1ULL << (i & 63);
+                e.offs.push_back(fmin_key_offset(e.slice_table[i]));
+            }
+        *n_slice = e.offs.size();
+    });
+}
+void emu_builder_slice(void* h, uint64_t* bits, uint32_t* offs) {
+    EmuBuilder& e = *static_cast<EmuBuilder*>(h);
+    memcpy(bits, e.bits.data(), e.bits.size() * 8);
+    if (!e.offs.empty()) memcpy(offs, e.offs.data(), e.offs.size() * 4);
+}
+int emu_builder_finish(void* h, const uint64_t* bits_all, uint64_t n_words, const uint32_t* offs_all, uint64_t n_offs) {
+    return guarded([&] {
+        EmuBuilder& e = *static_cast<EmuBuilder*>(h);
+        e.text.words.resize(e.text.disk_words() + 1);
+        save_index_from_slices(std::move(e.sbwt), std::move(e.lcs_file), std::move(e.text), std::move(e.ends), std::move(e.ustart), bits_all,
+                               n_words, offs_all, n_offs, e.prefix);
+        append_stats_line(e.prefix, 1, "");
     });
 }
 

@@ -131,6 +131,15 @@ def emu_lib() -> C.CDLL:
                                C.c_void_p, C.c_int]
     lib.emu_lcs.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_uint64]
     lib.emu_build.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]
+    lib.emu_builder_open.restype = C.c_void_p
+    lib.emu_builder_open.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int]
+    lib.emu_builder_free.argtypes = [C.c_void_p]
+    lib.emu_builder_info.argtypes = [C.c_void_p, C.c_void_p]
+    lib.emu_builder_stream.argtypes = [C.c_void_p, C.c_void_p]
+    lib.emu_builder_export.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    lib.emu_builder_merge.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]
+    lib.emu_builder_slice.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.emu_builder_finish.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]
     lib.emu_stats.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_uint64, C.c_char_p, C.c_uint64]
     return lib
 
@@ -157,6 +166,62 @@ def emu_build(sbwt, unitigs, prefix, per_chunk=0):
     lib = emu_lib()
     if lib.emu_build(os.fsencode(sbwt), os.fsencode(unitigs), os.fsencode(prefix), per_chunk):
         raise RuntimeError("emu: " + lib.emu_last_error().decode())
+
+
+class EmuShardedBuilder:
+    """Same methods as finito_b200.ShardedBuilder over HOST memory, the stream run by the kernel bodies on the CPU
+    (tests/emu).  Test infrastructure: lets gloo tests drive finito_b200/distributed.py without a GPU."""
+
+    memory = "cpu"
+
+    def __init__(self, sbwt, unitigs, out_prefix, rank, world):
+        self.lib = emu_lib()
+        self.h = self.lib.emu_builder_open(os.fsencode(sbwt), os.fsencode(unitigs), os.fsencode(out_prefix), rank, world)
+        if not self.h:
+            raise RuntimeError("emu: " + self.lib.emu_last_error().decode())
+        self.out_prefix = out_prefix
+
+    def _ok(self, rc):
+        if rc:
+            raise RuntimeError("emu: " + self.lib.emu_last_error().decode())
+
+    @property
+    def info(self):
+        v = np.zeros(9, dtype=np.int64)
+        self.lib.emu_builder_info(self.h, v.ctypes.data)
+        names = ("n_nodes", "slice_columns", "slice_words", "text_len", "n_unitigs", "n_chunks", "chunk_begin", "chunk_end",
+                 "bases_streamed")
+        d = dict(zip(names, (int(x) for x in v)))
+        d["stream_ms"] = 0.0
+        return d
+
+    def stream(self):
+        n = np.zeros(1, dtype=np.uint64)
+        self._ok(self.lib.emu_builder_stream(self.h, n.ctypes.data))
+        return int(n[0])
+
+    def export(self, ptr, capacity, world):
+        counts = np.zeros(world, dtype=np.uint64)
+        self._ok(self.lib.emu_builder_export(self.h, ptr, capacity, counts.ctypes.data))
+        return counts
+
+    def merge(self, ptr, n):
+        out = np.zeros(1, dtype=np.uint64)
+        self._ok(self.lib.emu_builder_merge(self.h, ptr, n, out.ctypes.data))
+        return int(out[0])
+
+    def slice(self, bits_ptr, offs_ptr):
+        self.lib.emu_builder_slice(self.h, bits_ptr, offs_ptr)
+
+    def finish(self, bits_all, offs_all):
+        bits_all = np.ascontiguousarray(bits_all, dtype=np.uint64)
+        offs_all = np.ascontiguousarray(offs_all, dtype=np.uint32)
+        self._ok(self.lib.emu_builder_finish(self.h, bits_all.ctypes.data, bits_all.size, offs_all.ctypes.data, offs_all.size))
+
+    def close(self):
+        if self.h:
+            self.lib.emu_builder_free(self.h)
+            self.h = None
 
 
 def emu_stats(sbwt, unitigs, type, t, per_chunk=0) -> str:
