@@ -55,6 +55,11 @@ class _BuilderInfo(C.Structure):
                [("rank", C.c_int32), ("world", C.c_int32), ("stream_ms", C.c_float)]
 
 
+class _BuildTiming(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("load_sbwt_ms", "lcs_ms", "read_unitigs_ms", "prepare_ms", "stream_merge_ms",
+                                         "stream_kernel_ms", "write_ms", "total_ms")] + [("unitig_bases", C.c_int64)]
+
+
 # every symbol include/finito_b200.h declares: name -> (restype, argtypes)
 _u64p = C.POINTER(C.c_uint64)
 ABI = {
@@ -81,6 +86,7 @@ ABI = {
     "fin_host_free": (None, [C.c_void_p]),
     "fin_build": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int, C.c_char_p,
                             C.c_size_t]),
+    "fin_build_last_timing": (C.c_int, [C.POINTER(_BuildTiming)]),
     "fin_lcs": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, _u64p]),
     "fin_builder_open": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int,
                                    C.POINTER(C.c_void_p)]),
@@ -297,6 +303,13 @@ class ShardedBuilder:
         offsets_all = np.ascontiguousarray(offsets_all, dtype=np.uint32)
         _check(lib().fin_builder_finish(self._h, bits_all.ctypes.data, bits_all.size, offsets_all.ctypes.data, offsets_all.size,
                                         os.fsencode(self.out_prefix)))
+
+
+def build_timing() -> dict:
+    """Stages of the last build_fmin() call on this thread (fin_build_last_timing)."""
+    t = _BuildTiming()
+    _check(lib().fin_build_last_timing(C.byref(t)))
+    return {n: (int if n == "unitig_bases" else float)(getattr(t, n)) for n, _ in _BuildTiming._fields_}
 
 
 def lcs_array(sbwt_path: str, with_variant_header: bool = True, device: int = 0) -> np.ndarray:

@@ -6,6 +6,8 @@
 #include <cub/device/device_select.cuh>
 #include <cub/iterator/counting_input_iterator.cuh>
 
+#include <ctime>
+
 #include "build_host.hpp"
 #include "engine.hpp"
 #include "build_kernels.cuh"
@@ -340,14 +342,24 @@ class RarestBuilder {
     DevBuf<unsigned int> d_err_;
 };
 
+extern thread_local fin_build_timing g_build_timing;
+static double wall_ms();
+
 static void build_rarest(SbwtHost&& sbwt, PackedVec&& lcs_file, const SeqBatch& unitigs, const std::string& out_prefix) {
+    const double t0 = wall_ms();
     RarestBuilder b(std::move(sbwt), std::move(lcs_file), unitigs, 0, 1);
+    const double t1 = wall_ms();
     b.stream();
     b.merge(nullptr, 0);
     std::vector<uint64_t> bits;
     std::vector<uint32_t> offs;
     b.slice_to_host(bits, offs);
+    const double t2 = wall_ms();
     b.finish(bits.data(), bits.size(), offs.data(), offs.size(), out_prefix);
+    g_build_timing.prepare_ms = (float)(t1 - t0);
+    g_build_timing.stream_merge_ms = (float)(t2 - t1);
+    g_build_timing.stream_kernel_ms = b.stream_ms();
+    g_build_timing.write_ms = (float)(wall_ms() - t2);
 }
 
 // ---- B5 / B6: --type shortest | verify, statistics only (build_fmin.hh:95-214,252-267) ---------------------------
@@ -504,15 +516,27 @@ void builder_finish(RarestBuilder& b, const uint64_t* bits_all, uint64_t n_bit_w
     append_stats_line(out_prefix, 1, "");
 }
 
+thread_local fin_build_timing g_build_timing{};
+fin_build_timing last_build_timing() { return g_build_timing; }
+
+static double wall_ms() {
+    timespec ts;
+    clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e3 + ts.tv_nsec / 1e6;
+}
+
 std::string build_fmin_device(const std::string& sbwt_path, const std::string& unitig_path, const std::string& out_prefix,
                               const std::string& type, int64_t t_arg, const std::string& lcs_path, int device) {
     const signed char t = (signed char)t_arg;  // build_fmin.hh:333 narrows to char
+    g_build_timing = fin_build_timing{};
+    const double t_begin = wall_ms();
     const std::vector<std::string> files = unitig_file_list(unitig_path);
     SbwtHost sbwt = load_sbwt_file(sbwt_path, true);
     if (type != "rarest" && type != "shortest" && type != "verify") throw arg_error("Error: unknown type: " + type);
     select_device(device);
     check_sbwt_limits(sbwt);
 
+    const double t_loaded = wall_ms();
     std::string lcs_file = lcs_path;
     if (lcs_file.empty()) {  // :373-380: compute, save, then load it back like the reference does
         lcs_file = out_prefix + ".LCS.sdsl";
@@ -522,10 +546,16 @@ std::string build_fmin_device(const std::string& sbwt_path, const std::string& u
         save_packed_file(lcs_file, lcs_bytes_to_packed(h, h.size(), sbwt.k), true);
     }
     PackedVec lcs = load_packed_file(lcs_file, 0);
+    const double t_lcs = wall_ms();
 
     std::string result;
     SeqBatch unitigs;
     append_sequences(files[0], unitigs);
+    const double t_unitigs = wall_ms();
+    g_build_timing.load_sbwt_ms = (float)(t_loaded - t_begin);
+    g_build_timing.lcs_ms = (float)(t_lcs - t_loaded);
+    g_build_timing.read_unitigs_ms = (float)(t_unitigs - t_lcs);
+    g_build_timing.unitig_bases = (int64_t)unitigs.seqs.size();
     if (type == "rarest") {
         if (t != 1) throw domain_error("t != 1 does not make sense with rarest type");  // :245-247
         build_rarest(std::move(sbwt), std::move(lcs), unitigs, out_prefix);
@@ -533,6 +563,7 @@ std::string build_fmin_device(const std::string& sbwt_path, const std::string& u
         result = build_stats(sbwt, lcs, unitigs, type, t);
     }
     append_stats_line(out_prefix, (int)t, result);
+    g_build_timing.total_ms = (float)(wall_ms() - t_begin);
     return result;
 }
 

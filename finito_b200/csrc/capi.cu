@@ -164,6 +164,13 @@ fin_status fin_build(const char* sbwt_path, const char* unitig_path, const char*
     });
 }
 
+fin_status fin_build_last_timing(fin_build_timing* out) {
+    return guarded([&] {
+        require(out != nullptr, "fin_build_last_timing: null argument");
+        *out = fin::last_build_timing();
+    });
+}
+
 fin_status fin_lcs(const char* sbwt_path, int with_variant_header, int device, uint8_t* out, uint64_t out_capacity,
                    uint64_t* n_nodes) {
     return guarded([&] {

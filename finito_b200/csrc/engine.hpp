@@ -88,6 +88,7 @@ class DeviceIndex {
 std::string build_fmin_device(const std::string& sbwt_path, const std::string& unitig_path, const std::string& out_prefix,
                               const std::string& type, int64_t t, const std::string& lcs_path, int device);
 std::vector<uint8_t> lcs_device(const SbwtHost& sbwt, int device);
+fin_build_timing last_build_timing();
 
 // staged build-fmin --type rarest, shardable over GPUs (build.cu)
 class RarestBuilder;

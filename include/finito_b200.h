@@ -152,6 +152,14 @@ void fin_host_free(void* p);
 fin_status fin_build(const char* sbwt_path, const char* unitig_path, const char* out_prefix, const char* type,
                      int64_t t, const char* lcs_path, int device, char* stats_out, size_t stats_cap);
 
+/* Wall-clock stages of the last fin_build call on this thread (milliseconds): the figures behind bench.py's
+ * "build-fmin unitig bp/sec".  stream_kernel_ms is the CUDA-event time of build_stream_kernel. */
+typedef struct fin_build_timing {
+    float load_sbwt_ms, lcs_ms, read_unitigs_ms, prepare_ms, stream_merge_ms, stream_kernel_ms, write_ms, total_ms;
+    int64_t unitig_bases;
+} fin_build_timing;
+fin_status fin_build_last_timing(fin_build_timing* out);
+
 /* LCS array only (lcs_basic_parallel_algorithm.hpp:52-120) as one byte per SBWT column. */
 fin_status fin_lcs(const char* sbwt_path, int with_variant_header, int device, uint8_t* out, uint64_t out_capacity,
                    uint64_t* n_nodes);
