@@ -201,6 +201,65 @@ def cpu_baseline(index_prefix, ds, args, all_threads, sample_reads=None):
             "detail": detail}
 
 
+def unitig_bases(ds):
+    n = 0
+    with open(ds["unitigs"], "rb") as f:
+        for line in f:
+            if not line.startswith(b">"):
+                n += len(line.strip())
+    return n
+
+
+def reference_build(ds, out_prefix):
+    """build-fmin of the unmodified reference binary (LCS on 8 OpenMP threads, the rest on one core), wall time."""
+    ref = reference_binary()
+    if not ref:
+        return None
+    t0 = time.perf_counter()
+    r = subprocess.run([ref, "build-fmin", "-o", out_prefix, "-i", ds["sbwt"], "-u", ds["unitigs"]], capture_output=True, text=True)
+    wall = time.perf_counter() - t0
+    if r.returncode != 0:
+        return None
+    bp = unitig_bases(ds)
+    return {"value": bp / wall, "unit": "bp/s", "wall_s": wall, "unitig_bp": bp, "kind": "reference",
+            "threads": "8 OpenMP threads for the LCS, 1 core for the rest (as shipped)"}
+
+
+def build_arm(fb, ds, rank, world, local_rank, steps, barrier):
+    """BASELINE.json's second metric: build-fmin unitig bp/sec = unitig bases / wall time of the whole build-fmin call
+    (SBWT + unitig file parsing, LCS, permutation, stream, merge, the seven index files written) through the C ABI.
+    N > 1: fin_builder_* sharded over the ranks with one NCCL all-to-all (finito_b200/distributed.py)."""
+    import torch
+
+    bp = unitig_bases(ds)
+    out = os.path.join(ds["dir"], "bench_build")
+    walls, stages = [], None
+    for i in range(1 + steps):  # one untimed warm-up build
+        barrier()
+        t0 = time.perf_counter()
+        if world == 1:
+            fb.build_fmin(ds["sbwt"], ds["unitigs"], out, device=local_rank)
+            stages = fb.build_timing()
+        else:
+            from finito_b200.distributed import build_fmin_sharded
+
+            b = fb.ShardedBuilder(ds["sbwt"], ds["unitigs"], out, rank, world, device=local_rank)
+            stages = build_fmin_sharded(b)
+            b.close()
+        barrier()
+        if i:
+            walls.append(time.perf_counter() - t0)
+    wall = float(np.mean(walls))
+    if world > 1:
+        import torch.distributed as dist
+
+        t = torch.tensor([wall], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        wall = float(t.item())
+    return {"metric": "build-fmin unitig bp/sec", "value": bp / wall, "unit": "bp/s", "wall_s": wall, "unitig_bp": bp, "builds_timed": steps,
+            "includes": "file parsing, LCS (device), permutation, stream, merge, index files written", "stages": stages}
+
+
 # ---------------------------------------------------------------------------------------------------------
 def main():
     args = parse_args()
@@ -295,6 +354,9 @@ def main():
     e2e_total = float(sum(e2e_times))
     assert c_e2e.positive == counts.positive
 
+    # ---- build-fmin arm (every rank builds from rank 0's inputs when sharded)
+    build = build_arm(fb, ds if world == 1 else dataset(args, 0), rank, world, local_rank, min(args.steps, 3), barrier)
+
     # ---- max over ranks
     if world > 1:
         t = torch.tensor([dev_total_ms, e2e_total, wall_dev], dtype=torch.float64, device="cuda")
@@ -328,6 +390,7 @@ def main():
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cpu = cpu_baseline(prefix, ds, args, all_threads=False, sample_reads=args.cpu_sample_reads)
+            build["cpu_baseline"] = reference_build(ds, os.path.join(ds["dir"], "bench_build_ref"))
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -340,7 +403,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n_bases + 8 * (n_reads + 1)),
                     "d2h_bytes_per_step": int(kmers_per_step * 8), "ms_per_step": e2e_total / args.steps * 1e3,
                     "api": "fin_search_batch32 (pinned host buffers, 3-stream sub-batch pipeline)"},
-            "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+            "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "build": build,
             "wall_s_device_arm": wall_dev,
         }
         print(json.dumps(line))
@@ -381,6 +444,7 @@ def reference_arm(args):
             "cpu_baseline": {k_: last[k_] for k_ in ("value", "unit", "cores", "kind", "sample")},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     line["cpu_baseline"]["value"] = v
+    line["build"] = reference_build(ds, os.path.join(ds["dir"], "bench_build_ref"))
     print(json.dumps(line))
 
 
