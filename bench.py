@@ -44,6 +44,7 @@ def parse_args():
     ap.add_argument("--read-len", type=int, default=150)
     ap.add_argument("--cpu-sample-reads", type=int, default=0, help="reads of the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-build-arm", action="store_true", help="skip the build-fmin bp/s arm (kernel experiments)")
     return ap.parse_args()
 
 
@@ -285,7 +286,7 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     ds = dataset(args, rank)
-    prefix = os.path.join(ds["dir"], "index")
+    prefix = os.path.join(ds["dir"], "fmin")  # not "index": <prefix>.sbwt would overwrite the input index.sbwt
     if not os.path.exists(prefix + ".FBV.sdsl"):
         t0 = time.perf_counter()
         fb.build_fmin(ds["sbwt"], ds["unitigs"], prefix, device=local_rank)
@@ -355,7 +356,9 @@ def main():
     assert c_e2e.positive == counts.positive
 
     # ---- build-fmin arm (every rank builds from rank 0's inputs when sharded)
-    build = build_arm(fb, ds if world == 1 else dataset(args, 0), rank, world, local_rank, min(args.steps, 3), barrier)
+    build = None
+    if not args.no_build_arm:
+        build = build_arm(fb, ds if world == 1 else dataset(args, 0), rank, world, local_rank, min(args.steps, 3), barrier)
 
     # ---- max over ranks
     if world > 1:
@@ -379,6 +382,11 @@ def main():
         peak, peak_src = measured_peak()
         achieved = bytes_per_launch / avg_search_s / 1e9
         traffic = profiled_traffic()
+        if traffic and int(traffic.get("genome", 5_000_000)) != args.genome:
+            traffic = None  # the committed capture is of another workload
+        l2_bytes = 126e6
+        regime = ("L2-resident at this config: the sector model counts every access as HBM traffic" if info["device_bytes"] < l2_bytes
+                  else f"{info['device_bytes'] / l2_bytes:.1f}x the 126 MB L2: random sectors mostly come from HBM")
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": traffic["dram_bytes_per_read"] * n_reads if traffic else None,
                     "traffic_source": (f"ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of a {traffic['reads_in_captured_launch']}-read launch "
@@ -386,11 +394,12 @@ def main():
                     "kernel": "search_reads_kernel", "kernel_ms": avg_search_s * 1e3, "kernel_share_of_step": float(np.sum(search_ms)) / dev_total_ms if world == 1 else None,
                     "algorithmic_bytes_per_launch": bytes_per_launch, "algorithmic_bytes_per_kmer": bytes_per_launch / kmers_per_step,
                     "peak_source": peak_src,
-                    "note": f"index is {info['device_bytes'] / 1e6:.1f} MB (L2-resident at this config): the sector model counts every access as HBM traffic"}
+                    "note": f"index is {info['device_bytes'] / 1e6:.1f} MB ({regime})"}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cpu = cpu_baseline(prefix, ds, args, all_threads=False, sample_reads=args.cpu_sample_reads)
-            build["cpu_baseline"] = reference_build(ds, os.path.join(ds["dir"], "bench_build_ref"))
+            if build:
+                build["cpu_baseline"] = reference_build(ds, os.path.join(ds["dir"], "bench_build_ref"))
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -414,7 +423,7 @@ def main():
 def reference_arm(args):
     """The reference's own CPU implementation on this box's host cores; each step = a bounded sample."""
     ds = dataset(args, 0)
-    prefix = os.path.join(ds["dir"], "index")
+    prefix = os.path.join(ds["dir"], "fmin")  # not "index": <prefix>.sbwt would overwrite the input index.sbwt
     if not os.path.exists(prefix + ".FBV.sdsl"):
         # the index files are inputs of the timed path; any builder that writes the reference's format will do
         ref = reference_binary()

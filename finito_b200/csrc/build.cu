@@ -28,43 +28,62 @@ template <class T> static DevBuf<T> to_device(const std::vector<T>& v, size_t pa
     return d;
 }
 
-// ---- B1: LCS bytes on the device (k launches of lcs_round_kernel) --------------------------------------
-static DevBuf<uint8_t> lcs_on_device(const SbwtHost& s) {
-    uint64_t nw = 0;
-    const std::vector<uint64_t> h_rows = sbwt_row_words(s, nw);
-    DevBuf<uint64_t> rows = to_device(h_rows);
-    const uint64_t N = (uint64_t)s.n_nodes;
-    const uint64_t padded = nw * 64 + 64;
-    DevBuf<uint8_t> last(padded), next(padded), lcs(padded);
-    DevBuf<uint32_t> word_dst(4 * nw);
+// ---- the SBWT rows on the device, with the rank of every 64-column word (shared by the LCS rounds and the lines) ----
+struct DeviceSbwt {
+    DevBuf<uint64_t> rows;       // rows[c * nw + w], bits past N cleared
+    DevBuf<uint32_t> word_dst;   // rank_c(64 w)
+    uint64_t nw = 0, N = 0;
+    LcsArgs args{};
+};
+
+static DeviceSbwt upload_sbwt(const SbwtHost& s) {
+    DeviceSbwt d;
+    d.N = (uint64_t)s.n_nodes;
+    d.nw = (d.N + 63) / 64;
+    const uint64_t nw = d.nw;
+    d.rows.alloc(4 * nw);
+    for (int c = 0; c < 4; c++) {
+        if (s.bits[c].words.size() < nw) throw format_error("SBWT row shorter than the number of columns");
+        FIN_CUDA(cudaMemcpy(d.rows.p + (uint64_t)c * nw, s.bits[c].words.data(), nw * 8, cudaMemcpyHostToDevice));
+    }
+    mask_row_tails_kernel<<<1, 32>>>(d.rows.p, nw, d.N);
+    d.word_dst.alloc(4 * nw);
     const unsigned T = 256;
-    row_popcount_kernel<<<(unsigned)((4 * nw + T - 1) / T), T>>>(rows.p, nw, word_dst.p);
-    g_launches++;
+    row_popcount_kernel<<<(unsigned)((4 * nw + T - 1) / T), T>>>(d.rows.p, nw, d.word_dst.p);
+    g_launches += 2;
     size_t tmp_bytes = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, word_dst.p, word_dst.p, (int64_t)nw);
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d.word_dst.p, d.word_dst.p, (int64_t)nw);
     DevBuf<uint8_t> tmp(tmp_bytes + 256);
     for (int c = 0; c < 4; c++) {
         size_t tb = tmp_bytes;
-        uint32_t* row = word_dst.p + (uint64_t)c * nw;
+        uint32_t* row = d.word_dst.p + (uint64_t)c * nw;
         FIN_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tb, row, row, (int64_t)nw));
         g_launches += 2;
     }
-    LcsArgs a{};
-    a.rows = rows.p;
-    a.word_dst = word_dst.p;
-    a.n = N;
-    a.n_words = nw;
-    for (int c = 0; c < 4; c++) a.C[c] = (uint32_t)s.C[c];
-    a.k = (uint8_t)s.k;
+    d.args.rows = d.rows.p;
+    d.args.word_dst = d.word_dst.p;
+    d.args.n = d.N;
+    d.args.n_words = nw;
+    for (int c = 0; c < 4; c++) d.args.C[c] = (uint32_t)s.C[c];
+    d.args.k = (uint8_t)s.k;
+    FIN_CUDA(cudaGetLastError());
+    return d;
+}
+
+// ---- B1: LCS bytes on the device (k launches of lcs_round_kernel), padded with zeros to 64 * nw + 64 bytes ----------
+static DevBuf<uint8_t> lcs_on_device(const DeviceSbwt& d) {
+    const uint64_t padded = d.nw * 64 + 64;
+    DevBuf<uint8_t> last(padded), next(padded), lcs(padded);
+    const unsigned T = 256;
     FIN_CUDA(cudaMemset(last.p, 0, padded));
     FIN_CUDA(cudaMemset(next.p, 0, padded));
     FIN_CUDA(cudaMemset(lcs.p, 0, padded));
-    lcs_init_kernel<<<(unsigned)((N + T - 1) / T), T>>>(a, last.p, lcs.p);
+    lcs_init_kernel<<<(unsigned)((d.N + T - 1) / T), T>>>(d.args, last.p, lcs.p);
     g_launches++;
     uint8_t* cur = last.p;
     uint8_t* nxt = next.p;
-    for (int64_t round = 0; round < s.k; round++) {
-        lcs_round_kernel<<<(unsigned)((nw + 127) / 128), 128>>>(a, cur, nxt, lcs.p, (uint8_t)round);
+    for (int round = 0; round < (int)d.args.k; round++) {
+        lcs_round_kernel<<<(unsigned)((d.nw + 127) / 128), 128>>>(d.args, cur, nxt, lcs.p, (uint8_t)round);
         g_launches++;
         std::swap(cur, nxt);
     }
@@ -76,10 +95,52 @@ static DevBuf<uint8_t> lcs_on_device(const SbwtHost& s) {
 std::vector<uint8_t> lcs_device(const SbwtHost& s, int device) {
     select_device(device);
     check_sbwt_limits(s);
-    DevBuf<uint8_t> d = lcs_on_device(s);
+    const DeviceSbwt ds = upload_sbwt(s);
+    DevBuf<uint8_t> d = lcs_on_device(ds);
     std::vector<uint8_t> h((size_t)s.n_nodes);
     FIN_CUDA(cudaMemcpy(h.data(), d.p, h.size(), cudaMemcpyDeviceToHost));
     return h;
+}
+
+// device array -> sdsl int_vector of the given width (bit packing on the device, one D2H of the packed words)
+template <class T> static PackedVec pack_on_device(const T* d_in, uint64_t n, int width) {
+    PackedVec v;
+    v.assign(n, (uint8_t)width);
+    const uint64_t nw = v.disk_words();
+    if (nw) {
+        DevBuf<uint64_t> d_words(nw);
+        pack_bits_kernel<T><<<(unsigned)((nw + 255) / 256), 256>>>(d_in, n, (uint32_t)width, d_words.p, nw);
+        g_launches++;
+        FIN_CUDA(cudaGetLastError());
+        FIN_CUDA(cudaMemcpy(v.words.data(), d_words.p, nw * 8, cudaMemcpyDeviceToHost));
+    }
+    return v;
+}
+
+// LCS file -> padded bytes on the device
+static DevBuf<uint8_t> lcs_bytes_from_packed(const PackedVec& lcs, uint64_t nw) {
+    if (lcs.width > 8) throw format_error("LCS wider than 8 bits (k <= 255)");
+    const uint64_t n = lcs.size(), padded = nw * 64 + 64;
+    DevBuf<uint8_t> bytes(padded);
+    FIN_CUDA(cudaMemset(bytes.p, 0, padded));
+    DevBuf<uint64_t> words = to_device(lcs.words);
+    if (n) {
+        unpack_bits_to_bytes_kernel<<<(unsigned)((n + 255) / 256), 256>>>(words.p, n, lcs.width, bytes.p);
+        g_launches++;
+        FIN_CUDA(cudaGetLastError());
+        FIN_CUDA(cudaDeviceSynchronize());
+    }
+    return bytes;
+}
+
+// the 128-byte lines (device_index.cuh) from the rows and the LCS bytes, Ustart / fmin bits left zero
+static DevBuf<uint64_t> make_lines_device(const DeviceSbwt& d, const uint8_t* d_lcs_bytes) {
+    const uint64_t n_lines = (d.N >> 6) + 2;
+    DevBuf<uint64_t> lines(n_lines * 16);
+    make_lines_kernel<<<(unsigned)((n_lines + 127) / 128), 128>>>(d.args, d_lcs_bytes, n_lines, reinterpret_cast<uint4*>(lines.p));
+    g_launches++;
+    FIN_CUDA(cudaGetLastError());
+    return lines;
 }
 
 static int window_capacity(int k) { return k <= 32 ? 32 : k <= 64 ? 64 : k <= 128 ? 128 : 256; }
@@ -134,7 +195,9 @@ static __global__ void tuple_merge_kernel(const uint64_t* __restrict__ tuples, u
 
 class RarestBuilder {
    public:
-    RarestBuilder(SbwtHost&& sbwt, PackedVec&& lcs_file, const SeqBatch& unitigs, int rank, int world)
+    // d_lcs_bytes: the LCS as padded bytes on the device (lcs_on_device / lcs_bytes_from_packed); consumed here
+    RarestBuilder(SbwtHost&& sbwt, PackedVec&& lcs_file, const DeviceSbwt& ds, DevBuf<uint8_t>&& d_lcs_bytes, const SeqBatch& unitigs,
+                  int rank, int world)
         : sbwt_(std::move(sbwt)), lcs_file_(std::move(lcs_file)), rank_(rank), world_(world) {
         if (world < 1 || rank < 0 || rank >= world) throw arg_error("build: rank / world out of range");
         k_ = (int)sbwt_.k;
@@ -142,27 +205,52 @@ class RarestBuilder {
         const uint64_t U = unitigs.size();
         if (lcs_file_.size() != N_) throw format_error("LCS length differs from the number of SBWT columns");
         check_unitigs(unitigs, k_);
-        d_lines_ = to_device(make_lines(sbwt_, &lcs_file_, nullptr, nullptr));
+        d_lines_ = make_lines_device(ds, d_lcs_bytes.p);
+        FIN_CUDA(cudaDeviceSynchronize());
+        d_lcs_bytes.release();
         ix_.lines = reinterpret_cast<const uint4*>(d_lines_.p);
         ix_.n_nodes = (idx_t)N_;
         ix_.k = k_;
+        d_err_.alloc(1);
+        FIN_CUDA(cudaMemset(d_err_.p, 0, 4));
 
-        // first k-mer columns on the file-order text, then the permuted text (B2)
-        std::vector<uint64_t> order(U), starts;
-        std::iota(order.begin(), order.end(), 0);
-        pack_unitigs(unitigs, order, text_, starts);
-        d_text_ = to_device(text_.words, 2);
-        DevBuf<uint64_t> d_starts = to_device(starts);
+        // B2 on the device: first k-mer columns straight from the ASCII unitigs, host sort of the columns, then the
+        // permuted 2-bit text in one pass
+        const uint64_t T = unitigs.seqs.size();
+        DevBuf<char> d_ascii(T + 1);
+        FIN_CUDA(cudaMemcpy(d_ascii.p, unitigs.seqs.data(), T, cudaMemcpyHostToDevice));
+        DevBuf<uint64_t> d_offsets = to_device(unitigs.offsets);
         DevBuf<uint32_t> d_cols(U);
-        first_kmer_kernel<<<(unsigned)((U + 127) / 128), 128>>>(ix_, d_text_.p, d_starts.p, (uint32_t)U, d_cols.p);
+        first_kmer_ascii_kernel<<<(unsigned)((U + 127) / 128), 128>>>(ix_, d_ascii.p, d_offsets.p, (uint32_t)U, d_cols.p, d_err_.p);
         g_launches++;
         FIN_CUDA(cudaGetLastError());
         std::vector<uint32_t> cols(U);
         FIN_CUDA(cudaMemcpy(cols.data(), d_cols.p, U * 4, cudaMemcpyDeviceToHost));
-        order = unitig_order(cols, N_, ustart_);
-        pack_unitigs(unitigs, order, text_, starts);
-        FIN_CUDA(cudaMemcpy(d_text_.p, text_.words.data(), text_.words.size() * 8, cudaMemcpyHostToDevice));
-        ends_ = unitig_ends(unitigs, order, starts);
+        check_bases();
+        const std::vector<uint64_t> order = unitig_order(cols, N_, ustart_);
+        std::vector<uint64_t> starts(U), src(U);
+        ends_.assign(U, 64);  // width stays 64 (PackedStrings.hh:44 passes the bit length as the default VALUE)
+        uint64_t pos = 0;
+        for (uint64_t j = 0; j < U; j++) {
+            const uint64_t u = order[j];
+            starts[j] = pos;
+            src[j] = unitigs.offsets[u];
+            pos += unitigs.offsets[u + 1] - unitigs.offsets[u];
+            ends_.words[j] = pos;
+        }
+        text_.assign(T, 2);
+        const uint64_t n_text_words = text_.words.size();  // disk words + 1 pad
+        d_text_.alloc(n_text_words + 2);
+        FIN_CUDA(cudaMemset(d_text_.p, 0, d_text_.bytes()));
+        {
+            DevBuf<uint64_t> d_starts = to_device(starts), d_src = to_device(src);
+            pack_text_kernel<<<(unsigned)((n_text_words + 255) / 256), 256>>>(d_ascii.p, d_starts.p, d_src.p, (uint32_t)U, T, d_text_.p,
+                                                                            n_text_words, d_err_.p);
+            g_launches++;
+            FIN_CUDA(cudaGetLastError());
+            FIN_CUDA(cudaMemcpy(text_.words.data(), d_text_.p, n_text_words * 8, cudaMemcpyDeviceToHost));
+        }
+        check_bases();
 
         chunks_ = plan_build_chunks(starts, ends_, k_, 0);
         const std::pair<size_t, size_t> mine = shard_chunks(chunks_, rank, world);
@@ -171,8 +259,6 @@ class RarestBuilder {
         slice_cols_ = world == 1 ? N_ : slice_columns(N_, world);
         slice_begin_ = (uint64_t)rank * slice_cols_;
         for (size_t c = chunk_begin_; c < chunk_end_; c++) bases_streamed_ += chunks_[c].n_stream;
-        d_err_.alloc(1);
-        FIN_CUDA(cudaMemset(d_err_.p, 0, 4));
     }
 
     uint64_t n_nodes() const { return N_; }
@@ -319,6 +405,11 @@ class RarestBuilder {
     }
 
    private:
+    void check_bases() {
+        unsigned err = 0;
+        FIN_CUDA(cudaMemcpy(&err, d_err_.p, 4, cudaMemcpyDeviceToHost));
+        if (err & kErrBadBase) throw domain_error("Invalid character");  // PackedStrings.hh:57
+    }
     void check_errors() {
         unsigned err = 0;
         FIN_CUDA(cudaMemcpy(&err, d_err_.p, 4, cudaMemcpyDeviceToHost));
@@ -345,9 +436,10 @@ class RarestBuilder {
 extern thread_local fin_build_timing g_build_timing;
 static double wall_ms();
 
-static void build_rarest(SbwtHost&& sbwt, PackedVec&& lcs_file, const SeqBatch& unitigs, const std::string& out_prefix) {
+static void build_rarest(SbwtHost&& sbwt, PackedVec&& lcs_file, const DeviceSbwt& ds, DevBuf<uint8_t>&& d_lcs_bytes, const SeqBatch& unitigs,
+                         const std::string& out_prefix) {
     const double t0 = wall_ms();
-    RarestBuilder b(std::move(sbwt), std::move(lcs_file), unitigs, 0, 1);
+    RarestBuilder b(std::move(sbwt), std::move(lcs_file), ds, std::move(d_lcs_bytes), unitigs, 0, 1);
     const double t1 = wall_ms();
     b.stream();
     b.merge(nullptr, 0);
@@ -364,15 +456,14 @@ static void build_rarest(SbwtHost&& sbwt, PackedVec&& lcs_file, const SeqBatch& 
 
 // ---- B5 / B6: --type shortest | verify, statistics only (build_fmin.hh:95-214,252-267) ---------------------------
 // Unitigs stay in FILE order here (no permutation): the shared fmin_found bit vector of B5 makes the result depend on it.
-static std::string build_stats(const SbwtHost& sbwt, const PackedVec& lcs_file, const SeqBatch& unitigs, const std::string& type,
-                               int64_t t) {
+static std::string build_stats(const SbwtHost& sbwt, const DeviceSbwt& ds, const uint8_t* d_lcs_bytes, const SeqBatch& unitigs,
+                               const std::string& type, int64_t t) {
     const int k = (int)sbwt.k;
     const uint64_t N = (uint64_t)sbwt.n_nodes, U = unitigs.size();
-    if (lcs_file.size() != N) throw format_error("LCS length differs from the number of SBWT columns");
     check_unitigs(unitigs, k);
     check_stats_t(t, sbwt.n_nodes);
 
-    DevBuf<uint64_t> d_lines = to_device(make_lines(sbwt, &lcs_file, nullptr, nullptr));
+    DevBuf<uint64_t> d_lines = make_lines_device(ds, d_lcs_bytes);
     IndexView ix{};
     ix.lines = reinterpret_cast<const uint4*>(d_lines.p);
     ix.n_nodes = (idx_t)N;
@@ -467,13 +558,20 @@ static std::string build_stats(const SbwtHost& sbwt, const PackedVec& lcs_file, 
 }
 
 // ---- staged builder behind the fin_builder_* entry points ---------------------------------------------------------
-static PackedVec lcs_for_build(const SbwtHost& sbwt, const std::string& lcs_path, const std::string& out_prefix, bool write_file) {
-    if (!lcs_path.empty()) return load_packed_file(lcs_path, 0);
-    // build_fmin.hh:373-380: compute and save; the reference then loads the file back, which yields the same vector
-    DevBuf<uint8_t> d = lcs_on_device(sbwt);
-    std::vector<uint8_t> h((size_t)sbwt.n_nodes);
-    FIN_CUDA(cudaMemcpy(h.data(), d.p, h.size(), cudaMemcpyDeviceToHost));
-    PackedVec lcs = lcs_bytes_to_packed(h, h.size(), sbwt.k);
+// LCS of a build: given as a file (--lcs) or computed on the device and saved (build_fmin.hh:373-380; the reference then
+// loads the file back, which yields the same vector).  Returns the file form and leaves the padded bytes on the device.
+static PackedVec lcs_for_build(const SbwtHost& sbwt, const DeviceSbwt& ds, const std::string& lcs_path, const std::string& out_prefix,
+                               bool write_file, DevBuf<uint8_t>& d_bytes) {
+    if (!lcs_path.empty()) {
+        PackedVec lcs = load_packed_file(lcs_path, 0);
+        if (lcs.size() != (uint64_t)sbwt.n_nodes) throw format_error("LCS length differs from the number of SBWT columns");
+        d_bytes = lcs_bytes_from_packed(lcs, ds.nw);
+        return lcs;
+    }
+    d_bytes = lcs_on_device(ds);
+    const int w = bit_length((uint64_t)(sbwt.k - 1));  // lcs_basic_parallel_algorithm.hpp:115
+    if (w == 0) throw domain_error("k = 1 is outside the parity domain");
+    PackedVec lcs = pack_on_device<uint8_t>(d_bytes.p, (uint64_t)sbwt.n_nodes, w);
     if (write_file) save_packed_file(out_prefix + ".LCS.sdsl", lcs, true);
     return lcs;
 }
@@ -484,10 +582,12 @@ RarestBuilder* builder_open(const std::string& sbwt_path, const std::string& uni
     SbwtHost sbwt = load_sbwt_file(sbwt_path, true);
     select_device(device);
     check_sbwt_limits(sbwt);
-    PackedVec lcs = lcs_for_build(sbwt, lcs_path, out_prefix, rank == 0);
+    const DeviceSbwt ds = upload_sbwt(sbwt);
+    DevBuf<uint8_t> d_lcs;
+    PackedVec lcs = lcs_for_build(sbwt, ds, lcs_path, out_prefix, rank == 0, d_lcs);
     SeqBatch unitigs;
     append_sequences(files[0], unitigs);
-    return new RarestBuilder(std::move(sbwt), std::move(lcs), unitigs, rank, world);
+    return new RarestBuilder(std::move(sbwt), std::move(lcs), ds, std::move(d_lcs), unitigs, rank, world);
 }
 void builder_free(RarestBuilder* b) { delete b; }
 fin_builder_info builder_info(const RarestBuilder& b) {
@@ -537,15 +637,9 @@ std::string build_fmin_device(const std::string& sbwt_path, const std::string& u
     check_sbwt_limits(sbwt);
 
     const double t_loaded = wall_ms();
-    std::string lcs_file = lcs_path;
-    if (lcs_file.empty()) {  // :373-380: compute, save, then load it back like the reference does
-        lcs_file = out_prefix + ".LCS.sdsl";
-        DevBuf<uint8_t> d = lcs_on_device(sbwt);
-        std::vector<uint8_t> h((size_t)sbwt.n_nodes);
-        FIN_CUDA(cudaMemcpy(h.data(), d.p, h.size(), cudaMemcpyDeviceToHost));
-        save_packed_file(lcs_file, lcs_bytes_to_packed(h, h.size(), sbwt.k), true);
-    }
-    PackedVec lcs = load_packed_file(lcs_file, 0);
+    const DeviceSbwt ds = upload_sbwt(sbwt);
+    DevBuf<uint8_t> d_lcs;
+    PackedVec lcs = lcs_for_build(sbwt, ds, lcs_path, out_prefix, true, d_lcs);
     const double t_lcs = wall_ms();
 
     std::string result;
@@ -558,9 +652,9 @@ std::string build_fmin_device(const std::string& sbwt_path, const std::string& u
     g_build_timing.unitig_bases = (int64_t)unitigs.seqs.size();
     if (type == "rarest") {
         if (t != 1) throw domain_error("t != 1 does not make sense with rarest type");  // :245-247
-        build_rarest(std::move(sbwt), std::move(lcs), unitigs, out_prefix);
+        build_rarest(std::move(sbwt), std::move(lcs), ds, std::move(d_lcs), unitigs, out_prefix);
     } else {
-        result = build_stats(sbwt, lcs, unitigs, type, t);
+        result = build_stats(sbwt, ds, d_lcs.p, unitigs, type, t);
     }
     append_stats_line(out_prefix, (int)t, result);
     g_build_timing.total_ms = (float)(wall_ms() - t_begin);

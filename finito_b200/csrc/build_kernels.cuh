@@ -375,6 +375,115 @@ static __global__ void fmin_bits_kernel(const unsigned long long* __restrict__ t
     if (i < n) offs_or_sentinel[i] = key ? fmin_key_offset(key) : 0xFFFFFFFFu;
 }
 
+// ---- preparation on the device: bit packing, the 128-byte lines, the permuted 2-bit text -------------------------
+// sdsl int_vector layout (int_vector.hpp:624-640): element i occupies bits [i*w, (i+1)*w) LSB-first.  One thread
+// assembles one 64-bit word of the packed vector from the elements that overlap it.
+template <class T>
+__global__ void pack_bits_kernel(const T* __restrict__ in, uint64_t n, uint32_t width, uint64_t* __restrict__ words, uint64_t n_words) {
+    const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= n_words) return;
+    const uint64_t bit0 = w * 64;
+    uint64_t i = bit0 / width;
+    uint64_t out = 0;
+    for (; i < n && i * width < bit0 + 64; i++) {
+        const uint64_t v = (uint64_t)in[i], b = i * width;
+        out |= b >= bit0 ? v << (b - bit0) : v >> (bit0 - b);
+    }
+    words[w] = out;
+}
+
+// the inverse, for widths <= 8 (an LCS file given with --lcs): one thread per element
+static __global__ void unpack_bits_to_bytes_kernel(const uint64_t* __restrict__ words, uint64_t n, uint32_t width, uint8_t* __restrict__ out) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t bit = i * width, wi = bit >> 6, off = bit & 63;
+    uint64_t v = words[wi] >> off;
+    if (off + width > 64) v |= words[wi + 1] << (64 - off);
+    out[i] = (uint8_t)(v & ((1ULL << width) - 1ULL));
+}
+
+// clears the bits past n in the last word of each of the 4 rows (they never count, SBWT.hh:395-424 stores whole words)
+static __global__ void mask_row_tails_kernel(uint64_t* __restrict__ rows, uint64_t n_words, uint64_t n) {
+    const uint32_t c = threadIdx.x;
+    if (c < 4 && (n & 63)) rows[(uint64_t)c * n_words + n_words - 1] &= (1ULL << (n & 63)) - 1ULL;
+}
+
+// the lines of device_index.cuh without Ustart / fmin bits (build-fmin streams before they exist): one thread per line
+static __global__ void make_lines_kernel(const LcsArgs a, const uint8_t* __restrict__ lcs_bytes, uint64_t n_lines, uint4* __restrict__ lines) {
+    const uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= n_lines) return;
+    uint4* line = lines + b * 8;
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        uint64_t bits = 0;
+        uint32_t cum;
+        if (b < a.n_words) {
+            bits = a.rows[(uint64_t)c * a.n_words + b];
+            cum = a.C[c] + a.word_dst[(uint64_t)c * a.n_words + b];
+        } else {  // past the end: rank of the whole row
+            cum = a.C[c] + a.word_dst[(uint64_t)c * a.n_words + a.n_words - 1] +
+                  (uint32_t)__popcll(a.rows[(uint64_t)c * a.n_words + a.n_words - 1]);
+        }
+        line[c] = make_uint4((uint32_t)bits, (uint32_t)(bits >> 32), cum, 0u);
+    }
+    // lcs_bytes is padded with zeros to 64 * n_words + 64 bytes
+    const uint4* src = reinterpret_cast<const uint4*>(lcs_bytes + b * 64);
+#pragma unroll
+    for (int q = 0; q < 4; q++) line[4 + q] = b <= a.n_words ? src[q] : make_uint4(0, 0, 0, 0);
+}
+
+FIN_D int ascii_code(uint32_t ch, bool& bad) {  // PackedStrings.hh:53-57: A,C,G,T only (the reader upper-cased already)
+    bad |= !(ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T');
+    return (int)(((ch >> 1) ^ (ch >> 2)) & 3u);
+}
+
+// SBWT column of the first k-mer of every unitig straight from the ASCII text (PackedStrings.hh:116,129-131)
+static __global__ void first_kmer_ascii_kernel(const IndexView ix, const char* __restrict__ ascii, const uint64_t* __restrict__ offsets,
+                                               uint32_t n_unitigs, uint32_t* __restrict__ columns, unsigned int* __restrict__ error_flags) {
+    const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= n_unitigs) return;
+    const char* s = ascii + offsets[u];
+    Ival I{0, ix.n_nodes - 1};
+    bool bad = false;
+    for (int i = 0; i < ix.k && !is_empty(I); i++) I = extend(ix, I, ascii_code((uint8_t)s[i], bad));
+    columns[u] = (!bad && !is_empty(I) && I.l == I.r) ? I.l : 0xFFFFFFFFu;
+    if (bad) atomicOr(error_flags, kErrBadBase);
+}
+
+// concatenation of the unitigs in permuted order, 2 bits per base (PackedStrings.hh:36-64): one thread per output word.
+// starts[j] = text position of the j-th unitig of the new order, src[j] = offset of its characters in `ascii`.
+static __global__ void pack_text_kernel(const char* __restrict__ ascii, const uint64_t* __restrict__ starts, const uint64_t* __restrict__ src,
+                                        uint32_t n_unitigs, uint64_t text_len, uint64_t* __restrict__ words, uint64_t n_words,
+                                        unsigned int* __restrict__ error_flags) {
+    const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= n_words) return;
+    const uint64_t p0 = w * 32;
+    uint64_t out = 0;
+    if (p0 < text_len) {
+        uint32_t lo = 0, hi = n_unitigs;  // last unitig whose start is <= p0
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (starts[mid] <= p0) lo = mid;
+            else hi = mid;
+        }
+        uint32_t j = lo;
+        uint64_t next_start = j + 1 < n_unitigs ? starts[j + 1] : text_len;
+        const char* s = ascii + src[j] - starts[j];  // s[p] is the character of text position p
+        bool bad = false;
+        const uint64_t p1 = min(p0 + 32, text_len);
+        for (uint64_t p = p0; p < p1; p++) {
+            if (p == next_start) {
+                j++;
+                next_start = j + 1 < n_unitigs ? starts[j + 1] : text_len;
+                s = ascii + src[j] - starts[j];
+            }
+            out |= (uint64_t)ascii_code((uint8_t)s[p], bad) << (2 * (p - p0));
+        }
+        if (bad) atomicOr(error_flags, kErrBadBase);
+    }
+    words[w] = out;
+}
+
 // ---- statistics modes (B5, B6) ------------------------------------------------------------------------------
 template <int KCAP, int PASS>
 __global__ void __launch_bounds__(128) shortest_stream_kernel(const IndexView ix, const uint64_t* __restrict__ text,

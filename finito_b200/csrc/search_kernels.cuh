@@ -512,8 +512,11 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
 #ifdef __CUDACC__
 // Persistent warps: a lane that finishes its read takes the next one from a global counter (one atomic per
 // group of lanes that run dry in the same iteration), so no lane idles while reads remain.
+#ifndef FIN_SEARCH_MIN_BLOCKS
+#define FIN_SEARCH_MIN_BLOCKS 8  // 64 registers; 10 and 12 blocks spill and lose 4-30 % (profiles/r1_sweep_occupancy.log)
+#endif
 template <int KCAP, class HitT, bool COUNT>
-__global__ void __launch_bounds__(128) search_reads_kernel(const IndexView ix, const uint64_t* __restrict__ packed,
+__global__ void __launch_bounds__(128, FIN_SEARCH_MIN_BLOCKS) search_reads_kernel(const IndexView ix, const uint64_t* __restrict__ packed,
                                                            const uint64_t* __restrict__ read_offsets, const uint64_t n_reads,
                                                            const uint64_t* __restrict__ out_offsets,
                                                            HitPair<HitT>* __restrict__ out, SearchTotals* __restrict__ totals,

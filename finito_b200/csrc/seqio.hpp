@@ -65,33 +65,46 @@ inline void append_sequences(const std::string& path, SeqBatch& out) {
     if (p == end || *p != (fmt == SeqFormat::Fasta ? '>' : '@'))  // SeqIO.hh read_first_char_and_sanity_check
         throw io_error(std::string("ERROR: ") + (fmt == SeqFormat::Fasta ? "FASTA" : "FASTQ") + " file " + path +
                        " does not start with '" + (fmt == SeqFormat::Fasta ? ">" : "@") + "'");
-    out.seqs.reserve(out.seqs.size() + buf.size());
+    // worst case every byte is a base; whole lines are copied with memcpy and upper-cased afterwards in one pass
+    const size_t base0 = out.seqs.size();
+    out.seqs.resize(base0 + buf.size());
+    char* dst = out.seqs.data() + base0;
     auto skip_line = [&]() {
-        while (p < end && *p != '\n') p++;
-        if (p < end) p++;
+        const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
+        p = nl ? nl + 1 : end;
+    };
+    auto copy_line = [&]() {  // copies up to (not including) the newline, consumes the newline
+        const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
+        const char* stop = nl ? nl : end;
+        memcpy(dst, p, (size_t)(stop - p));
+        dst += stop - p;
+        p = nl ? nl + 1 : end;
     };
     if (fmt == SeqFormat::Fasta) {
         while (p < end) {
             skip_line();  // header
-            const size_t before = out.seqs.size();
-            while (p < end && *p != '>') {
-                if (*p != '\n') out.seqs.push_back((char)toupper((unsigned char)*p));
-                p++;
-            }
-            if (out.seqs.size() == before) throw domain_error("Error: empty sequence in FASTA file.");
-            out.offsets.push_back(out.seqs.size());
+            const char* before = dst;
+            while (p < end && *p != '>') copy_line();
+            if (dst == before) throw domain_error("Error: empty sequence in FASTA file.");
+            out.offsets.push_back((uint64_t)(dst - out.seqs.data()));
         }
     } else {
         while (p < end) {
             skip_line();  // header
-            const size_t before = out.seqs.size();
-            while (p < end && *p != '\n') out.seqs.push_back((char)toupper((unsigned char)*p++));
-            if (p < end) p++;
+            const char* before = dst;
+            copy_line();
             skip_line();  // '+'
             skip_line();  // qualities
-            if (out.seqs.size() == before) throw domain_error("Error: empty sequence in FASTQ file.");
-            out.offsets.push_back(out.seqs.size());
+            if (dst == before) throw domain_error("Error: empty sequence in FASTQ file.");
+            out.offsets.push_back((uint64_t)(dst - out.seqs.data()));
         }
+    }
+    const size_t n_new = (size_t)(dst - (out.seqs.data() + base0));
+    out.seqs.resize(base0 + n_new);
+    char* q = out.seqs.data() + base0;
+    for (size_t i = 0; i < n_new; i++) {  // toupper of the reference's reader (SeqIO.hh:232), branch-free so it vectorises
+        const char c = q[i];
+        q[i] = (char)(c - ((c >= 'a' && c <= 'z') ? 32 : 0));
     }
 }
 
