@@ -387,6 +387,11 @@ def main():
         l2_bytes = 126e6
         regime = ("L2-resident at this config: the sector model counts every access as HBM traffic" if info["device_bytes"] < l2_bytes
                   else f"{info['device_bytes'] / l2_bytes:.1f}x the 126 MB L2: random sectors mostly come from HBM")
+        try:
+            random_peaks = {b: fb.probe_random_sectors(local_rank, 8 << 30, 3, b) for b in (32, 64, 128)}
+            random_peak = random_peaks[32]
+        except fb.FinitoError:
+            random_peaks, random_peak = None, None
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": traffic["dram_bytes_per_read"] * n_reads if traffic else None,
                     "traffic_source": (f"ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of a {traffic['reads_in_captured_launch']}-read launch "
@@ -394,6 +399,8 @@ def main():
                     "kernel": "search_reads_kernel", "kernel_ms": avg_search_s * 1e3, "kernel_share_of_step": float(np.sum(search_ms)) / dev_total_ms if world == 1 else None,
                     "algorithmic_bytes_per_launch": bytes_per_launch, "algorithmic_bytes_per_kmer": bytes_per_launch / kmers_per_step,
                     "peak_source": peak_src,
+                    "random_sector_peak": random_peak, "random_access_peaks_by_bytes": random_peaks, "frac_of_random_sector_peak": achieved / random_peak if random_peak else None,
+                    "random_sector_peak_source": "fin_probe_random_sectors: independent random 32-byte reads over an 8 GiB table, measured in this run",
                     "note": f"index is {info['device_bytes'] / 1e6:.1f} MB ({regime})"}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:

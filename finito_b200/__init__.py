@@ -82,6 +82,7 @@ ABI = {
     "fin_search_set_counting": (C.c_int, [C.c_void_p, C.c_int]),
     "fin_search_last_timing": (C.c_int, [C.c_void_p, C.POINTER(_Timing)]),
     "fin_launch_count": (C.c_uint64, []),
+    "fin_probe_random_sectors": (C.c_int, [C.c_int, C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "fin_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "fin_host_free": (None, [C.c_void_p]),
     "fin_build": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int, C.c_char_p,
@@ -303,6 +304,13 @@ class ShardedBuilder:
         offsets_all = np.ascontiguousarray(offsets_all, dtype=np.uint32)
         _check(lib().fin_builder_finish(self._h, bits_all.ctypes.data, bits_all.size, offsets_all.ctypes.data, offsets_all.size,
                                         os.fsencode(self.out_prefix)))
+
+
+def probe_random_sectors(device: int = 0, table_bytes: int = 8 << 30, repeats: int = 3, bytes_per_access: int = 32) -> float:
+    """GB/s of independent random 32-byte sector reads (fin_probe_random_sectors): the HBM random-access roofline."""
+    out = C.c_double()
+    _check(lib().fin_probe_random_sectors(device, table_bytes, repeats, bytes_per_access, C.byref(out)))
+    return float(out.value)
 
 
 def build_timing() -> dict:

@@ -139,6 +139,13 @@ fin_status fin_search_last_timing(const fin_index* index, fin_search_timing* out
 
 uint64_t fin_launch_count(void) { return fin::g_launches; }
 
+fin_status fin_probe_random_sectors(int device, uint64_t table_bytes, int repeats, int bytes_per_access, double* gb_per_s) {
+    return guarded([&] {
+        require(gb_per_s != nullptr, "fin_probe_random_sectors: null argument");
+        *gb_per_s = fin::probe_random_sectors(device, table_bytes, repeats, bytes_per_access);
+    });
+}
+
 fin_status fin_host_alloc(size_t bytes, void** out) {
     return guarded([&] {
         require(out != nullptr, "fin_host_alloc: null argument");

@@ -93,8 +93,19 @@ FIN_D idx_t step_c(const IndexView& ix, const idx_t p, const int c) {
 // r+1 share a line, which is the common case once the interval is narrow.
 FIN_D Ival extend(const IndexView& ix, const Ival I, const int c) {
     Ival J;
+#ifdef FIN_EXTEND_SHARED_ROW
+    // l and r + 1 usually fall into the same 64-column line: then one 16-byte load serves both ranks
+    const idx_t p = I.l, q = I.r + 1;
+    const uint4 row = __ldg(ix.lines + (((p >> 6) << 3) | (uint32_t)c));
+    uint4 row2 = row;
+    if ((q >> 6) != (p >> 6)) row2 = __ldg(ix.lines + (((q >> 6) << 3) | (uint32_t)c));
+    const uint64_t b1 = (uint64_t)row.x | ((uint64_t)row.y << 32), b2 = (uint64_t)row2.x | ((uint64_t)row2.y << 32);
+    J.l = row.z + (idx_t)__popcll(b1 & ((1ULL << (p & 63)) - 1ULL));
+    J.r = row2.z + (idx_t)__popcll(b2 & ((1ULL << (q & 63)) - 1ULL)) - 1;
+#else
     J.l = step_c(ix, I.l, c);
     J.r = step_c(ix, I.r + 1, c) - 1;  // equal ranks give r == l - 1: empty
+#endif
     return J;
 }
 

@@ -99,7 +99,7 @@ static int window_capacity(int k) { return k <= 32 ? 32 : k <= 64 ? 64 : k <= 12
 template <int KCAP, class HitT, bool COUNT>
 static void launch_search_k(const IndexView& v, const uint64_t* packed, const uint64_t* offsets, uint64_t n_reads,
                             const uint64_t* out_offsets, HitPair<HitT>* o, SearchTotals* totals, int n_strands, cudaStream_t st) {
-    const int threads = 128;
+    const int threads = FIN_SEARCH_THREADS;
     static thread_local int resident[64] = {0};  // per device
     int dev = 0;
     FIN_CUDA(cudaGetDevice(&dev));

@@ -109,14 +109,27 @@ enum : unsigned { kDropLeft = 1u, kDropRight = 2u };
 // u64 index of the aligned 8-byte LCS word of column p inside the lines array (< n_nodes / 4: fits 32 bits)
 FIN_D uint32_t lcs_word_index(const idx_t p) { return ((p >> 6) << 4) | 8u | ((p >> 3) & 7u); }
 
+// Left end: w = the LCS word of column l.  Returns the new l; found = the scan stopped inside this word.
+template <bool WIDE> FIN_D idx_t drop_left_word(const uint64_t w, const idx_t l, const int new_len, bool& found) {
+    const uint32_t j = l & 7u;
+    const uint64_t stop = bytes_below<WIDE>(w, new_len) << (8u * (7u - j));  // bytes above l shifted out
+    found = stop != 0;  // always true in the word of column 0: LCS[0] = 0
+    return found ? l - (idx_t)(__clzll((long long)stop) >> 3) : l - j - 1u;
+}
+// Right end: w = the LCS word of column r + 1.  Returns the new r.
+template <bool WIDE> FIN_D idx_t drop_right_word(const uint64_t w, const idx_t r, const int new_len, bool& found) {
+    const idx_t rp = r + 1;
+    const uint32_t j = rp & 7u;
+    const uint64_t stop = bytes_below<WIDE>(w, new_len) >> (8u * j);  // bytes below r+1 shifted out
+    found = stop != 0;
+    return found ? r + (idx_t)((__ffsll((long long)stop) - 1) >> 3) : (rp | 7u);
+}
+
 // Left end: w = the LCS word of column I.l.  Clears kDropLeft in pend unless the scan runs off the word.
 template <bool WIDE, bool COUNT>
 FIN_D void drop_left(const uint64_t w, Ival& I, const int new_len, unsigned& pend, unsigned& n_lcs) {
-    const idx_t l = I.l;
-    const uint32_t j = l & 7u;
-    const uint64_t stop = bytes_below<WIDE>(w, new_len) << (8u * (7u - j));  // bytes above l shifted out
-    const bool found = stop != 0;  // always true in the word of column 0: LCS[0] = 0
-    const idx_t nl = found ? l - (idx_t)(__clzll((long long)stop) >> 3) : l - j - 1u;
+    bool found;
+    const idx_t l = I.l, nl = drop_left_word<WIDE>(w, l, new_len, found);
     if (COUNT) n_lcs += (l - nl) + (found && nl > 0 ? 1u : 0u);
     if (found) pend &= ~kDropLeft;
     I.l = nl;
@@ -125,11 +138,8 @@ FIN_D void drop_left(const uint64_t w, Ival& I, const int new_len, unsigned& pen
 // Right end: w = the LCS word of column I.r + 1.
 template <bool WIDE, bool COUNT>
 FIN_D void drop_right(const uint64_t w, Ival& I, const int new_len, unsigned& pend, const idx_t n_nodes, unsigned& n_lcs) {
-    const idx_t rp = I.r + 1;
-    const uint32_t j = rp & 7u;
-    const uint64_t stop = bytes_below<WIDE>(w, new_len) >> (8u * j);  // bytes below r+1 shifted out
-    const bool found = stop != 0;
-    const idx_t nr = found ? I.r + (idx_t)((__ffsll((long long)stop) - 1) >> 3) : (rp | 7u);
+    bool found;
+    const idx_t nr = drop_right_word<WIDE>(w, I.r, new_len, found);
     if (COUNT) n_lcs += (nr - I.r) + (found && nr < n_nodes - 1 ? 1u : 0u);
     if (found) pend &= ~kDropRight;
     I.r = nr;
@@ -187,7 +197,7 @@ constexpr int kMaxReadLen = (1 << 24) - 1;
 // Every lane of the warp calls step() in every iteration, so the phases can be fenced with warp barriers: they keep
 // the compiler from threading a phase into the branches of the one before it (which would execute it once per
 // incoming path, each time for a few lanes).
-#ifdef FIN_EMU
+#if defined(FIN_EMU) || defined(FIN_NO_FENCE)
 #define FIN_PHASE_FENCE() do {} while (0)
 #else
 #define FIN_PHASE_FENCE() __syncwarp()
@@ -362,10 +372,32 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                 bestU_col = ucol;
             }
         }
+#ifdef FIN_BRANCHY_DROPS
         if (pendI & kDropLeft) drop_left<WIDE, COUNT>(w_il, I, lenI, pendI, rc.c_lcs);
         if (pendI & kDropRight) drop_right<WIDE, COUNT>(w_ir, I, lenI, pendI, N, rc.c_lcs);
         if (pendK & kDropLeft) drop_left<WIDE, COUNT>(w_kl, Ik, lenK, pendK, rc.c_lcs);
         if (pendK & kDropRight) drop_right<WIDE, COUNT>(w_kr, Ik, lenK, pendK, N, rc.c_lcs);
+#else
+        // all four word steps computed by every lane, committed by select: no divergent regions in this phase
+        {
+            bool f_il, f_ir, f_kl, f_kr;
+            const idx_t n_il = drop_left_word<WIDE>(w_il, I.l, lenI, f_il), n_ir = drop_right_word<WIDE>(w_ir, I.r, lenI, f_ir);
+            const idx_t n_kl = drop_left_word<WIDE>(w_kl, Ik.l, lenK, f_kl), n_kr = drop_right_word<WIDE>(w_kr, Ik.r, lenK, f_kr);
+            const bool d_il = pendI & kDropLeft, d_ir = pendI & kDropRight, d_kl = pendK & kDropLeft, d_kr = pendK & kDropRight;
+            if (COUNT) {
+                if (d_il) rc.c_lcs += (I.l - n_il) + (f_il && n_il > 0 ? 1u : 0u);
+                if (d_ir) rc.c_lcs += (n_ir - I.r) + (f_ir && n_ir < N - 1 ? 1u : 0u);
+                if (d_kl) rc.c_lcs += (Ik.l - n_kl) + (f_kl && n_kl > 0 ? 1u : 0u);
+                if (d_kr) rc.c_lcs += (n_kr - Ik.r) + (f_kr && n_kr < N - 1 ? 1u : 0u);
+            }
+            I.l = d_il ? n_il : I.l;
+            I.r = d_ir ? n_ir : I.r;
+            Ik.l = d_kl ? n_kl : Ik.l;
+            Ik.r = d_kr ? n_kr : Ik.r;
+            pendI &= ~((d_il && f_il ? kDropLeft : 0u) | (d_ir && f_ir ? kDropRight : 0u));
+            pendK &= ~((d_kl && f_kl ? kDropLeft : 0u) | (d_kr && f_kr ? kDropRight : 0u));
+        }
+#endif
     }
     FIN_PHASE_FENCE();
 
@@ -512,11 +544,14 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
 #ifdef __CUDACC__
 // Persistent warps: a lane that finishes its read takes the next one from a global counter (one atomic per
 // group of lanes that run dry in the same iteration), so no lane idles while reads remain.
+#ifndef FIN_SEARCH_THREADS
+#define FIN_SEARCH_THREADS 128
+#endif
 #ifndef FIN_SEARCH_MIN_BLOCKS
 #define FIN_SEARCH_MIN_BLOCKS 8  // 64 registers; 10 and 12 blocks spill and lose 4-30 % (profiles/r1_sweep_occupancy.log)
 #endif
 template <int KCAP, class HitT, bool COUNT>
-__global__ void __launch_bounds__(128, FIN_SEARCH_MIN_BLOCKS) search_reads_kernel(const IndexView ix, const uint64_t* __restrict__ packed,
+__global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) search_reads_kernel(const IndexView ix, const uint64_t* __restrict__ packed,
                                                            const uint64_t* __restrict__ read_offsets, const uint64_t n_reads,
                                                            const uint64_t* __restrict__ out_offsets,
                                                            HitPair<HitT>* __restrict__ out, SearchTotals* __restrict__ totals,

@@ -130,6 +130,11 @@ fin_status fin_search_last_timing(const fin_index* index, fin_search_timing* out
  * gpu_launches claim is read from here). */
 uint64_t fin_launch_count(void);
 
+/* Measurement aid: GB/s of data-independent random reads of `bytes_per_access` (32, 64 or 128: aligned runs of 32-byte sectors) over a table of
+ * `table_bytes` (use >= 4 GiB so that the 126 MB L2 does not matter), best of `repeats`.  The HBM random-access roofline
+ * bench.py reports beside the copy peak. */
+fin_status fin_probe_random_sectors(int device, uint64_t table_bytes, int repeats, int bytes_per_access, double* gb_per_s);
+
 /* Pinned host memory for the batch buffers (cudaHostAlloc / cudaFreeHost). */
 fin_status fin_host_alloc(size_t bytes, void** out);
 void fin_host_free(void* p);
