@@ -399,8 +399,11 @@ def main():
                     "kernel": "search_reads_kernel", "kernel_ms": avg_search_s * 1e3, "kernel_share_of_step": float(np.sum(search_ms)) / dev_total_ms if world == 1 else None,
                     "algorithmic_bytes_per_launch": bytes_per_launch, "algorithmic_bytes_per_kmer": bytes_per_launch / kmers_per_step,
                     "peak_source": peak_src,
-                    "random_sector_peak": random_peak, "random_access_peaks_by_bytes": random_peaks, "frac_of_random_sector_peak": achieved / random_peak if random_peak else None,
-                    "random_sector_peak_source": "fin_probe_random_sectors: independent random 32-byte reads over an 8 GiB table, measured in this run",
+                    "random_access_probe_gbs_by_bytes": random_peaks,
+                    "random_access_probe_note": "fin_probe_random_sectors, measured in this run: REQUESTED bytes/s of data-independent random 32/64/128-byte reads over an 8 GiB table "
+                                                "(no cache reuse at all; ncu shows the DRAM moves ~4x the requested bytes at 32 B: profiles/r1_probe_random_sectors_ncu.txt). "
+                                                "The search kernel's requests mostly hit L1/L2 (two ends of an interval, its LCS words and rank rows share a line), so its sector-model "
+                                                "figure is not bounded by this probe; its DRAM traffic is in `traffic`",
                     "note": f"index is {info['device_bytes'] / 1e6:.1f} MB ({regime})"}
         cpu = None
         if world == 1 and not args.no_cpu_baseline:

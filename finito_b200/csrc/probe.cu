@@ -19,7 +19,7 @@ static __global__ void __launch_bounds__(256) random_sector_kernel(const uint4* 
 #pragma unroll
         for (int j = 0; j < INFLIGHT; j++) {
             s = s * 6364136223846793005ULL + 1442695040888963407ULL;
-            const uint64_t loc = (s >> 20) % n_locations;
+            const uint64_t loc = __umul64hi(s, n_locations);  // uniform in [0, n_locations) without a division
 #pragma unroll
             for (int q = 0; q < 2 * SECTORS; q++) v[j][q] = __ldg(table + 2 * SECTORS * loc + q);
         }

@@ -100,19 +100,26 @@ template <int KCAP, class HitT, bool COUNT>
 static void launch_search_k(const IndexView& v, const uint64_t* packed, const uint64_t* offsets, uint64_t n_reads,
                             const uint64_t* out_offsets, HitPair<HitT>* o, SearchTotals* totals, int n_strands, cudaStream_t st) {
     const int threads = FIN_SEARCH_THREADS;
+#ifdef FIN_DQ_SHARED
+    const size_t dq_smem = KCAP == 32 ? (size_t)threads * KCAP * sizeof(uint64_t) : 0;  // the candidate rings
+#else
+    const size_t dq_smem = 0;
+#endif
     static thread_local int resident[64] = {0};  // per device
     int dev = 0;
     FIN_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) throw arg_error("CUDA device ordinal out of range");
     if (!resident[dev]) {
         int per_sm = 0, sms = 0;
-        FIN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, search_reads_kernel<KCAP, HitT, COUNT>, threads, 0));
+        if (dq_smem > 48 * 1024)
+            FIN_CUDA(cudaFuncSetAttribute(search_reads_kernel<KCAP, HitT, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dq_smem));
+        FIN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, search_reads_kernel<KCAP, HitT, COUNT>, threads, dq_smem));
         FIN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         resident[dev] = std::max(1, per_sm) * std::max(1, sms);
     }
     const uint64_t need = (n_reads + threads - 1) / threads;
     const unsigned blocks = (unsigned)std::min<uint64_t>(need, (uint64_t)resident[dev]);
-    search_reads_kernel<KCAP, HitT, COUNT><<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands);
+    search_reads_kernel<KCAP, HitT, COUNT><<<blocks, threads, dq_smem, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands);
     g_launches++;
     FIN_CUDA(cudaGetLastError());
 }

@@ -205,8 +205,20 @@ constexpr int kMaxReadLen = (1 << 24) - 1;
 
 enum : int { ST_EXT = 0, ST_EXTK = 1, ST_POST = 2, ST_SHRINK = 3, ST_EMIT = 4, ST_IDLE = 5 };
 
+// FIN_DQ_SHARED: for k <= 32 the candidate ring lives in shared memory, slot i of thread t at [i * blockDim + t] (no bank
+// conflicts when the lanes touch the same slot); otherwise it is a thread-local array (stride 1).
+#if defined(FIN_DQ_SHARED) && !defined(FIN_EMU)
+#define FIN_DQ_STRIDE(KCAP) ((KCAP) == 32 ? FIN_SEARCH_THREADS : 1)
+#else
+#define FIN_DQ_STRIDE(KCAP) 1
+#endif
+#ifndef FIN_SEARCH_THREADS
+#define FIN_SEARCH_THREADS 128
+#endif
+
 template <int KCAP, class HitT, bool COUNT> struct Chain {
     static constexpr bool WIDE = KCAP > 128;
+    static constexpr int DQS = FIN_DQ_STRIDE(KCAP);
     // the read
     uint64_t b0 = 0;
     HitPair<HitT>* o = nullptr;
@@ -360,11 +372,11 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         const idx_t il = I.l, ir = I.r + 1, kl = Ik.l, kr = Ik.r + 1;
         uint32_t uw = 0;
         uint64_t w_il = 0, w_ir = 0, w_kl = 0, w_kr = 0;
-        if (single) uw = __ldg(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
-        if (pendI & kDropLeft) w_il = __ldg(lw + lcs_word_index(il));
-        if (pendI & kDropRight) w_ir = __ldg(lw + lcs_word_index(ir));
-        if (pendK & kDropLeft) w_kl = __ldg(lw + lcs_word_index(kl));
-        if (pendK & kDropRight) w_kr = __ldg(lw + lcs_word_index(kr));
+        if (single) uw = ldg_line_u32(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
+        if (pendI & kDropLeft) w_il = ldg_line_u64(lw + lcs_word_index(il));
+        if (pendI & kDropRight) w_ir = ldg_line_u64(lw + lcs_word_index(ir));
+        if (pendK & kDropLeft) w_kl = ldg_line_u64(lw + lcs_word_index(kl));
+        if (pendK & kDropRight) w_kr = ldg_line_u64(lw + lcs_word_index(kr));
         if (single) {
             if (COUNT) rc.c_ustart++;
             if ((uw >> (ucol & 31)) & 1u) {
@@ -412,20 +424,20 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
             // back live in registers, so only a pop touches the slots.
             while (dq_n > 0 && bk > cur) {
                 dq_n--;
-                if (dq_n > 0) bk = dq[(dq_head + dq_n - 1) & (KCAP - 1)];
+                if (dq_n > 0) bk = dq[((dq_head + dq_n - 1) & (KCAP - 1)) * DQS];
             }
             if (dq_n == KCAP) {  // only entries that left the window can fill the ring: expire them now
                 while (dq_n > 0 && cand_start(fr) < kmer_start) {
                     dq_head = (dq_head + 1) & (KCAP - 1);
                     dq_n--;
-                    if (dq_n > 0) fr = dq[dq_head];
+                    if (dq_n > 0) fr = dq[dq_head * DQS];
                 }
                 if (dq_n == KCAP) {  // cannot happen for live entries; keeps memory safe out of domain
                     rc.err |= kErrWindowUnderflow;
                     dq_n--;
                 }
             }
-            dq[(dq_head + dq_n) & (KCAP - 1)] = cur;
+            dq[((dq_head + dq_n) & (KCAP - 1)) * DQS] = cur;
             dq_n++;
             bk = cur;
             if (dq_n == 1) fr = cur;
@@ -444,7 +456,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         while (dq_n > 0 && cand_start(fr) < kmer_start) {
             dq_head = (dq_head + 1) & (KCAP - 1);
             dq_n--;
-            if (dq_n > 0) fr = dq[dq_head];
+            if (dq_n > 0) fr = dq[dq_head * DQS];
         }
         if (emit) {
             present = true;
@@ -559,7 +571,13 @@ __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) sea
     const unsigned full = 0xFFFFFFFFu;
     const unsigned lane = threadIdx.x & 31u;
     Chain<KCAP, HitT, COUNT> ch;
+#if defined(FIN_DQ_SHARED)
+    extern __shared__ uint64_t dq_shared[];
+    uint64_t dq_local[KCAP == 32 ? 1 : KCAP];
+    uint64_t* dq = KCAP == 32 ? dq_shared + threadIdx.x : dq_local;
+#else
     uint64_t dq[KCAP];
+#endif
     ReadCounters rc;
     bool dry = false;  // the counter ran past the last read
     while (true) {
