@@ -111,6 +111,9 @@ static void launch_search_k(const IndexView& v, const uint64_t* packed, const ui
     if (dev < 0 || dev >= 64) throw arg_error("CUDA device ordinal out of range");
     if (!resident[dev]) {
         int per_sm = 0, sms = 0;
+        if (dq_smem == 0)  // no shared memory: all of the unified L1/shared array as L1 (the index lines live there)
+            FIN_CUDA(cudaFuncSetAttribute(search_reads_kernel<KCAP, HitT, COUNT>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                          (int)cudaSharedmemCarveoutMaxL1));
         if (dq_smem > 48 * 1024)
             FIN_CUDA(cudaFuncSetAttribute(search_reads_kernel<KCAP, HitT, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dq_smem));
         FIN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, search_reads_kernel<KCAP, HitT, COUNT>, threads, dq_smem));

@@ -169,6 +169,21 @@ FIN_D Ival drop_first_char(const IndexView& ix, const int new_len, Ival I, unsig
 
 template <class HitT> struct alignas(2 * sizeof(HitT)) HitPair { HitT unitig, pos; };
 
+// Hits are written once and never read again by the kernel (except the reverse strand's look at its own read's slots):
+// with FIN_STREAM_STORES they are stored evict-first so that 8 bytes per k-mer of output do not push the index out of the L2.
+template <class HitT> FIN_D void store_hit(HitPair<HitT>* dst, const HitPair<HitT> h) {
+#if defined(FIN_STREAM_STORES) && !defined(FIN_EMU)
+    if (sizeof(HitT) == 4) {
+        __stcs(reinterpret_cast<int2*>(dst), make_int2((int)h.unitig, (int)h.pos));
+    } else {
+        __stcs(reinterpret_cast<long long*>(dst), (long long)h.unitig);
+        __stcs(reinterpret_cast<long long*>(dst) + 1, (long long)h.pos);
+    }
+#else
+    *dst = h;
+#endif
+}
+
 // Candidate finimizers are packed into one u64 so that the unsigned order equals the reference's tuple
 // order (freq, len, colex, end) with freq == 1 throughout (common.hh:84,147): len:8 | colex:32 | end:24.
 FIN_D uint64_t cand_pack(int len, idx_t colex, int end) {
@@ -259,7 +274,12 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
     // 2-bit code of the character at `end` of the current strand (reverse complement: read backwards, complemented)
     FIN_D void fetch_base(const uint64_t* __restrict__ packed) {
         const uint64_t b = b0 + (uint64_t)(strand ? len - 1 - end : end);
+#if defined(FIN_BASES_NO_L1) && !defined(FIN_EMU)
+        uint32_t w;  // streamed once: do not spend L1 lines on the reads, the index lines live there
+        asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(w) : "l"(reinterpret_cast<const uint32_t*>(packed) + (b >> 4)));
+#else
         const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(packed) + (b >> 4));
+#endif
         c = (int)((w >> (2 * (b & 15))) & 3u) ^ (strand ? 3 : 0);
     }
 
@@ -426,6 +446,11 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                 dq_n--;
                 if (dq_n > 0) bk = dq[((dq_head + dq_n - 1) & (KCAP - 1)) * DQS];
             }
+#ifndef FIN_DQ_NO_RESET
+            // an empty ring restarts at slot 0: the live entries then stay in the first few slots instead of rotating
+            // through all KCAP of them, which keeps the thread-local footprint (and its share of the L1) small
+            if (dq_n == 0) dq_head = 0;
+#endif
             if (dq_n == KCAP) {  // only entries that left the window can fill the ring: expire them now
                 while (dq_n > 0 && cand_start(fr) < kmer_start) {
                     dq_head = (dq_head + 1) & (KCAP - 1);
@@ -458,6 +483,9 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
             dq_n--;
             if (dq_n > 0) fr = dq[dq_head * DQS];
         }
+#ifndef FIN_DQ_NO_RESET
+        if (dq_n == 0) dq_head = 0;
+#endif
         if (emit) {
             present = true;
             if (dq_n > 0) {
@@ -524,7 +552,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                 HitPair<HitT> h;
                 h.unitig = hit ? (HitT)walk_uid : (HitT)-1;
                 h.pos = hit ? (HitT)(walk_g - (idx_t)(k - 1) - walk_ustart) : (HitT)-1;
-                o[j] = h;
+                store_hit(o + j, h);
                 if (hit) {
                     rc.found[0]++;
                     rc.positive++;
@@ -536,7 +564,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                     HitPair<HitT> h;
                     h.unitig = (HitT)walk_uid;
                     h.pos = (HitT)(walk_g - (idx_t)(k - 1) - walk_ustart);
-                    o[i] = h;
+                    store_hit(o + i, h);
                     rc.positive++;
                 }
             }
