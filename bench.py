@@ -348,6 +348,15 @@ def main():
         _, c_e2e = ix.search_batch((h_seqs_np, offs), hit_bits=32, out=h_out_np)
         e2e_times.append(time.perf_counter() - t1)
     barrier()
+    # context for the end-to-end figure: what the host link gives for the same result buffer in one plain copy
+    link = []
+    for _ in range(2):
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        h_out.copy_(d_out, non_blocking=True)
+        torch.cuda.synchronize()
+        link.append(h_out.numel() * 4 / (time.perf_counter() - t1) / 1e9)
+    d2h_link_gbs = max(link)
     clocks = None
     sampler.stop_flag.set()
     sampler.join(timeout=3)
@@ -421,7 +430,9 @@ def main():
                        "index_build_s": build_s},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n_bases + 8 * (n_reads + 1)),
                     "d2h_bytes_per_step": int(kmers_per_step * 8), "ms_per_step": e2e_total / args.steps * 1e3,
-                    "api": "fin_search_batch32 (pinned host buffers, 3-stream sub-batch pipeline)"},
+                    "api": "fin_search_batch32 (pinned host buffers, 3-stream sub-batch pipeline)",
+                    "d2h_link_gbs": d2h_link_gbs, "d2h_floor_ms_per_step": kmers_per_step * 8 / d2h_link_gbs / 1e6,
+                    "note": "the hits (8 B per k-mer) leave over PCIe: the step cannot be shorter than d2h_floor_ms_per_step on this host"},
             "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "build": build,
             "wall_s_device_arm": wall_dev,
         }

@@ -133,13 +133,31 @@ static DevBuf<uint8_t> lcs_bytes_from_packed(const PackedVec& lcs, uint64_t nw) 
     return bytes;
 }
 
-// the 128-byte lines (device_index.cuh) from the rows and the LCS bytes, Ustart / fmin bits left zero
-static DevBuf<uint64_t> make_lines_device(const DeviceSbwt& d, const uint8_t* d_lcs_bytes) {
+// the 128-byte lines (device_index.cuh) from the rows and the LCS bytes; Ustart / fmin words (device) or null
+static DevBuf<uint64_t> make_lines_device(const DeviceSbwt& d, const uint8_t* d_lcs_bytes, const uint64_t* d_ustart = nullptr,
+                                          const uint64_t* d_fmin = nullptr) {
     const uint64_t n_lines = (d.N >> 6) + 2;
     DevBuf<uint64_t> lines(n_lines * 16);
-    make_lines_kernel<<<(unsigned)((n_lines + 127) / 128), 128>>>(d.args, d_lcs_bytes, n_lines, reinterpret_cast<uint4*>(lines.p));
+    make_lines_kernel<<<(unsigned)((n_lines + 127) / 128), 128>>>(d.args, d_lcs_bytes, d_ustart, d_fmin, n_lines,
+                                                                  reinterpret_cast<uint4*>(lines.p));
     g_launches++;
     FIN_CUDA(cudaGetLastError());
+    return lines;
+}
+
+// FinimizerIndex::load: the lines of a complete index, laid out on the device (the host only reads the files)
+DevBuf<uint64_t> index_lines_device(const IndexHost& h) {
+    const uint64_t N = (uint64_t)h.sbwt.n_nodes;
+    if (N >= kIndexLimit32) throw limit_error("index too large for the 32-bit column/text positions of this build");
+    if (N < 2) throw domain_error("SBWT with fewer than 2 columns");
+    const DeviceSbwt ds = upload_sbwt(h.sbwt);
+    DevBuf<uint8_t> lcs = lcs_bytes_from_packed(h.lcs, ds.nw);
+    if (h.ustart.words.size() < ds.nw || h.fmin.words.size() < ds.nw) throw format_error("Ustart / fmin bit vectors shorter than the SBWT");
+    DevBuf<uint64_t> us(ds.nw), fm(ds.nw);
+    FIN_CUDA(cudaMemcpy(us.p, h.ustart.words.data(), ds.nw * 8, cudaMemcpyHostToDevice));
+    FIN_CUDA(cudaMemcpy(fm.p, h.fmin.words.data(), ds.nw * 8, cudaMemcpyHostToDevice));
+    DevBuf<uint64_t> lines = make_lines_device(ds, lcs.p, us.p, fm.p);
+    FIN_CUDA(cudaDeviceSynchronize());
     return lines;
 }
 

@@ -408,11 +408,15 @@ static __global__ void mask_row_tails_kernel(uint64_t* __restrict__ rows, uint64
     if (c < 4 && (n & 63)) rows[(uint64_t)c * n_words + n_words - 1] &= (1ULL << (n & 63)) - 1ULL;
 }
 
-// the lines of device_index.cuh without Ustart / fmin bits (build-fmin streams before they exist): one thread per line
-static __global__ void make_lines_kernel(const LcsArgs a, const uint8_t* __restrict__ lcs_bytes, uint64_t n_lines, uint4* __restrict__ lines) {
+// the lines of device_index.cuh: one thread per line.  ustart / fmin = the words of those bit vectors, or null
+// (build-fmin streams before they exist): zeros then.
+static __global__ void make_lines_kernel(const LcsArgs a, const uint8_t* __restrict__ lcs_bytes, const uint64_t* __restrict__ ustart,
+                                         const uint64_t* __restrict__ fmin, uint64_t n_lines, uint4* __restrict__ lines) {
     const uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= n_lines) return;
     uint4* line = lines + b * 8;
+    const uint64_t us = ustart && b < a.n_words ? ustart[b] : 0, fm = fmin && b < a.n_words ? fmin[b] : 0;
+    const uint32_t extra[4] = {(uint32_t)us, (uint32_t)(us >> 32), (uint32_t)fm, (uint32_t)(fm >> 32)};
 #pragma unroll
     for (int c = 0; c < 4; c++) {
         uint64_t bits = 0;
@@ -424,7 +428,7 @@ static __global__ void make_lines_kernel(const LcsArgs a, const uint8_t* __restr
             cum = a.C[c] + a.word_dst[(uint64_t)c * a.n_words + a.n_words - 1] +
                   (uint32_t)__popcll(a.rows[(uint64_t)c * a.n_words + a.n_words - 1]);
         }
-        line[c] = make_uint4((uint32_t)bits, (uint32_t)(bits >> 32), cum, 0u);
+        line[c] = make_uint4((uint32_t)bits, (uint32_t)(bits >> 32), cum, extra[c]);
     }
     // lcs_bytes is padded with zeros to 64 * n_words + 64 bytes
     const uint4* src = reinterpret_cast<const uint4*>(lcs_bytes + b * 64);

@@ -89,6 +89,7 @@ std::string build_fmin_device(const std::string& sbwt_path, const std::string& u
                               const std::string& type, int64_t t, const std::string& lcs_path, int device);
 std::vector<uint8_t> lcs_device(const SbwtHost& sbwt, int device);
 fin_build_timing last_build_timing();
+DevBuf<uint64_t> index_lines_device(const IndexHost& h);  // build.cu: the 128-byte lines of a loaded index, built on the device
 double probe_random_sectors(int device, uint64_t table_bytes, int repeats, int bytes_per_access);  // probe.cu
 
 // staged build-fmin --type rarest, shardable over GPUs (build.cu)

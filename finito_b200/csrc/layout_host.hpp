@@ -115,7 +115,7 @@ struct HostLayout {
     int64_t k = 0, n_kmers = 0;
 };
 
-inline HostLayout build_host_layout(const IndexHost& h) {
+inline HostLayout build_host_layout(const IndexHost& h, bool with_lines = true) {
     HostLayout L;
     const uint64_t N = (uint64_t)h.sbwt.n_nodes, T = h.text.size(), U = h.ends.size(), F = h.offsets.size();
     if (N >= kIndexLimit32 || T >= kIndexLimit32)
@@ -125,7 +125,7 @@ inline HostLayout build_host_layout(const IndexHost& h) {
     L.n_nodes = N; L.text_len = T; L.n_unitigs = U; L.n_fmin = F;
     L.k = h.sbwt.k; L.n_kmers = h.sbwt.n_kmers;
     for (int c = 0; c < 4; c++) L.C[c] = h.sbwt.C[c];
-    L.lines = make_lines(h.sbwt, &h.lcs, &h.ustart, &h.fmin);
+    if (with_lines) L.lines = make_lines(h.sbwt, &h.lcs, &h.ustart, &h.fmin);  // the device path builds them with make_lines_kernel
     {
         const uint64_t* r[1] = {h.ustart.words.data()};
         L.ustart = make_rank_sectors(r, 1, N);

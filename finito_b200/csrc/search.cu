@@ -49,8 +49,8 @@ DeviceIndex::DeviceIndex(const IndexHost& h, int device) : device_(device) {
     if (device < 0 || device >= n_dev) throw arg_error("CUDA device ordinal out of range");
     FIN_CUDA(cudaSetDevice(device));
 
-    const HostLayout L = build_host_layout(h);
-    lines_ = upload(L.lines.data(), L.lines.size());
+    const HostLayout L = build_host_layout(h, false);
+    lines_ = index_lines_device(h);
     ustart_ = upload(L.ustart.data(), L.ustart.size());
     fmin_ = upload(L.fmin.data(), L.fmin.size());
     tstart_ = upload(L.tstart.data(), L.tstart.size());

@@ -1,0 +1,83 @@
+"""The finito_b200 CLI (finito_b200/csrc/cli_main.cpp) as a drop-in for the reference's `build-fmin` / `search-fmin`
+(src/main.cpp:13-59): same command lines, same files, same text.  CPU part: usage and error behaviour.  GPU part: run
+side by side with the UNMODIFIED reference binary (oracle/_ref/finito_ref, prebuilt, travels to the GPU box) on
+BASELINE.json configs[1]-shaped input and compare every output byte."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import finito_b200 as fb
+import helpers as H
+from datasets import make_dataset
+
+CLI = fb.CLI_PATH
+
+
+def run(*args, cwd=None):
+    return subprocess.run([CLI, *args], cwd=cwd, capture_output=True, text=True)
+
+
+def test_usage_and_exit_codes_like_the_reference():
+    r = run()
+    assert r.returncode == 1 and "Available commands" in r.stderr and "build-fmin" in r.stderr  # src/main.cpp:21-31
+    for cmd in ("build-fmin", "search-fmin"):
+        r = run(cmd)
+        assert r.returncode == 1 and "Usage:" in r.stderr and r.stdout == ""  # search_fmin.hh:148-151, build_fmin.hh:327-330
+        assert run(cmd, "-h").returncode == 1
+    r = run("nonsense")
+    assert r.returncode == 1 and "Invalid command: nonsense" in r.stderr  # src/main.cpp:49-57
+    if H.have_ref():
+        ref = H.ref_run()
+        assert "Available commands" in ref.stderr and ref.returncode == 1
+
+
+def test_unreadable_inputs_fail_cleanly(tmp_path):
+    d = os.path.join(H.GOLDEN, "syn_k31")
+    r = run("build-fmin", "-o", str(tmp_path / "x"), "-i", "/nonexistent.sbwt", "-u", os.path.join(d, "unitigs.fna"))
+    assert r.returncode == 1 and not os.path.exists(tmp_path / "x.FBV.sdsl")
+    r = run("search-fmin", "-i", os.path.join(d, "ref"), "-q", "/nonexistent.fna")
+    assert r.returncode == 1 and r.stdout == ""
+
+
+def write_fasta(path, seqs, offs, n):
+    with open(path, "wb") as f:
+        raw = seqs.tobytes()
+        for i in range(n):
+            f.write(b">r%d\n" % i)
+            f.write(raw[int(offs[i]):int(offs[i + 1])])
+            f.write(b"\n")
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not H.have_ref(), reason="needs the prebuilt reference binary oracle/_ref/finito_ref")
+@pytest.mark.parametrize("k,genome_len,n_reads", [(31, 2_000_000, 20_000), (63, 500_000, 5_000)])
+def test_cli_is_byte_identical_to_the_reference_binary(k, genome_len, n_reads, tmp_path):
+    ds = make_dataset("cli", genome_len=genome_len, k=k, n_reads=n_reads, read_len=150, seed=77 + k)
+    seqs, offs = ds["reads"]
+    q = str(tmp_path / "reads.fna")
+    write_fasta(q, seqs, offs, n_reads)
+    ours, ref = str(tmp_path / "ours"), str(tmp_path / "ref")
+    r = run("build-fmin", "-o", ours, "-i", ds["sbwt"], "-u", ds["unitigs"])
+    assert r.returncode == 0, r.stderr[-500:]
+    assert r.stdout == "String appended to the file successfully.\n"  # build_fmin.hh:396
+    rr = H.ref_run("build-fmin", "-o", ref, "-i", ds["sbwt"], "-u", ds["unitigs"])
+    assert rr.returncode == 0, rr.stderr[-500:]
+    for suf in H.INDEX_SUFFIXES + ["_stats.txt"]:
+        assert H.files_equal(ours + suf, ref + suf), suf
+    # each binary searches the OTHER one's index: the files are interchangeable
+    r = run("search-fmin", "-i", ref, "-q", q, "-o", ours + ".out")
+    assert r.returncode == 0, r.stderr[-500:]
+    rr = H.ref_run("search-fmin", "-i", ours, "-q", q, "-o", ref + ".out")
+    assert rr.returncode == 0, rr.stderr[-500:]
+    assert H.files_equal(ours + ".out", ref + ".out")
+    # stdout mode
+    r = subprocess.run([CLI, "search-fmin", "-i", ours, "-q", q], capture_output=True)
+    assert r.returncode == 0 and r.stdout == open(ref + ".out", "rb").read()
+    # stats modes print the same line
+    for typ, t in (("shortest", 4),):  # verify is O(k^2) per window in the reference: covered by golden/stats_modes.json
+        a = run("build-fmin", "-o", ours + typ, "-i", ds["sbwt"], "-u", ds["unitigs"], "--type", typ, "-t", str(t), "--lcs", ours + ".LCS.sdsl")
+        b = H.ref_run("build-fmin", "-o", ref + typ, "-i", ds["sbwt"], "-u", ds["unitigs"], "--type", typ, "-t", str(t), "--lcs", ours + ".LCS.sdsl")
+        assert a.returncode == 0 and b.returncode == 0, (a.stderr[-300:], b.stderr[-300:])
+        assert open(ours + typ + "_stats.txt").read() == open(ref + typ + "_stats.txt").read(), typ
