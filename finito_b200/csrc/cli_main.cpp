@@ -2,8 +2,10 @@
 // (src/main.cpp:21-59, include/build_fmin.hh:302-401, include/search_fmin.hh:130-212): same flags, same files,
 // same text output.  Host code only: parsing, batching and text formatting; all computation goes through the
 // C ABI of libfinito_b200.so (include/finito_b200.h) to the GPU.
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <iostream>
 #include <map>
@@ -158,7 +160,7 @@ struct QueryTotals {
     int64_t found_fwd = 0, found_rc = 0, positive = 0, n_queries = 0;
 };
 
-void run_query_file(fin_index* index, int64_t k, const std::string& infile, FILE* out, QueryTotals& tot) {
+void run_query_file(const std::vector<fin_index*>& indexes, int64_t k, const std::string& infile, FILE* out, QueryTotals& tot) {
     log_line("Running streaming queries from input file " + infile);
     fin::SeqBatch all;
     fin::append_sequences(infile, all);
@@ -175,12 +177,35 @@ void run_query_file(fin_index* index, int64_t k, const std::string& infile, FILE
         for (uint64_t i = r0; i <= r1; i++) offs[i - r0] = all.offsets[i] - all.offsets[r0];
         const uint64_t n_hits = fin_count_kmers(offs.data(), r1 - r0, k);
         hits.resize(std::max<uint64_t>(1, n_hits) * 2);
-        fin_search_counts c{};
-        check(fin_search_batch(index, all.seqs.data() + all.offsets[r0], offs.data(), r1 - r0, hits.data(), n_hits, &c));
-        tot.found_fwd += c.found_fwd;
-        tot.found_rc += c.found_rc;
-        tot.positive += c.positive;
-        tot.n_queries += c.n_queries;
+        // reads are independent (search_fmin.hh:43): the batch is cut into one contiguous block per GPU, every GPU holds
+        // the whole index, one host thread drives each handle; the hits land in disjoint ranges of the same buffer
+        const size_t n_dev = std::max<size_t>(1, std::min<size_t>(indexes.size(), (size_t)(r1 - r0)));
+        std::vector<fin_search_counts> cs(n_dev);
+        std::vector<std::string> errors(n_dev);
+        std::vector<std::thread> gpu_threads;
+        const uint64_t nb_reads = r1 - r0;
+        for (size_t d = 0; d < n_dev; d++) {
+            const uint64_t a = nb_reads * d / n_dev, b = nb_reads * (d + 1) / n_dev;
+            const uint64_t hit_a = fin_count_kmers(offs.data(), a, k), hit_n = fin_count_kmers(offs.data() + a, b - a, k);
+            auto work = [&, d, a, b, hit_a, hit_n] {
+                std::vector<uint64_t> sub(offs.begin() + (long)a, offs.begin() + (long)b + 1);
+                for (uint64_t& o : sub) o -= offs[a];
+                cs[d] = fin_search_counts{};
+                if (fin_search_batch(indexes[d], all.seqs.data() + all.offsets[r0] + offs[a], sub.data(), b - a, hits.data() + 2 * hit_a,
+                                     hit_n, &cs[d]) != FIN_OK)
+                    errors[d] = fin_last_error();  // thread-local message: read it on this thread
+            };
+            if (n_dev == 1) work();
+            else gpu_threads.emplace_back(work);
+        }
+        for (auto& t : gpu_threads) t.join();
+        for (size_t d = 0; d < n_dev; d++) {
+            if (!errors[d].empty()) throw std::runtime_error(errors[d]);
+            tot.found_fwd += cs[d].found_fwd;
+            tot.found_rc += cs[d].found_rc;
+            tot.positive += cs[d].positive;
+            tot.n_queries += cs[d].n_queries;
+        }
         // text formatting on all host cores, written in read order
         const uint64_t nr = r1 - r0, per = (nr + n_threads - 1) / n_threads;
         std::vector<uint64_t> hit_start(n_threads + 1, 0);
@@ -230,9 +255,21 @@ int search_fmin_command(int argc, char** argv) {
     }
     const std::string prefix = opts.get("index-file");
     std::cerr << "Loading index..." << std::endl;
-    fin_index* index = nullptr;
-    check(fin_index_load(prefix.c_str(), 0, &index));
-    std::cerr << "Index loaded" << std::endl;
+    // FIN_DEVICES = number of GPUs to shard the reads over (default: all visible ones)
+    int n_devices = std::max(1, fin_device_count());
+    if (const char* e = std::getenv("FIN_DEVICES")) n_devices = std::max(1, std::min(n_devices, std::atoi(e)));
+    std::vector<fin_index*> indexes((size_t)n_devices, nullptr);
+    auto free_all = [&] {
+        for (fin_index* ix : indexes) fin_index_free(ix);
+    };
+    try {
+        for (int d = 0; d < n_devices; d++) check(fin_index_load(prefix.c_str(), d, &indexes[(size_t)d]));
+    } catch (...) {
+        free_all();
+        throw;
+    }
+    fin_index* index = indexes[0];
+    std::cerr << "Index loaded" << (n_devices > 1 ? " on " + std::to_string(n_devices) + " GPUs" : std::string()) << std::endl;
     fin_index_info info{};
     check(fin_index_info_get(index, &info));
     std::cerr << "k = " << info.k << " SBWT nodes: " << info.n_nodes << " kmers: " << info.n_kmers << std::endl;
@@ -244,10 +281,10 @@ int search_fmin_command(int argc, char** argv) {
         QueryTotals tot;
         const int64_t t0 = now_micros();
         try {
-            run_query_file(index, info.k, query_files[i], out, tot);
+            run_query_file(indexes, info.k, query_files[i], out, tot);
         } catch (...) {
             if (!to_stdout) std::fclose(out);
-            fin_index_free(index);
+            free_all();
             throw;
         }
         if (!to_stdout) std::fclose(out);
@@ -279,7 +316,7 @@ int search_fmin_command(int argc, char** argv) {
         std::fclose(sf2);
     }
     log_line("bytes: " + std::to_string(info.device_bytes));
-    fin_index_free(index);
+    free_all();
     return 0;
 }
 

@@ -256,13 +256,22 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
     uint32_t walk_uid = 0;
     uint64_t tword = 0;
     int walk_j = 0;
+#ifdef FIN_BASE_WORD_CACHE
+    uint32_t bw = 0;          // the 16 packed bases around the current position
+#endif
     uint64_t fr = 0, bk = 0;  // front and back of the candidate window, cached in registers
+#ifdef FIN_BK2
+    uint64_t bk2 = 0;         // the entry below the back, or 0 when not cached
+#endif
 
     FIN_D void begin_strand(const IndexView& ix, const uint64_t* __restrict__ packed) {
         start = kmer_start = 0;
         I.l = 0; I.r = ix.n_nodes - 1;
         Ik = I;
         dq_head = dq_n = 0;
+#ifdef FIN_BK2
+        bk2 = 0;
+#endif
         bestU_pos = -1;
         walking = false;
         pendI = pendK = 0;
@@ -278,7 +287,13 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
         uint32_t w;  // streamed once: do not spend L1 lines on the reads, the index lines live there
         asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(w) : "l"(reinterpret_cast<const uint32_t*>(packed) + (b >> 4)));
 #else
+#ifdef FIN_BASE_WORD_CACHE
+        // 16 bases per 32-bit word: reload only when the position enters a new word (or a strand begins)
+        if (end == 0 || (b & 15) == (strand ? 15u : 0u)) bw = __ldg(reinterpret_cast<const uint32_t*>(packed) + (b >> 4));
+        const uint32_t w = bw;
+#else
         const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(packed) + (b >> 4));
+#endif
 #endif
         c = (int)((w >> (2 * (b & 15))) & 3u) ^ (strand ? 3 : 0);
     }
@@ -442,6 +457,18 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         } else {
             // monotone window: drop the candidates that are larger than the new one, then append it.  Front and
             // back live in registers, so only a pop touches the slots.
+#ifdef FIN_BK2
+            // the entry below the back is usually known (it was the back before the last push): the first pop then
+            // needs no load from the ring.  bk2 == 0 means "not cached" (a candidate is never 0: its length is >= 1).
+            if (dq_n > 0 && bk > cur) {
+                dq_n--;
+                if (dq_n > 0) {
+                    if (bk2 == 0) bk2 = dq[((dq_head + dq_n - 1) & (KCAP - 1)) * DQS];
+                    bk = bk2;
+                }
+                bk2 = 0;
+            }
+#endif
             while (dq_n > 0 && bk > cur) {
                 dq_n--;
                 if (dq_n > 0) bk = dq[((dq_head + dq_n - 1) & (KCAP - 1)) * DQS];
@@ -460,9 +487,13 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                 if (dq_n == KCAP) {  // cannot happen for live entries; keeps memory safe out of domain
                     rc.err |= kErrWindowUnderflow;
                     dq_n--;
+                    bk = 0;
                 }
             }
             dq[((dq_head + dq_n) & (KCAP - 1)) * DQS] = cur;
+#ifdef FIN_BK2
+            bk2 = dq_n > 0 ? bk : 0;
+#endif
             dq_n++;
             bk = cur;
             if (dq_n == 1) fr = cur;
@@ -485,6 +516,9 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         }
 #ifndef FIN_DQ_NO_RESET
         if (dq_n == 0) dq_head = 0;
+#endif
+#ifdef FIN_BK2
+        if (dq_n < 2) bk2 = 0;
 #endif
         if (emit) {
             present = true;

@@ -81,3 +81,26 @@ def test_cli_is_byte_identical_to_the_reference_binary(k, genome_len, n_reads, t
         b = H.ref_run("build-fmin", "-o", ref + typ, "-i", ds["sbwt"], "-u", ds["unitigs"], "--type", typ, "-t", str(t), "--lcs", ours + ".LCS.sdsl")
         assert a.returncode == 0 and b.returncode == 0, (a.stderr[-300:], b.stderr[-300:])
         assert open(ours + typ + "_stats.txt").read() == open(ref + typ + "_stats.txt").read(), typ
+
+
+@pytest.mark.gpu
+def test_cli_search_sharded_over_all_gpus_prints_the_same(tmp_path):
+    """search-fmin cuts every batch into one block of reads per visible GPU (FIN_DEVICES caps it): same bytes out."""
+    if fb.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    ds = make_dataset("cli", genome_len=2_000_000, k=31, n_reads=20_000, read_len=150, seed=108)
+    seqs, offs = ds["reads"]
+    q = str(tmp_path / "reads.fna")
+    write_fasta(q, seqs, offs, 20_000)
+    prefix = str(tmp_path / "ix")
+    assert run("build-fmin", "-o", prefix, "-i", ds["sbwt"], "-u", ds["unitigs"]).returncode == 0
+    outs = []
+    for n in ("1", str(fb.device_count())):
+        o = str(tmp_path / f"out{n}.txt")
+        r = subprocess.run([CLI, "search-fmin", "-i", prefix, "-q", q, "-o", o], capture_output=True, text=True,
+                           env=dict(os.environ, FIN_DEVICES=n))
+        assert r.returncode == 0, r.stderr[-400:]
+        if n != "1":
+            assert f"on {n} GPUs" in r.stderr
+        outs.append(open(o, "rb").read())
+    assert outs[0] == outs[1] and len(outs[0]) > 0
