@@ -8,6 +8,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
+#include <condition_variable>
+#include <memory>
+#include <mutex>
 #include <map>
 #include <string>
 #include <thread>
@@ -131,52 +134,147 @@ inline char* put_int(char* p, int64_t v) {
     return p;
 }
 
-void format_reads(const int64_t* hits, const uint64_t* offsets, uint64_t r0, uint64_t r1, uint64_t hit0, int64_t k, std::string& out) {
+// Text of reads [r0, r1) of a batch into `out` (grown as needed, never zero-filled).  Worst case per hit: "(" + 20 + "," +
+// 20 + ")" + " " = 44 bytes; the bound actually used comes from the largest values the index can report.
+struct TextBuf {
+    std::unique_ptr<char[]> p;
+    size_t cap = 0, len = 0;
+    void reserve(size_t n) {
+        if (n > cap) {
+            p.reset(new char[n]);
+            cap = n;
+        }
+    }
+};
+
+template <class HitT>
+void format_reads(const HitT* hits, const uint64_t* offsets, uint64_t r0, uint64_t r1, uint64_t hit0, int64_t k, size_t bytes_per_hit,
+                  TextBuf& out) {
     uint64_t n_hits = 0;
     for (uint64_t r = r0; r < r1; r++) {
         const uint64_t len = offsets[r + 1] - offsets[r];
         if (len >= (uint64_t)k) n_hits += len - k + 1;
     }
-    out.resize(n_hits * 44 + (r1 - r0) + 16);
-    char* p = &out[0];
-    const int64_t* h = hits + 2 * hit0;
+    out.reserve(n_hits * bytes_per_hit + (r1 - r0) + 16);
+    char* p = out.p.get();
+    const HitT* h = hits + 2 * hit0;
     for (uint64_t r = r0; r < r1; r++) {
         const uint64_t len = offsets[r + 1] - offsets[r];
         const uint64_t n = len >= (uint64_t)k ? len - k + 1 : 0;
         for (uint64_t i = 0; i < n; i++, h += 2) {
             if (i) *p++ = ' ';
             *p++ = '(';
-            p = put_int(p, h[0]);
+            p = put_int(p, (int64_t)h[0]);
             *p++ = ',';
-            p = put_int(p, h[1]);
+            p = put_int(p, (int64_t)h[1]);
             *p++ = ')';
         }
         *p++ = '\n';
     }
-    out.resize((size_t)(p - out.data()));
+    out.len = (size_t)(p - out.p.get());
+}
+
+int decimal_digits(int64_t v) {
+    int n = 1;
+    while (v >= 10) {
+        v /= 10;
+        n++;
+    }
+    return n;
 }
 
 struct QueryTotals {
     int64_t found_fwd = 0, found_rc = 0, positive = 0, n_queries = 0;
 };
 
-void run_query_file(const std::vector<fin_index*>& indexes, int64_t k, const std::string& infile, FILE* out, QueryTotals& tot) {
-    log_line("Running streaming queries from input file " + infile);
-    fin::SeqBatch all;
-    fin::append_sequences(infile, all);
+// run_fmin_queries_streaming (search_fmin.hh:33-84) as a two-stage pipeline: the main thread searches batch i+1 on the
+// GPU(s) while a writer thread formats batch i on all host cores and writes it, in read order.  Hits travel as 2 x int32
+// whenever the index allows it, through pinned buffers.
+template <class HitT>
+void run_query_batches(const std::vector<fin_index*>& indexes, int64_t k, const fin::SeqBatch& all, FILE* out, QueryTotals& tot,
+                       size_t bytes_per_hit) {
     const uint64_t n = all.size();
-    const uint64_t max_reads = 1u << 21, max_bases = 512ull << 20;
+    const uint64_t max_reads = 1u << 19, max_bases = 128ull << 20;
     const unsigned n_threads = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
-    std::vector<int64_t> hits;
-    std::vector<uint64_t> offs;
-    std::vector<std::string> parts(n_threads);
+    // batch boundaries and the largest batch (sizes the two pinned hit buffers)
+    std::vector<uint64_t> cuts{0};
+    uint64_t max_hits = 1;
     for (uint64_t r0 = 0; r0 < n;) {
         uint64_t r1 = r0 + 1;
         while (r1 < n && r1 - r0 < max_reads && all.offsets[r1 + 1] - all.offsets[r0] <= max_bases) r1++;
-        offs.assign(r1 - r0 + 1, 0);
-        for (uint64_t i = r0; i <= r1; i++) offs[i - r0] = all.offsets[i] - all.offsets[r0];
-        const uint64_t n_hits = fin_count_kmers(offs.data(), r1 - r0, k);
-        hits.resize(std::max<uint64_t>(1, n_hits) * 2);
+        max_hits = std::max(max_hits, fin_count_kmers(all.offsets.data() + r0, r1 - r0, k));
+        cuts.push_back(r1);
+        r0 = r1;
+    }
+    struct Slot {
+        HitT* hits = nullptr;
+        std::vector<uint64_t> offs;
+        uint64_t n_hits = 0;
+        bool full = false;
+    } slots[2];
+    for (Slot& s : slots) {
+        void* p = nullptr;
+        check(fin_host_alloc(max_hits * 2 * sizeof(HitT), &p));
+        s.hits = static_cast<HitT*>(p);
+    }
+    std::mutex mu;
+    std::condition_variable cv;
+    bool done = false;
+    std::string writer_error;
+    int64_t us_format = 0, us_write = 0, us_search = 0, us_wait_slot = 0;
+
+    std::thread writer([&] {
+        std::vector<TextBuf> parts(n_threads);
+        for (size_t b = 0;; b++) {
+            Slot& s = slots[b & 1];
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return s.full || done; });
+                if (!s.full) return;
+            }
+            if (writer_error.empty()) {
+                const uint64_t nr = s.offs.size() - 1, per = (nr + n_threads - 1) / n_threads;
+                std::vector<uint64_t> hit_start(n_threads + 1, 0);
+                for (unsigned t = 0; t < n_threads; t++) {
+                    const uint64_t a = std::min<uint64_t>(nr, t * per), e = std::min<uint64_t>(nr, (t + 1) * per);
+                    hit_start[t + 1] = hit_start[t] + fin_count_kmers(s.offs.data() + a, e - a, k);
+                }
+                const int64_t t0 = now_micros();
+                std::vector<std::thread> workers;
+                for (unsigned t = 0; t < n_threads; t++) {
+                    const uint64_t a = std::min<uint64_t>(nr, t * per), e = std::min<uint64_t>(nr, (t + 1) * per);
+                    workers.emplace_back([&, t, a, e] { format_reads<HitT>(s.hits, s.offs.data(), a, e, hit_start[t], k, bytes_per_hit, parts[t]); });
+                }
+                for (auto& w : workers) w.join();
+                const int64_t t1 = now_micros();
+                for (unsigned t = 0; t < n_threads; t++)
+                    if (parts[t].len && std::fwrite(parts[t].p.get(), 1, parts[t].len, out) != parts[t].len)
+                        writer_error = "Error writing the output file";
+                us_format += t1 - t0;
+                us_write += now_micros() - t1;
+            }
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                s.full = false;
+            }
+            cv.notify_all();
+        }
+    });
+
+    std::string search_error;
+    for (size_t b = 0; b + 1 < cuts.size() && search_error.empty(); b++) {
+        const uint64_t r0 = cuts[b], r1 = cuts[b + 1];
+        Slot& s = slots[b & 1];
+        const int64_t tw = now_micros();
+        {
+            std::unique_lock<std::mutex> lk(mu);
+            cv.wait(lk, [&] { return !s.full; });
+        }
+        const int64_t ts = now_micros();
+        us_wait_slot += ts - tw;
+        s.offs.assign(r1 - r0 + 1, 0);
+        for (uint64_t i = r0; i <= r1; i++) s.offs[i - r0] = all.offsets[i] - all.offsets[r0];
+        s.n_hits = fin_count_kmers(s.offs.data(), r1 - r0, k);
         // reads are independent (search_fmin.hh:43): the batch is cut into one contiguous block per GPU, every GPU holds
         // the whole index, one host thread drives each handle; the hits land in disjoint ranges of the same buffer
         const size_t n_dev = std::max<size_t>(1, std::min<size_t>(indexes.size(), (size_t)(r1 - r0)));
@@ -185,45 +283,64 @@ void run_query_file(const std::vector<fin_index*>& indexes, int64_t k, const std
         std::vector<std::thread> gpu_threads;
         const uint64_t nb_reads = r1 - r0;
         for (size_t d = 0; d < n_dev; d++) {
-            const uint64_t a = nb_reads * d / n_dev, b = nb_reads * (d + 1) / n_dev;
-            const uint64_t hit_a = fin_count_kmers(offs.data(), a, k), hit_n = fin_count_kmers(offs.data() + a, b - a, k);
-            auto work = [&, d, a, b, hit_a, hit_n] {
-                std::vector<uint64_t> sub(offs.begin() + (long)a, offs.begin() + (long)b + 1);
-                for (uint64_t& o : sub) o -= offs[a];
+            const uint64_t a = nb_reads * d / n_dev, e = nb_reads * (d + 1) / n_dev;
+            const uint64_t hit_a = fin_count_kmers(s.offs.data(), a, k), hit_n = fin_count_kmers(s.offs.data() + a, e - a, k);
+            auto work = [&, d, a, e, hit_a, hit_n] {
+                std::vector<uint64_t> sub(s.offs.begin() + (long)a, s.offs.begin() + (long)e + 1);
+                for (uint64_t& o : sub) o -= s.offs[a];
                 cs[d] = fin_search_counts{};
-                if (fin_search_batch(indexes[d], all.seqs.data() + all.offsets[r0] + offs[a], sub.data(), b - a, hits.data() + 2 * hit_a,
-                                     hit_n, &cs[d]) != FIN_OK)
-                    errors[d] = fin_last_error();  // thread-local message: read it on this thread
+                const char* seqs = all.seqs.data() + all.offsets[r0] + s.offs[a];
+                fin_status st;
+                if (sizeof(HitT) == 4)
+                    st = fin_search_batch32(indexes[d], seqs, sub.data(), e - a, reinterpret_cast<int32_t*>(s.hits) + 2 * hit_a, hit_n, &cs[d]);
+                else
+                    st = fin_search_batch(indexes[d], seqs, sub.data(), e - a, reinterpret_cast<int64_t*>(s.hits) + 2 * hit_a, hit_n, &cs[d]);
+                if (st != FIN_OK) errors[d] = fin_last_error();  // thread-local message: read it on this thread
             };
             if (n_dev == 1) work();
             else gpu_threads.emplace_back(work);
         }
         for (auto& t : gpu_threads) t.join();
         for (size_t d = 0; d < n_dev; d++) {
-            if (!errors[d].empty()) throw std::runtime_error(errors[d]);
+            if (!errors[d].empty()) search_error = errors[d];
             tot.found_fwd += cs[d].found_fwd;
             tot.found_rc += cs[d].found_rc;
             tot.positive += cs[d].positive;
             tot.n_queries += cs[d].n_queries;
         }
-        // text formatting on all host cores, written in read order
-        const uint64_t nr = r1 - r0, per = (nr + n_threads - 1) / n_threads;
-        std::vector<uint64_t> hit_start(n_threads + 1, 0);
-        for (unsigned t = 0; t < n_threads; t++) {
-            const uint64_t a = std::min<uint64_t>(nr, t * per), b = std::min<uint64_t>(nr, (t + 1) * per);
-            hit_start[t + 1] = hit_start[t] + fin_count_kmers(offs.data() + a, b - a, k);
+        us_search += now_micros() - ts;
+        if (!search_error.empty()) break;
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            s.full = true;
         }
-        std::vector<std::thread> workers;
-        for (unsigned t = 0; t < n_threads; t++) {
-            const uint64_t a = std::min<uint64_t>(nr, t * per), b = std::min<uint64_t>(nr, (t + 1) * per);
-            workers.emplace_back([&, t, a, b] { format_reads(hits.data(), offs.data(), a, b, hit_start[t], k, parts[t]); });
-        }
-        for (auto& w : workers) w.join();
-        for (unsigned t = 0; t < n_threads; t++)
-            if (!parts[t].empty() && std::fwrite(parts[t].data(), 1, parts[t].size(), out) != parts[t].size())
-                throw std::runtime_error("Error writing the output file");
-        r0 = r1;
+        cv.notify_all();
     }
+    {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return (!slots[0].full && !slots[1].full) || !search_error.empty(); });
+        done = true;
+    }
+    cv.notify_all();
+    writer.join();
+    for (Slot& s : slots) fin_host_free(s.hits);
+    log_line("pipeline: GPU search " + std::to_string(us_search / 1000) + " ms, waiting for the writer " + std::to_string(us_wait_slot / 1000) +
+             " ms | writer: formatting " + std::to_string(us_format / 1000) + " ms, fwrite " + std::to_string(us_write / 1000) + " ms (" +
+             std::to_string(cuts.size() - 1) + " batches)");
+    if (!search_error.empty()) throw std::runtime_error(search_error);
+    if (!writer_error.empty()) throw std::runtime_error(writer_error);
+}
+
+void run_query_file(const std::vector<fin_index*>& indexes, const fin_index_info& info, const std::string& infile, FILE* out,
+                    QueryTotals& tot) {
+    log_line("Running streaming queries from input file " + infile);
+    fin::SeqBatch all;
+    fin::append_sequences(infile, all);
+    // "(u,p) ": the widest pair this index can report, or "(-1,-1) "
+    const size_t bytes_per_hit = (size_t)std::max(8, decimal_digits(info.n_unitigs) + decimal_digits(info.text_len) + 4);
+    const bool fits32 = info.n_unitigs < 0x7FFFFFFF && info.text_len < 0x7FFFFFFF;
+    if (fits32) run_query_batches<int32_t>(indexes, info.k, all, out, tot, bytes_per_hit);
+    else run_query_batches<int64_t>(indexes, info.k, all, out, tot, bytes_per_hit);
 }
 
 int search_fmin_command(int argc, char** argv) {
@@ -281,7 +398,7 @@ int search_fmin_command(int argc, char** argv) {
         QueryTotals tot;
         const int64_t t0 = now_micros();
         try {
-            run_query_file(indexes, info.k, query_files[i], out, tot);
+            run_query_file(indexes, info, query_files[i], out, tot);
         } catch (...) {
             if (!to_stdout) std::fclose(out);
             free_all();

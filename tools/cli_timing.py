@@ -35,6 +35,9 @@ def timed(*cmd, env=None):
     dt = time.perf_counter() - t0
     if r.returncode != 0:
         sys.exit(f"{' '.join(cmd)} failed: {r.stderr[-500:]}")
+    for line in r.stderr.splitlines():
+        if "pipeline:" in line or "Index loaded" in line or "Running streaming" in line:
+            print("      |", line)
     return dt
 
 
