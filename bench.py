@@ -405,6 +405,8 @@ def main():
                     "traffic": traffic["dram_bytes_per_read"] * n_reads if traffic else None,
                     "traffic_source": (f"ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of a {traffic['reads_in_captured_launch']}-read launch "
                                        f"({traffic['version']}), scaled per read to this launch") if traffic else None,
+                    "dram_gbs": traffic["dram_bytes_per_read"] * n_reads / avg_search_s / 1e9 if traffic else None,
+                    "dram_frac": traffic["dram_bytes_per_read"] * n_reads / avg_search_s / 1e9 / peak if traffic else None,
                     "kernel": "search_reads_kernel", "kernel_ms": avg_search_s * 1e3, "kernel_share_of_step": float(np.sum(search_ms)) / dev_total_ms if world == 1 else None,
                     "algorithmic_bytes_per_launch": bytes_per_launch, "algorithmic_bytes_per_kmer": bytes_per_launch / kmers_per_step,
                     "peak_source": peak_src,

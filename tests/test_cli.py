@@ -104,3 +104,46 @@ def test_cli_search_sharded_over_all_gpus_prints_the_same(tmp_path):
             assert f"on {n} GPUs" in r.stderr
         outs.append(open(o, "rb").read())
     assert outs[0] == outs[1] and len(outs[0]) > 0
+
+
+@pytest.mark.gpu
+def test_cli_input_formats_fastq_gzip_and_file_lists(tmp_path):
+    """The reader's other inputs (SBWT/src/SeqIO.cpp:19-52: format from the extension, .gz through zlib) and the `.txt`
+    list mode of -q / -o (search_fmin.hh:153-172), against the text the reference wrote for the same queries."""
+    import gzip
+
+    d = os.path.join(H.GOLDEN, "syn_k31")
+    want = open(os.path.join(d, "ref_out.txt"), "rb").read()
+    reads = H.read_fasta(os.path.join(d, "queries.fna"))
+    fq = str(tmp_path / "q.fastq")
+    with open(fq, "w") as f:
+        for i, r in enumerate(reads):
+            f.write(f"@r{i}\n{r.lower() if i % 3 == 0 else r}\n+\n{'I' * len(r)}\n")
+    fagz, fqgz = str(tmp_path / "q.fna.gz"), str(tmp_path / "q.fq.gz")
+    with gzip.open(fagz, "wb") as f:
+        f.write(open(os.path.join(d, "queries.fna"), "rb").read())
+    with gzip.open(fqgz, "wb") as f:
+        f.write(open(fq, "rb").read())
+    for q in (fq, fagz, fqgz):
+        out = str(tmp_path / "out.txt")
+        r = run("search-fmin", "-i", os.path.join(d, "ref"), "-q", q, "-o", out)
+        assert r.returncode == 0, (q, r.stderr[-300:])
+        assert open(out, "rb").read() == want, q
+    # list mode: two query files, two output files
+    qlist, olist = str(tmp_path / "queries.txt"), str(tmp_path / "outs.txt")
+    open(qlist, "w").write(f"{fq}\n{fagz}\n")
+    open(olist, "w").write(f"{tmp_path / 'o1.txt'}\n{tmp_path / 'o2.txt'}\n")
+    r = run("search-fmin", "-i", os.path.join(d, "ref"), "-q", qlist, "-o", olist)
+    assert r.returncode == 0, r.stderr[-300:]
+    assert open(tmp_path / "o1.txt", "rb").read() == want and open(tmp_path / "o2.txt", "rb").read() == want
+    open(olist, "w").write(f"{tmp_path / 'o1.txt'}\n")
+    r = run("search-fmin", "-i", os.path.join(d, "ref"), "-q", qlist, "-o", olist)
+    assert r.returncode == 1 and "does not match" in r.stderr
+    # unitigs as gzipped FASTA for build-fmin
+    ugz = str(tmp_path / "unitigs.fna.gz")
+    with gzip.open(ugz, "wb") as f:
+        f.write(open(os.path.join(d, "unitigs.fna"), "rb").read())
+    prefix = str(tmp_path / "fromgz")
+    assert run("build-fmin", "-o", prefix, "-i", os.path.join(d, "input.sbwt"), "-u", ugz).returncode == 0
+    for suf in H.INDEX_SUFFIXES:
+        assert H.files_equal(prefix + suf, os.path.join(d, "ref" + suf)), suf
