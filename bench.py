@@ -110,7 +110,7 @@ def profiled_traffic():
     """dram bytes per launch of the search kernel from the committed ncu capture, if there is one."""
     p = os.path.join(ROOT, "profiles", "search_kernel_traffic.json")
     if os.path.exists(p):
-        return json.load(open(p))
+        return json.load(open(p))  # one capture, or a list of captures (one per workload)
     return None
 
 
@@ -391,8 +391,9 @@ def main():
         peak, peak_src = measured_peak()
         achieved = bytes_per_launch / avg_search_s / 1e9
         traffic = profiled_traffic()
-        if traffic and int(traffic.get("genome", 5_000_000)) != args.genome:
-            traffic = None  # the committed capture is of another workload
+        if isinstance(traffic, dict):
+            traffic = [traffic]
+        traffic = next((t for t in traffic or [] if int(t.get("genome", 5_000_000)) == args.genome and int(t.get("k", 31)) == args.k), None)
         l2_bytes = 126e6
         regime = ("L2-resident at this config: the sector model counts every access as HBM traffic" if info["device_bytes"] < l2_bytes
                   else f"{info['device_bytes'] / l2_bytes:.1f}x the 126 MB L2: random sectors mostly come from HBM")
