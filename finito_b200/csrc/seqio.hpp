@@ -36,7 +36,21 @@ inline SeqFormat sequence_file_format(std::string name) {  // SBWT/src/SeqIO.cpp
 }
 
 inline std::vector<char> read_maybe_gz(const std::string& path) {
-    gzFile f = gzopen(path.c_str(), "rb");  // transparent for plain files
+    if (!has_suffix(path, ".gz")) {  // the reference decides by the extension too (SeqIO.cpp:19-52): plain file, one read
+        FILE* pf = fopen(path.c_str(), "rb");
+        if (!pf) throw io_error("Error opening file " + path);
+        std::vector<char> whole;
+        if (fseek(pf, 0, SEEK_END) == 0) {
+            const long n = ftell(pf);
+            if (n > 0) whole.resize((size_t)n);
+            fseek(pf, 0, SEEK_SET);
+        }
+        const size_t got = whole.empty() ? 0 : fread(whole.data(), 1, whole.size(), pf);
+        fclose(pf);
+        if (got != whole.size()) throw io_error("Error reading file " + path);
+        return whole;
+    }
+    gzFile f = gzopen(path.c_str(), "rb");
     if (!f) throw io_error("Error opening file " + path);
     gzbuffer(f, 1 << 20);
     std::vector<char> buf;
