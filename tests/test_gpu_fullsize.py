@@ -20,7 +20,13 @@ def colex_ranked(unitigs, k):
     return [unitigs[i] for i in order]
 
 
-@pytest.fixture(scope="module", params=[(31, 5_000_000, 1_000_000), (63, 2_000_000, 300_000)], ids=["config2_k31", "k63"])
+PARAMS, IDS = [(31, 5_000_000, 1_000_000), (63, 2_000_000, 300_000)], ["config2_k31", "k63"]
+if os.environ.get("FIN_FULLSIZE_GENOME"):  # one-off runs at other sizes, e.g. 200000000 for an index far beyond the L2
+    PARAMS.append((int(os.environ.get("FIN_FULLSIZE_K", "31")), int(os.environ["FIN_FULLSIZE_GENOME"]), 1_000_000))
+    IDS.append("env_size")
+
+
+@pytest.fixture(scope="module", params=PARAMS, ids=IDS)
 def big(request, gpu_lib, tmp_path_factory):
     k, genome_len, n_reads = request.param
     ds = make_dataset("full", genome_len=genome_len, k=k, n_reads=n_reads, read_len=150, seed=20260102 + k,
