@@ -193,17 +193,20 @@ class FinimizerIndex:
         seqs, offs = _as_batch(reads)
         n = len(offs) - 1
         k = self.info["k"]
-        total = int(lib().fin_count_kmers(offs.ctypes.data, n, k))
         dtype = np.int64 if hit_bits == 64 else np.int32
+        total = None
         if out is None:
+            total = int(lib().fin_count_kmers(offs.ctypes.data, n, k))
             out = np.empty((total, 2), dtype=dtype)
-        assert out.dtype == dtype and out.size >= 2 * total and out.flags.c_contiguous
+        assert out.dtype == dtype and out.flags.c_contiguous  # a caller-supplied buffer is checked by the library (capacity)
         c = _Counts()
         fn = lib().fin_search_batch if hit_bits == 64 else lib().fin_search_batch32
         if forward_only:
             assert hit_bits == 64
             fn = lib().fin_search_forward
         _check(fn(self._h, seqs.ctypes.data, offs.ctypes.data, n, out.ctypes.data, out.size // 2, C.byref(c)))
+        if total is None:
+            total = int(c.n_queries)  # = sum max(0, len - k + 1), search_fmin.hh:69
         return out[:total], SearchCounts(c.found_fwd, c.found_rc, c.positive, c.n_queries)
 
     def search(self, query: str):

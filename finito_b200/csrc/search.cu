@@ -256,10 +256,8 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
     if (sizeof(HitT) == 4 && !fits32_) throw limit_error("this index needs 64-bit hits (use fin_search_batch)");
     FIN_CUDA(cudaSetDevice(device_));
     const int k = view_.k;
-    const uint64_t total = fin_count_kmers(read_offsets, n_reads, k);
-    if (total > out_capacity) throw arg_error("out_capacity is smaller than the number of k-mer positions of the batch");
-    for (uint64_t i = 0; i < n_reads; i++)
-        if (read_offsets[i + 1] < read_offsets[i]) throw arg_error("read_offsets must be non-decreasing");
+    // the offsets are validated and the k-mer positions counted sub-batch by sub-batch while the GPU already works on
+    // the previous ones: no pass over the whole batch stands between the call and the first copy
 
     if (slots_.empty()) {
         for (int i = 0; i < kSlots; i++) {
@@ -297,9 +295,19 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
         }
         const uint64_t nr = r1 - r0, nb = read_offsets[r1] - base0;
         uint64_t nkm = 0;
+        bool ordered = true;
         for (uint64_t i = r0; i < r1; i++) {
+            ordered &= read_offsets[i + 1] >= read_offsets[i];
             const uint64_t len = read_offsets[i + 1] - read_offsets[i];
-            if (len >= (uint64_t)k) nkm += len - (uint64_t)k + 1;
+            nkm += len >= (uint64_t)k ? len - (uint64_t)k + 1 : 0;
+        }
+        if (!ordered || out_pos + nkm > out_capacity) {
+            for (auto& sl : slots_) {  // let the sub-batches in flight finish before reporting
+                if (sl->busy) cudaEventSynchronize(sl->done);
+                sl->busy = false;
+            }
+            if (!ordered) throw arg_error("read_offsets must be non-decreasing");
+            throw arg_error("out_capacity is smaller than the number of k-mer positions of the batch");
         }
 
         SearchSlot& s = *slots_[turn % kSlots];
