@@ -261,6 +261,28 @@ def build_arm(fb, ds, rank, world, local_rank, steps, barrier):
             "includes": "file parsing, LCS (device), permutation, stream, merge, index files written", "stages": stages}
 
 
+def bind_to_gpu_numa_node(device):
+    """One process per GPU: run on the cores next to that GPU (NVML's ideal CPU set) so that the pinned host buffers
+    of the end-to-end arm are allocated on the GPU's own NUMA node.  Best effort; FIN_BENCH_NO_AFFINITY=1 turns it off."""
+    if os.environ.get("FIN_BENCH_NO_AFFINITY") == "1":
+        return None
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(device)
+        n_cpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(h, (n_cpu + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus and len(cpus) < n_cpu:
+            os.sched_setaffinity(0, cpus)
+            return f"{len(cpus)} of {n_cpu} cpus"
+    except Exception:
+        pass
+    return None
+
+
 # ---------------------------------------------------------------------------------------------------------
 def main():
     args = parse_args()
@@ -282,6 +304,7 @@ def main():
     if not torch.cuda.is_available() or fb.device_count() < 1:
         raise SystemExit("bench.py: no CUDA device (there is no CPU fallback)")
     torch.cuda.set_device(local_rank)
+    affinity = bind_to_gpu_numa_node(local_rank) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -428,7 +451,7 @@ def main():
             "dtype": "u64", "data": "synthetic",
             "config": {"workload": workload_name(args), "k": args.k, "t": 1, "type": "rarest", "reads_per_gpu_per_step": n_reads,
                        "kmers_per_gpu_per_step": kmers_per_step, "found_fraction": counts.positive / counts.n_queries,
-                       "index_nodes": info["n_nodes"], "index_device_bytes": info["device_bytes"], "parallelism": f"reads sharded x{world}, index replicated, no collective",
+                       "index_nodes": info["n_nodes"], "index_device_bytes": info["device_bytes"], "parallelism": f"reads sharded x{world}, index replicated, no collective", "cpu_affinity": affinity,
                        "l2": "per-step inputs+outputs (1.5 GB reads, 9.6 GB hits at the default size) exceed the 126 MB L2; the index itself is L2-resident by design of this config",
                        "index_build_s": build_s},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n_bases + 8 * (n_reads + 1)),
