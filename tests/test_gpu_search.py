@@ -148,3 +148,27 @@ def test_device_resident_entry_point(synthetic, gpu_lib):
                                  d_out.data_ptr(), 4)
         assert ms > 0 and c == wc
         assert np.array_equal(d_out.cpu().numpy(), want)
+
+
+def test_bad_batches_are_refused_and_the_handle_survives(synthetic, gpu_lib):
+    """Capacity and offset checks happen per sub-batch inside the pipeline: the call reports FIN_ERR_ARG and the handle works on."""
+    import ctypes as C
+
+    fb = gpu_lib
+    ds, prefix = synthetic
+    seqs, offs = ds["reads"]
+    n = 5000
+    sub_seqs, sub_offs = np.ascontiguousarray(seqs[: int(offs[n])]), np.ascontiguousarray(offs[: n + 1])
+    with fb.FinimizerIndex.load(prefix) as ix:
+        want, wc = ix.search_batch((sub_seqs, sub_offs))
+        total = want.shape[0]
+        out = np.empty((total, 2), dtype=np.int64)
+        c = fb._Counts()
+        st = fb.lib().fin_search_batch(ix._h, sub_seqs.ctypes.data, sub_offs.ctypes.data, n, out.ctypes.data, total - 1, C.byref(c))
+        assert st == fb.FIN_ERR_ARG and b"out_capacity" in fb.lib().fin_last_error()
+        bad = sub_offs.copy()
+        bad[100], bad[101] = bad[101], bad[100]
+        st = fb.lib().fin_search_batch(ix._h, sub_seqs.ctypes.data, bad.ctypes.data, n, out.ctypes.data, total, C.byref(c))
+        assert st == fb.FIN_ERR_ARG and b"non-decreasing" in fb.lib().fin_last_error()
+        again, ac = ix.search_batch((sub_seqs, sub_offs), out=out)
+        assert np.array_equal(again, want) and ac == wc
