@@ -27,6 +27,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
 
 METRIC = "search-fmin k-mers localized/sec"
 UNIT = "k-mers/s"
@@ -49,7 +50,7 @@ def parse_args():
 
 
 def dataset(args, rank=0):
-    from datasets import make_dataset
+    from fin_datasets import make_dataset
 
     # planted repeats as in SURVEY.md §8(d) config 2: 50 families x 5 copies x 2 kb at 1 % divergence per 5 Mbp
     return make_dataset("bench", genome_len=args.genome, k=args.k, n_reads=args.reads, read_len=args.read_len,
@@ -251,14 +252,62 @@ def build_arm(fb, ds, rank, world, local_rank, steps, barrier):
         if i:
             walls.append(time.perf_counter() - t0)
     wall = float(np.mean(walls))
+    parity = None
     if world > 1:
         import torch.distributed as dist
 
         t = torch.tensor([wall], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         wall = float(t.item())
-    return {"metric": "build-fmin unitig bp/sec", "value": bp / wall, "unit": "bp/s", "wall_s": wall, "unitig_bp": bp, "builds_timed": steps,
-            "includes": "file parsing, LCS (device), permutation, stream, merge, index files written", "stages": stages}
+        # parity of the NCCL path on this very hardware: the seven files the sharded build wrote against a single-GPU
+        # fin_build of the same inputs (itself pinned byte for byte to the reference's files by tests/)
+        if rank == 0:
+            single = os.path.join(ds["dir"], "bench_build_single")
+            fb.build_fmin(ds["sbwt"], ds["unitigs"], single, device=local_rank)
+            sha = {suf: (file_sha256(out + suf), file_sha256(single + suf)) for suf in INDEX_SUFFIXES}
+            parity = {"parity_ok": all(a == b for a, b in sha.values()),
+                      "sha256_sharded": {suf: a[:16] for suf, (a, _) in sha.items()},
+                      "sha256_single_gpu": {suf: b[:16] for suf, (_, b) in sha.items()},
+                      "compared": f"{len(sha)} index files of the {world}-rank NCCL build vs fin_build on one GPU, same inputs"}
+        barrier()
+    res = {"metric": "build-fmin unitig bp/sec", "value": bp / wall, "unit": "bp/s", "wall_s": wall, "unitig_bp": bp, "builds_timed": steps,
+           "includes": "file parsing, LCS (device), permutation, stream, merge, index files written", "stages": stages}
+    if parity:
+        res.update(parity)
+    return res
+
+
+INDEX_SUFFIXES = [".O.sdsl", ".FBV.sdsl", ".packed_unitigs.sdsl", ".unitig_endpoints.sdsl", ".Ustart.sdsl", ".LCS.sdsl", ".sbwt"]
+
+
+def file_sha256(path):
+    import hashlib
+
+    h = hashlib.sha256()
+    with open(path, "rb") as f:
+        for blk in iter(lambda: f.read(1 << 24), b""):
+            h.update(blk)
+    return h.hexdigest()
+
+
+def sharded_search_parity(fb, ix, ds, rank, world, n_reads=200_000):
+    """N > 1 only: the first n_reads of rank 0's workload searched (a) sharded over all ranks through
+    finito_b200.distributed.search_sharded and (b) on rank 0's GPU alone; hits and the four counters must be equal."""
+    import hashlib
+
+    from finito_b200.distributed import search_sharded
+
+    seqs, offs = ds["reads"]
+    n = min(n_reads, len(offs) - 1)
+    seqs, offs = seqs[: int(offs[n])], offs[: n + 1]
+    all_hits, counts, _ = search_sharded(ix, seqs, offs, hit_bits=32)
+    if rank != 0:
+        return None
+    want, c = ix.search_batch((seqs, offs), hit_bits=32)
+    wc = [c.found_fwd, c.found_rc, c.positive, c.n_queries]
+    return {"parity_ok": bool(np.array_equal(all_hits, want) and counts == wc), "reads": int(n), "counters_sharded": counts,
+            "counters_single_gpu": wc, "sha256_hits_sharded": hashlib.sha256(np.ascontiguousarray(all_hits).tobytes()).hexdigest()[:16],
+            "sha256_hits_single_gpu": hashlib.sha256(np.ascontiguousarray(want).tobytes()).hexdigest()[:16]}
 
 
 def bind_to_gpu_numa_node(device):
@@ -392,6 +441,19 @@ def main():
     if not args.no_build_arm:
         build = build_arm(fb, ds if world == 1 else dataset(args, 0), rank, world, local_rank, min(args.steps, 3), barrier)
 
+    # ---- N > 1: the sharded search against the single-GPU search on the same reads (every rank uses rank 0's reads)
+    search_parity = None
+    if world > 1:
+        ds0 = dataset(args, 0)
+        pfx0 = os.path.join(ds0["dir"], "fmin")
+        if rank == 0 and not os.path.exists(pfx0 + ".FBV.sdsl"):
+            fb.build_fmin(ds0["sbwt"], ds0["unitigs"], pfx0, device=local_rank)
+        barrier()
+        ix0 = ix if rank == 0 else fb.FinimizerIndex.load(pfx0, device=local_rank)
+        search_parity = sharded_search_parity(fb, ix0, ds0, rank, world)
+        if rank != 0:
+            ix0.close()
+
     # ---- max over ranks
     if world > 1:
         t = torch.tensor([dev_total_ms, e2e_total, wall_dev], dtype=torch.float64, device="cuda")
@@ -460,7 +522,7 @@ def main():
                     "d2h_link_gbs": d2h_link_gbs, "d2h_floor_ms_per_step": kmers_per_step * 8 / d2h_link_gbs / 1e6,
                     "note": "the hits (8 B per k-mer) leave over PCIe: the step cannot be shorter than d2h_floor_ms_per_step on this host"},
             "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "build": build,
-            "wall_s_device_arm": wall_dev,
+            "search_parity": search_parity, "wall_s_device_arm": wall_dev,
         }
         print(json.dumps(line))
     if world > 1:

@@ -72,6 +72,14 @@ def main():
         # the reference's own cases plus every unitig and its reverse complement as queries
         qs += case["unitigs"] + [rc(u) for u in case["unitigs"]]
         make_case("kat_" + case["name"], case["k"], case["unitigs"], qs, 0)
+    # BASELINE.json configs[0]: the literal ref_implementation/example.fna (three paper-example unitigs), queried
+    # against itself and its reverse complements.  k=4 (at k=31 the file holds no k-mer at all).
+    example = "/root/reference/ref_implementation/example.fna"
+    if os.path.exists(example):
+        ex = [l.strip() for l in open(example) if l.strip() and not l.startswith(">")]
+        make_case("example_fna_k4", 4, ex, ex + [rc(u) for u in ex], 4)
+    if "--only-example" in sys.argv:
+        return
     rng = random.Random(20260101)
     tmp = os.path.join(ROOT, "_work", "golden_tmp")
     for name, glen, k, seed, fam, nreads, rlen in [("syn_k31", 12000, 31, 11, 3, 60, 150), ("syn_k63", 6000, 63, 12, 2, 30, 200),

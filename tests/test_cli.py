@@ -10,7 +10,7 @@ import pytest
 
 import finito_b200 as fb
 import helpers as H
-from datasets import make_dataset
+from fin_datasets import make_dataset
 
 CLI = fb.CLI_PATH
 

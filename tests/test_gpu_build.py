@@ -7,7 +7,7 @@ import pytest
 
 import helpers as H
 from conftest import golden_cases
-from datasets import make_dataset
+from fin_datasets import make_dataset
 
 pytestmark = pytest.mark.gpu
 

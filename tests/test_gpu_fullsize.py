@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 import helpers as H
-from datasets import make_dataset
+from fin_datasets import make_dataset
 
 pytestmark = pytest.mark.gpu
 

@@ -8,7 +8,7 @@ import pytest
 
 import helpers as H
 from conftest import golden_cases
-from datasets import make_dataset
+from fin_datasets import make_dataset
 
 
 @pytest.mark.parametrize("case", golden_cases())

@@ -12,7 +12,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 import numpy as np  # noqa: E402
 
 import finito_b200 as fb  # noqa: E402
-from datasets import make_dataset  # noqa: E402
+from fin_datasets import make_dataset  # noqa: E402
 
 n_reads = int(sys.argv[1]) if len(sys.argv) > 1 else 2_000_000
 n_ref = int(sys.argv[2]) if len(sys.argv) > 2 else 200_000

@@ -27,7 +27,10 @@ def make_dataset(name, genome_len, k, n_reads, read_len=150, seed=1, error=0.01,
     if families is None:
         families = max(1, genome_len // 100_000)
     rep_len = min(rep_len, max(2 * k, genome_len // 20))
+    # every generator parameter is part of the cache tag (a changed parameter must never reuse stale data)
     tag = f"{name}_g{genome_len}_k{k}_r{n_reads}x{read_len}_s{seed}_f{families}"
+    if (error, copies, rep_len, divergence) != (0.01, 5, min(2000, max(2 * k, genome_len // 20)), 0.01):
+        tag += f"_e{error:g}_c{copies}_l{rep_len}_d{divergence:g}"
     d = os.path.join(WORK, tag)
     os.makedirs(d, exist_ok=True)
     genome, unitigs, sbwt = (os.path.join(d, f) for f in ("genome.fna", "unitigs.fna", "index.sbwt"))
