@@ -406,11 +406,51 @@ def main():
     gpu_launches = fb.launch_count() - launches1
     dev_total_ms = float(sum(pipeline_ms))
 
-    # ---- end-to-end arm: pinned host buffers through fin_search_batch32
+    # ---- device-resident arm, answers as run-length records (fin_search_device_runs)
+    runs_cap = 16 * n_reads
+    d_ro = torch.empty(n_reads + 1, dtype=torch.int64, device="cuda")
+    d_runs = torch.empty((runs_cap, 4), dtype=torch.int32, device="cuda")
+    for _ in range(args.warmup):
+        n_runs, counts_runs, _ = ix.search_device_runs(d_seqs.data_ptr(), d_offs.data_ptr(), n_reads, n_bases, d_ro.data_ptr(), d_runs.data_ptr(), runs_cap)
+    barrier()
+    runs_ms, runs_search_ms = [], []
+    for _ in range(args.steps):
+        n_runs, counts_runs, ms = ix.search_device_runs(d_seqs.data_ptr(), d_offs.data_ptr(), n_reads, n_bases, d_ro.data_ptr(), d_runs.data_ptr(), runs_cap)
+        runs_ms.append(ms)
+        runs_search_ms.append(ix.last_timing()["search_kernel_ms"])
+    barrier()
+    assert counts_runs == counts
+    runs_total_ms = float(sum(runs_ms))
+    del d_runs, d_ro
+
+    # ---- end-to-end arm, runs: pinned host buffers through fin_search_batch_runs
     h_seqs = torch.empty(n_bases, dtype=torch.uint8).pin_memory()
     h_seqs.numpy()[:] = seqs
+    h_seqs_np = h_seqs.numpy()
+    h_runs = torch.empty((int(n_runs * 1.05) + 1024, 4), dtype=torch.int32).pin_memory()
+    h_ro = torch.empty(n_reads + 1, dtype=torch.int64).pin_memory()
+    h_runs_np = h_runs.numpy().view(np.uint32).reshape(-1).view(fb.RUN_DTYPE)
+    h_ro_np = h_ro.numpy().view(np.uint64)
+    for _ in range(min(args.warmup, 2)):
+        ix.search_batch_runs((h_seqs_np, offs), runs=h_runs_np, run_offsets=h_ro_np)
+    barrier()
+    e2e_runs_times = []
+    for _ in range(args.steps):
+        t1 = time.perf_counter()
+        ro_e, runs_e, c_runs_e2e = ix.search_batch_runs((h_seqs_np, offs), runs=h_runs_np, run_offsets=h_ro_np)
+        e2e_runs_times.append(time.perf_counter() - t1)
+    barrier()
+    assert c_runs_e2e == counts and len(runs_e) == n_runs
+    e2e_runs_total = float(sum(e2e_runs_times))
+    # expand-on-host cost of the dense table from the runs (what a caller that wants the table pays on the CPU)
+    t1 = time.perf_counter()
+    sample_reads = min(n_reads, 1_000_000)
+    fb.expand_runs(offs[: sample_reads + 1], args.k, h_ro_np[: sample_reads + 1], h_runs_np, hit_bits=32, threads=cpu_threads())
+    expand_s_per_read = (time.perf_counter() - t1) / sample_reads
+
+    # ---- end-to-end arm: pinned host buffers through fin_search_batch32
     h_out = torch.empty((kmers_per_step, 2), dtype=torch.int32).pin_memory()
-    h_seqs_np, h_out_np = h_seqs.numpy(), h_out.numpy()
+    h_out_np = h_out.numpy()
     for _ in range(min(args.warmup, 2)):
         ix.search_batch((h_seqs_np, offs), hit_bits=32, out=h_out_np)
     barrier()
@@ -456,9 +496,9 @@ def main():
 
     # ---- max over ranks
     if world > 1:
-        t = torch.tensor([dev_total_ms, e2e_total, wall_dev], dtype=torch.float64, device="cuda")
+        t = torch.tensor([dev_total_ms, e2e_total, wall_dev, runs_total_ms, e2e_runs_total], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_total_ms, e2e_total, wall_dev = (float(x) for x in t.cpu())
+        dev_total_ms, e2e_total, wall_dev, runs_total_ms, e2e_runs_total = (float(x) for x in t.cpu())
     value = world * kmers_per_step * args.steps / (dev_total_ms / 1e3)
     e2e_value = world * kmers_per_step * args.steps / e2e_total
 
@@ -522,6 +562,13 @@ def main():
                     "d2h_link_gbs": d2h_link_gbs, "d2h_floor_ms_per_step": kmers_per_step * 8 / d2h_link_gbs / 1e6,
                     "note": "the hits (8 B per k-mer) leave over PCIe: the step cannot be shorter than d2h_floor_ms_per_step on this host"},
             "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "build": build,
+            "runs": {"value": world * kmers_per_step * args.steps / (runs_total_ms / 1e3), "unit": UNIT, "ms_per_step": runs_total_ms / args.steps,
+                     "search_kernel_ms": float(np.mean(runs_search_ms)), "runs_per_read": n_runs / n_reads, "bytes_per_read": 16 * n_runs / n_reads + 8,
+                     "api": "fin_search_device_runs",
+                     "e2e": {"value": world * kmers_per_step * args.steps / e2e_runs_total, "unit": UNIT, "ms_per_step": e2e_runs_total / args.steps * 1e3,
+                             "h2d_bytes_per_step": int(n_bases + 8 * (n_reads + 1)), "d2h_bytes_per_step": int(16 * n_runs + 8 * (n_reads + 1)),
+                             "api": "fin_search_batch_runs (pinned host buffers)"},
+                     "expand_on_host_ms_per_step": expand_s_per_read * n_reads * 1e3, "expand_threads": cpu_threads()},
             "search_parity": search_parity, "wall_s_device_arm": wall_dev,
         }
         print(json.dumps(line))

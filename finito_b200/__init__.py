@@ -78,6 +78,12 @@ ABI = {
                                      C.POINTER(_Counts)]),
     "fin_search_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p,
                                     C.c_int, C.POINTER(_Counts), C.POINTER(C.c_float)]),
+    "fin_search_batch_runs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, _u64p,
+                                        C.POINTER(_Counts)]),
+    "fin_search_device_runs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p,
+                                         C.c_uint64, _u64p, C.POINTER(_Counts), C.POINTER(C.c_float)]),
+    "fin_expand_runs": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int,
+                                  C.c_int]),
     "fin_search_access_counters": (C.c_int, [C.c_void_p, C.POINTER(_Access)]),
     "fin_search_set_counting": (C.c_int, [C.c_void_p, C.c_int]),
     "fin_search_last_timing": (C.c_int, [C.c_void_p, C.POINTER(_Timing)]),
@@ -99,6 +105,10 @@ ABI = {
     "fin_builder_slice": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "fin_builder_finish": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_char_p]),
 }
+
+# fin_run (include/finito_b200.h): merged k-mer positions [first_kmer, first_kmer + len) of a read -> one unitig
+RUN_DTYPE = np.dtype([("first_kmer", np.uint32), ("len_rc", np.uint32), ("unitig", np.uint32), ("first_offset", np.uint32)])
+RUN_RC = 0x80000000
 
 _lib = None
 
@@ -209,6 +219,36 @@ class FinimizerIndex:
             total = int(c.n_queries)  # = sum max(0, len - k + 1), search_fmin.hh:69
         return out[:total], SearchCounts(c.found_fwd, c.found_rc, c.positive, c.n_queries)
 
+    def search_batch_runs(self, reads, runs: np.ndarray | None = None, run_offsets: np.ndarray | None = None):
+        """search-fmin for a batch with the answer as run-length records (fin_search_batch_runs):
+        (run_offsets[n_reads + 1], runs[n_runs] of RUN_DTYPE, SearchCounts).  A too small `runs` buffer is retried once
+        with the size the library reports."""
+        seqs, offs = _as_batch(reads)
+        n = len(offs) - 1
+        if run_offsets is None:
+            run_offsets = np.empty(n + 1, dtype=np.uint64)
+        if runs is None:
+            runs = np.empty(max(1024, 8 * n), dtype=RUN_DTYPE)
+        assert runs.dtype == RUN_DTYPE and run_offsets.dtype == np.uint64 and len(run_offsets) >= n + 1
+        c, nr = _Counts(), C.c_uint64()
+        for attempt in range(2):
+            st = lib().fin_search_batch_runs(self._h, seqs.ctypes.data, offs.ctypes.data, n, run_offsets.ctypes.data,
+                                             runs.ctypes.data, len(runs), C.byref(nr), C.byref(c))
+            if st == FIN_ERR_ARG and nr.value > len(runs) and attempt == 0:
+                runs = np.empty(int(nr.value), dtype=RUN_DTYPE)
+                continue
+            _check(st)
+            break
+        return run_offsets[: n + 1], runs[: nr.value], SearchCounts(c.found_fwd, c.found_rc, c.positive, c.n_queries)
+
+    def search_device_runs(self, d_seqs: int, d_offsets: int, n_reads: int, n_bases: int, d_run_offsets: int, d_runs: int,
+                           runs_capacity: int):
+        """Same on device-resident buffers (raw device pointers); returns (n_runs, SearchCounts, kernel milliseconds)."""
+        c, ms, nr = _Counts(), C.c_float(), C.c_uint64()
+        _check(lib().fin_search_device_runs(self._h, d_seqs, d_offsets, n_reads, n_bases, d_run_offsets, d_runs, runs_capacity,
+                                            C.byref(nr), C.byref(c), C.byref(ms)))
+        return int(nr.value), SearchCounts(c.found_fwd, c.found_rc, c.positive, c.n_queries), float(ms.value)
+
     def search(self, query: str):
         """FinimizerIndex::search(query): forward strand only (include/FinimizerIndex.hh:119-185)."""
         hits, _ = self.search_batch([query], forward_only=True)
@@ -307,6 +347,22 @@ class ShardedBuilder:
         offsets_all = np.ascontiguousarray(offsets_all, dtype=np.uint32)
         _check(lib().fin_builder_finish(self._h, bits_all.ctypes.data, bits_all.size, offsets_all.ctypes.data, offsets_all.size,
                                         os.fsencode(self.out_prefix)))
+
+
+def expand_runs(read_offsets: np.ndarray, k: int, run_offsets: np.ndarray, runs: np.ndarray, hit_bits: int = 64,
+                out: np.ndarray | None = None, threads: int = 1) -> np.ndarray:
+    """fin_expand_runs: runs -> the (unitig, offset) table of search_batch, on the host."""
+    offs = np.ascontiguousarray(read_offsets, dtype=np.uint64)
+    ro = np.ascontiguousarray(run_offsets, dtype=np.uint64)
+    runs = np.ascontiguousarray(runs, dtype=RUN_DTYPE)
+    n = len(offs) - 1
+    dtype = np.int64 if hit_bits == 64 else np.int32
+    if out is None:
+        out = np.empty((int(lib().fin_count_kmers(offs.ctypes.data, n, k)), 2), dtype=dtype)
+    assert out.dtype == dtype and out.flags.c_contiguous
+    _check(lib().fin_expand_runs(offs.ctypes.data, n, k, ro.ctypes.data, runs.ctypes.data, out.ctypes.data, out.size // 2,
+                                 hit_bits // 8, threads))
+    return out
 
 
 def probe_random_sectors(device: int = 0, table_bytes: int = 8 << 30, repeats: int = 3, bytes_per_access: int = 32) -> float:

@@ -3,6 +3,7 @@
 #include <new>
 
 #include "engine.hpp"
+#include "runs_host.hpp"
 
 struct fin_index {
     std::unique_ptr<fin::DeviceIndex> dev;
@@ -42,7 +43,7 @@ extern "C" {
 
 const char* fin_last_error(void) { return g_error.c_str(); }
 
-int fin_abi_version(void) { return 1; }
+int fin_abi_version(void) { return 2; }
 
 int fin_device_count(void) {
     int n = 0;
@@ -113,6 +114,38 @@ fin_status fin_search_device(fin_index* index, const void* d_seqs, const uint64_
     return guarded([&] {
         require(index && d_read_offsets && (d_seqs || n_bases == 0) && (d_out || total_kmers == 0), "fin_search_device: null argument");
         index->dev->search_device(d_seqs, d_read_offsets, n_reads, n_bases, total_kmers, d_out, hit_bytes, counts, kernel_ms);
+    });
+}
+
+fin_status fin_search_batch_runs(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
+                                 uint64_t* run_offsets, fin_run* runs, uint64_t runs_capacity, uint64_t* n_runs,
+                                 fin_search_counts* counts) {
+    return guarded([&] {
+        require(index && read_offsets && run_offsets && n_runs && (seqs || n_reads == 0) && (runs || runs_capacity == 0),
+                "fin_search_batch_runs: null argument");
+        *n_runs = index->dev->search_host_runs(seqs, read_offsets, n_reads, run_offsets, runs, runs_capacity, counts);
+        if (*n_runs > runs_capacity) throw fin::arg_error("runs_capacity is smaller than the number of runs of the batch (see *n_runs)");
+    });
+}
+
+fin_status fin_search_device_runs(fin_index* index, const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads,
+                                  uint64_t n_bases, uint64_t* d_run_offsets, fin_run* d_runs, uint64_t runs_capacity,
+                                  uint64_t* n_runs, fin_search_counts* counts, float* kernel_ms) {
+    return guarded([&] {
+        require(index && d_read_offsets && d_run_offsets && n_runs && (d_seqs || n_bases == 0) && (d_runs || runs_capacity == 0),
+                "fin_search_device_runs: null argument");
+        *n_runs = index->dev->search_device_runs(d_seqs, d_read_offsets, n_reads, n_bases, d_run_offsets, d_runs, runs_capacity, counts,
+                                                 kernel_ms);
+        if (*n_runs > runs_capacity) throw fin::arg_error("runs_capacity is smaller than the number of runs of the batch (see *n_runs)");
+    });
+}
+
+fin_status fin_expand_runs(const uint64_t* read_offsets, uint64_t n_reads, int64_t k, const uint64_t* run_offsets,
+                           const fin_run* runs, void* out_pairs, uint64_t out_capacity, int hit_bytes, int n_threads) {
+    return guarded([&] {
+        require(read_offsets && run_offsets && (runs || run_offsets[n_reads] == 0) && (out_pairs || out_capacity == 0),
+                "fin_expand_runs: null argument");
+        fin::expand_runs_host(read_offsets, n_reads, k, run_offsets, runs, out_pairs, out_capacity, hit_bytes, n_threads);
     });
 }
 

@@ -81,38 +81,9 @@ FIN_D uint32_t rank1(const ulonglong2* __restrict__ sectors, idx_t p) {
     return sector_count(a, b, q);
 }
 
-// Loads of the streaming search.  With FIN_LINE_PREFETCH the load asks the L2 to bring in the whole 128-byte line on a
-// miss (ld.global.nc.L2::128B): the LCS words of a column interval are touched first, the rank rows of the same line one
-// step later, so one DRAM round trip serves both instead of two dependent ones.
-#if defined(FIN_EMU) || !defined(FIN_LINE_PREFETCH)
-FIN_D uint64_t ldg_line_u64(const uint64_t* p) { return __ldg(p); }
-FIN_D uint32_t ldg_line_u32(const uint32_t* p) { return __ldg(p); }
-FIN_D uint4 ldg_line_u128(const uint4* p) { return __ldg(p); }
-#else
-FIN_D uint64_t ldg_line_u64(const uint64_t* p) {
-    uint64_t v;
-    asm volatile("ld.global.nc.L2::128B.u64 %0, [%1];" : "=l"(v) : "l"(p));
-    return v;
-}
-FIN_D uint32_t ldg_line_u32(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.global.nc.L2::128B.u32 %0, [%1];" : "=r"(v) : "l"(p));
-    return v;
-}
-FIN_D uint4 ldg_line_u128(const uint4* p) {
-#ifdef FIN_RANK_LINE_PREFETCH
-    uint4 v;
-    asm volatile("ld.global.nc.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
-    return v;
-#else
-    return __ldg(p);
-#endif
-}
-#endif
-
 // C[c] + rank_c(p): the column the edge labelled c out of the first column >= p leads to
 FIN_D idx_t step_c(const IndexView& ix, const idx_t p, const int c) {
-    const uint4 row = ldg_line_u128(ix.lines + (((p >> 6) << 3) | (uint32_t)c));  // 32-bit index: n_nodes / 8 < 2^29
+    const uint4 row = __ldg(ix.lines + (((p >> 6) << 3) | (uint32_t)c));  // 32-bit index: n_nodes / 8 < 2^29
     const uint64_t bits = (uint64_t)row.x | ((uint64_t)row.y << 32);
     return row.z + (idx_t)__popcll(bits & ((1ULL << (p & 63)) - 1ULL));
 }
@@ -122,19 +93,8 @@ FIN_D idx_t step_c(const IndexView& ix, const idx_t p, const int c) {
 // r+1 share a line, which is the common case once the interval is narrow.
 FIN_D Ival extend(const IndexView& ix, const Ival I, const int c) {
     Ival J;
-#ifdef FIN_EXTEND_SHARED_ROW
-    // l and r + 1 usually fall into the same 64-column line: then one 16-byte load serves both ranks
-    const idx_t p = I.l, q = I.r + 1;
-    const uint4 row = __ldg(ix.lines + (((p >> 6) << 3) | (uint32_t)c));
-    uint4 row2 = row;
-    if ((q >> 6) != (p >> 6)) row2 = __ldg(ix.lines + (((q >> 6) << 3) | (uint32_t)c));
-    const uint64_t b1 = (uint64_t)row.x | ((uint64_t)row.y << 32), b2 = (uint64_t)row2.x | ((uint64_t)row2.y << 32);
-    J.l = row.z + (idx_t)__popcll(b1 & ((1ULL << (p & 63)) - 1ULL));
-    J.r = row2.z + (idx_t)__popcll(b2 & ((1ULL << (q & 63)) - 1ULL)) - 1;
-#else
     J.l = step_c(ix, I.l, c);
     J.r = step_c(ix, I.r + 1, c) - 1;  // equal ranks give r == l - 1: empty
-#endif
     return J;
 }
 

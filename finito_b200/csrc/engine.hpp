@@ -50,6 +50,8 @@ template <class T> struct DevBuf {
 };
 
 struct SearchSlot;  // per-stream staging buffers of the batch pipeline
+struct SearchTotals;
+struct EventTimer;
 
 class DeviceIndex {
    public:
@@ -66,11 +68,20 @@ class DeviceIndex {
                      fin_search_counts* counts, int n_strands = 2);
     void search_device(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases,
                        uint64_t total_kmers, void* d_out, int hit_bytes, fin_search_counts* counts, float* kernel_ms);
+    // the same answers as run-length records (include/finito_b200.h fin_run); returns the number of runs
+    uint64_t search_host_runs(const char* seqs, const uint64_t* read_offsets, uint64_t n_reads, uint64_t* run_offsets, fin_run* runs,
+                              uint64_t runs_capacity, fin_search_counts* counts);
+    uint64_t search_device_runs(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases,
+                                uint64_t* d_run_offsets, fin_run* d_runs, uint64_t runs_capacity, fin_search_counts* counts,
+                                float* kernel_ms);
     fin_access_counters last_access{};
     bool count_accesses = false;
     fin_search_timing last_timing{};
 
    private:
+    uint64_t prepare_device_batch(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases);
+    void finish_device_batch(EventTimer& t, fin_search_counts* counts, float* kernel_ms, SearchTotals& tot);
+    void ensure_slots();
     int device_;
     IndexView view_{};
     fin_index_info info_{};
@@ -79,8 +90,8 @@ class DeviceIndex {
     DevBuf<uint32_t> offsets_, ends_;
     std::vector<std::unique_ptr<SearchSlot>> slots_;
     // scratch of search_device
-    DevBuf<uint64_t> dev_packed_, dev_out_offsets_;
-    DevBuf<uint8_t> dev_scan_tmp_;
+    DevBuf<uint64_t> dev_packed_, dev_out_offsets_, dev_fmask_, dev_keys_a_, dev_keys_b_;
+    DevBuf<uint8_t> dev_scan_tmp_, dev_sort_tmp_, dev_recs_a_;
     DevBuf<uint8_t> dev_totals_;
 };
 

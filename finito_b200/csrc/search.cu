@@ -5,9 +5,12 @@
 #include <cstdlib>
 #include <cstring>
 
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <thread>
 
 #include "engine.hpp"
+#include "runs_host.hpp"
 #include "search_kernels.cuh"
 
 namespace fin {
@@ -19,18 +22,22 @@ thread_local uint64_t g_launches = 0;
 // -------------------------------------------------------------------------------------------------------
 struct SearchSlot {
     cudaStream_t stream = nullptr;
-    cudaEvent_t done = nullptr;
-    DevBuf<uint8_t> ascii, scan_tmp;
-    DevBuf<uint64_t> packed, offsets, out_offsets;
+    cudaEvent_t counted = nullptr, done = nullptr;  // kernels + totals copy finished / everything finished
+    DevBuf<uint8_t> ascii, scan_tmp, sort_tmp;
+    DevBuf<uint64_t> packed, offsets, out_offsets, fmask;
     DevBuf<uint8_t> hits;
+    DevBuf<uint64_t> keys_a, keys_b, run_offsets;  // runs mode: appended / sorted keys, CSR offsets
+    DevBuf<RunRec> recs_a, recs_b;
     DevBuf<uint8_t> totals;
     SearchTotals* h_totals = nullptr;  // pinned
-    std::vector<uint64_t> h_offsets;   // rebased read offsets of the sub-batch
     uint64_t* h_offsets_pinned = nullptr;
     size_t h_offsets_cap = 0;
     bool busy = false;
+    // the sub-batch in flight (runs mode needs it again when the record count is known)
+    uint64_t r0 = 0, nr = 0, nb = 0, nkm = 0, base0 = 0;
     ~SearchSlot() {
         if (stream) cudaStreamDestroy(stream);
+        if (counted) cudaEventDestroy(counted);
         if (done) cudaEventDestroy(done);
         if (h_totals) cudaFreeHost(h_totals);
         if (h_offsets_pinned) cudaFreeHost(h_offsets_pinned);
@@ -96,76 +103,107 @@ DeviceIndex::~DeviceIndex() {
 static int window_capacity(int k) { return k <= 32 ? 32 : k <= 64 ? 64 : k <= 128 ? 128 : 256; }
 
 // persistent grid: as many blocks as are resident at once (148 SMs x blocks per SM), never more than the reads need
-template <int KCAP, class HitT, bool COUNT>
+template <int KCAP, class HitT, bool COUNT, bool RUNS>
 static void launch_search_k(const IndexView& v, const uint64_t* packed, const uint64_t* offsets, uint64_t n_reads,
-                            const uint64_t* out_offsets, HitPair<HitT>* o, SearchTotals* totals, int n_strands, cudaStream_t st) {
+                            const SearchOut<HitT>& out, SearchTotals* totals, int n_strands, cudaStream_t st) {
     const int threads = FIN_SEARCH_THREADS;
-#ifdef FIN_DQ_SHARED
-    const size_t dq_smem = KCAP == 32 ? (size_t)threads * KCAP * sizeof(uint64_t) : 0;  // the candidate rings
-#else
-    const size_t dq_smem = 0;
-#endif
     static thread_local int resident[64] = {0};  // per device
     int dev = 0;
     FIN_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) throw arg_error("CUDA device ordinal out of range");
+    auto kernel = search_reads_kernel<KCAP, HitT, COUNT, RUNS>;
     if (!resident[dev]) {
         int per_sm = 0, sms = 0;
-        if (dq_smem == 0)  // no shared memory: all of the unified L1/shared array as L1 (the index lines live there)
-            FIN_CUDA(cudaFuncSetAttribute(search_reads_kernel<KCAP, HitT, COUNT>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                          (int)cudaSharedmemCarveoutMaxL1));
-        if (dq_smem > 48 * 1024)
-            FIN_CUDA(cudaFuncSetAttribute(search_reads_kernel<KCAP, HitT, COUNT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dq_smem));
-        FIN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, search_reads_kernel<KCAP, HitT, COUNT>, threads, dq_smem));
+        // no shared memory: all of the unified L1/shared array as L1 (the index lines live there)
+        FIN_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxL1));
+        FIN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0));
         FIN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         resident[dev] = std::max(1, per_sm) * std::max(1, sms);
     }
     const uint64_t need = (n_reads + threads - 1) / threads;
     const unsigned blocks = (unsigned)std::min<uint64_t>(need, (uint64_t)resident[dev]);
-    search_reads_kernel<KCAP, HitT, COUNT><<<blocks, threads, dq_smem, st>>>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands);
+    kernel<<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out, totals, n_strands);
     g_launches++;
     FIN_CUDA(cudaGetLastError());
 }
 
-template <class HitT, bool COUNT>
+template <class HitT, bool COUNT, bool RUNS>
 static void launch_search_t(const IndexView& v, const uint64_t* packed, const uint64_t* offsets, uint64_t n_reads,
-                            const uint64_t* out_offsets, void* out, SearchTotals* totals, int n_strands, cudaStream_t st) {
-    HitPair<HitT>* o = reinterpret_cast<HitPair<HitT>*>(out);
+                            const SearchOut<HitT>& out, SearchTotals* totals, int n_strands, cudaStream_t st) {
     switch (window_capacity(v.k)) {
-        case 32: launch_search_k<32, HitT, COUNT>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands, st); break;
-        case 64: launch_search_k<64, HitT, COUNT>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands, st); break;
-        case 128: launch_search_k<128, HitT, COUNT>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands, st); break;
-        default: launch_search_k<256, HitT, COUNT>(v, packed, offsets, n_reads, out_offsets, o, totals, n_strands, st); break;
+        case 32: launch_search_k<32, HitT, COUNT, RUNS>(v, packed, offsets, n_reads, out, totals, n_strands, st); break;
+        case 64: launch_search_k<64, HitT, COUNT, RUNS>(v, packed, offsets, n_reads, out, totals, n_strands, st); break;
+        case 128: launch_search_k<128, HitT, COUNT, RUNS>(v, packed, offsets, n_reads, out, totals, n_strands, st); break;
+        default: launch_search_k<256, HitT, COUNT, RUNS>(v, packed, offsets, n_reads, out, totals, n_strands, st); break;
     }
 }
 
-// pack + k-mer counts + exclusive scan + search on one stream; every pointer is device memory
-static void launch_pipeline(const IndexView& v, const uint8_t* d_ascii, uint64_t n_bases, const uint64_t* d_offsets,
-                            uint64_t n_reads, uint64_t* d_packed, uint64_t* d_out_offsets, void* d_scan_tmp,
-                            size_t scan_tmp_bytes, void* d_out, int hit_bytes, SearchTotals* d_totals, bool count,
-                            int n_strands, cudaStream_t st, cudaEvent_t before_search = nullptr) {
-    if (n_reads == 0) return;
+// words of the forward strand's found mask for a batch (SearchOut::fmask)
+static uint64_t fmask_words(uint64_t n_reads, uint64_t total_kmers) { return (total_kmers >> 6) + n_reads + 2; }
+
+// what the pipeline writes: dense hits (hit_bytes 4 / 8, d_hits) or runs (hit_bytes 0, sink)
+struct PipelineOut {
+    int hit_bytes = 4;
+    void* d_hits = nullptr;
+    uint64_t* d_fmask = nullptr;
+    RunSink sink{nullptr, nullptr, nullptr, 0};
+};
+
+// pack + k-mer counts + exclusive scan on one stream; every pointer is device memory
+static void launch_prepare(const IndexView& v, const uint8_t* d_ascii, uint64_t n_bases, const uint64_t* d_offsets, uint64_t n_reads,
+                           uint64_t* d_packed, uint64_t* d_out_offsets, void* d_scan_tmp, size_t scan_tmp_bytes,
+                           SearchTotals* d_totals, cudaStream_t st) {
     const uint64_t n_words = (n_bases + 31) / 32 + 1;
-    {
-        const unsigned threads = 256;
-        pack_reads_kernel<<<(unsigned)((n_words + threads - 1) / threads), threads, 0, st>>>(d_ascii, n_bases, d_packed, n_words,
-                                                                                             d_totals);
-        g_launches++;
-        kmer_counts_kernel<<<(unsigned)((n_reads + threads - 1) / threads), threads, 0, st>>>(d_offsets, n_reads, v.k,
-                                                                                              d_out_offsets);
-        g_launches++;
-        FIN_CUDA(cudaGetLastError());
-    }
-    FIN_CUDA(cub::DeviceScan::ExclusiveSum(d_scan_tmp, scan_tmp_bytes, d_out_offsets, d_out_offsets, (int64_t)n_reads, st));
+    const unsigned threads = 256;
+    pack_reads_kernel<<<(unsigned)((n_words + threads - 1) / threads), threads, 0, st>>>(d_ascii, n_bases, d_packed, n_words, d_totals);
+    g_launches++;
+    kmer_counts_kernel<<<(unsigned)((n_reads + 1 + threads - 1) / threads), threads, 0, st>>>(d_offsets, n_reads, n_bases, v.k,
+                                                                                                d_out_offsets, d_totals);
+    g_launches++;
+    FIN_CUDA(cudaGetLastError());
+    FIN_CUDA(cub::DeviceScan::ExclusiveSum(d_scan_tmp, scan_tmp_bytes, d_out_offsets, d_out_offsets, (int64_t)(n_reads + 1), st));
     g_launches += 2;
-    if (before_search) FIN_CUDA(cudaEventRecord(before_search, st));
-    if (hit_bytes == 4) {
-        if (count) launch_search_t<int32_t, true>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, n_strands, st);
-        else launch_search_t<int32_t, false>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, n_strands, st);
-    } else {
-        if (count) launch_search_t<int64_t, true>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, n_strands, st);
-        else launch_search_t<int64_t, false>(v, d_packed, d_offsets, n_reads, d_out_offsets, d_out, d_totals, n_strands, st);
+}
+
+static void launch_search(const IndexView& v, const uint64_t* d_packed, const uint64_t* d_offsets, uint64_t n_reads,
+                          const uint64_t* d_out_offsets, const PipelineOut& po, SearchTotals* d_totals, bool count, int n_strands,
+                          cudaStream_t st) {
+    if (n_reads == 0) return;
+    if (po.hit_bytes == 8) {
+        SearchOut<int64_t> out{reinterpret_cast<HitPair<int64_t>*>(po.d_hits), d_out_offsets, po.d_fmask, po.sink};
+        if (count) launch_search_t<int64_t, true, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
+        else launch_search_t<int64_t, false, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
+        return;
     }
+    SearchOut<int32_t> out{reinterpret_cast<HitPair<int32_t>*>(po.d_hits), d_out_offsets, po.d_fmask, po.sink};
+    if (po.hit_bytes == 4) {
+        if (count) launch_search_t<int32_t, true, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
+        else launch_search_t<int32_t, false, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
+    } else {
+        if (count) launch_search_t<int32_t, true, true>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
+        else launch_search_t<int32_t, false, true>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
+    }
+}
+
+// runs mode, after the record count is known: sort by (read, first k-mer), CSR offsets (+ base)
+static size_t sort_tmp_bytes_for(uint64_t n) {
+    size_t bytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr, (const RunRec*)nullptr, (RunRec*)nullptr,
+                                    (int64_t)n);
+    return bytes + 256;
+}
+
+static void launch_run_sort(const uint64_t* keys_in, uint64_t* keys_out, const RunRec* recs_in, RunRec* recs_out, uint64_t n_runs,
+                            uint64_t n_reads, uint64_t base, uint64_t* d_run_offsets, void* d_tmp, size_t tmp_bytes, cudaStream_t st) {
+    if (n_runs) {
+        const int end_bit = std::min(64, kRunKeyPosBits + std::max(1, bit_length(n_reads)));
+        FIN_CUDA(cub::DeviceRadixSort::SortPairs(d_tmp, tmp_bytes, keys_in, keys_out, recs_in, recs_out, (int64_t)n_runs, 0, end_bit, st));
+        g_launches += (end_bit + 7) / 8 + 1;
+    }
+    const unsigned threads = 256;
+    run_bounds_kernel<<<(unsigned)((n_runs + 1 + threads - 1) / threads), threads, 0, st>>>(keys_out, n_runs, n_reads, base, d_run_offsets);
+    g_launches++;
+    FIN_CUDA(cudaGetLastError());
 }
 
 static size_t scan_tmp_bytes_for(uint64_t n) {
@@ -176,6 +214,7 @@ static size_t scan_tmp_bytes_for(uint64_t n) {
 }
 
 static void check_flags(unsigned flags) {
+    if (flags & kErrBadOffsets) throw arg_error("read_offsets must be non-decreasing and end at n_bases");
     if (flags & kErrBadBase)
         throw domain_error("Error: unknown character in the query (only A, C, G, T are inside the parity domain, common.hh:108-111)");
     if (flags & kErrReadTooLong) throw limit_error("a query sequence is longer than 16777215 bases");
@@ -202,44 +241,106 @@ static void accumulate(const SearchTotals& t, fin_search_counts& c, fin_access_c
 // -------------------------------------------------------------------------------------------------------
 // device-resident batch
 // -------------------------------------------------------------------------------------------------------
+struct EventTimer {  // three events on the default stream: start, before the search kernel, end
+    cudaEvent_t e0 = nullptr, em = nullptr, e1 = nullptr;
+    EventTimer() {
+        FIN_CUDA(cudaEventCreate(&e0));
+        FIN_CUDA(cudaEventCreate(&em));
+        FIN_CUDA(cudaEventCreate(&e1));
+    }
+    ~EventTimer() {
+        cudaEventDestroy(e0);
+        cudaEventDestroy(em);
+        cudaEventDestroy(e1);
+    }
+};
+
+// prepare + the host-side check of what the device found in the caller's offsets; returns the k-mer positions
+uint64_t DeviceIndex::prepare_device_batch(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases) {
+    dev_packed_.ensure((n_bases + 31) / 32 + 2);
+    dev_out_offsets_.ensure(n_reads + 2);
+    const size_t tmp = scan_tmp_bytes_for(n_reads + 1);
+    dev_scan_tmp_.ensure(tmp);
+    dev_totals_.ensure(sizeof(SearchTotals));
+    FIN_CUDA(cudaMemsetAsync(dev_totals_.p, 0, sizeof(SearchTotals), 0));
+    launch_prepare(view_, (const uint8_t*)d_seqs, n_bases, d_read_offsets, n_reads, dev_packed_.p, dev_out_offsets_.p, dev_scan_tmp_.p,
+                   tmp, (SearchTotals*)dev_totals_.p, 0);
+    uint64_t total = 0;
+    unsigned flags = 0;
+    FIN_CUDA(cudaMemcpyAsync(&total, dev_out_offsets_.p + n_reads, 8, cudaMemcpyDeviceToHost, 0));
+    FIN_CUDA(cudaMemcpyAsync(&flags, &((SearchTotals*)dev_totals_.p)->error_flags, 4, cudaMemcpyDeviceToHost, 0));
+    FIN_CUDA(cudaStreamSynchronize(0));
+    check_flags(flags & kErrBadOffsets);
+    if ((total >> 6) + n_reads >= 0xFFFFFFF0ull) throw limit_error("batch too large for one call: split it");
+    dev_fmask_.ensure(fmask_words(n_reads, total));
+    return total;
+}
+
+void DeviceIndex::finish_device_batch(EventTimer& t, fin_search_counts* counts, float* kernel_ms, SearchTotals& tot) {
+    FIN_CUDA(cudaEventRecord(t.e1, 0));
+    FIN_CUDA(cudaMemcpy(&tot, dev_totals_.p, sizeof tot, cudaMemcpyDeviceToHost));
+    FIN_CUDA(cudaEventSynchronize(t.e1));
+    float ms = 0;
+    FIN_CUDA(cudaEventElapsedTime(&ms, t.e0, t.e1));
+    last_timing.pipeline_ms = ms;
+    FIN_CUDA(cudaEventElapsedTime(&last_timing.prepare_ms, t.e0, t.em));
+    FIN_CUDA(cudaEventElapsedTime(&last_timing.search_kernel_ms, t.em, t.e1));
+    if (kernel_ms) *kernel_ms = ms;
+    check_flags(tot.error_flags);
+    fin_search_counts c{};
+    last_access = fin_access_counters{};
+    accumulate(tot, c, last_access);
+    if (counts) *counts = c;
+}
+
 void DeviceIndex::search_device(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases,
                                 uint64_t total_kmers, void* d_out, int hit_bytes, fin_search_counts* counts, float* kernel_ms) {
     if (hit_bytes != 4 && hit_bytes != 8) throw arg_error("hit_bytes must be 4 or 8");
     if (hit_bytes == 4 && !fits32_) throw limit_error("this index needs 64-bit hits");
-    (void)total_kmers;
     FIN_CUDA(cudaSetDevice(device_));
-    dev_packed_.ensure((n_bases + 31) / 32 + 2);
-    dev_out_offsets_.ensure(n_reads + 1);
-    const size_t tmp = scan_tmp_bytes_for(n_reads);
-    dev_scan_tmp_.ensure(tmp);
-    dev_totals_.ensure(sizeof(SearchTotals));
-    FIN_CUDA(cudaMemsetAsync(dev_totals_.p, 0, sizeof(SearchTotals), 0));
-    cudaEvent_t e0, e1, em;
-    FIN_CUDA(cudaEventCreate(&e0));
-    FIN_CUDA(cudaEventCreate(&e1));
-    FIN_CUDA(cudaEventCreate(&em));
-    FIN_CUDA(cudaEventRecord(e0, 0));
-    if (n_reads == 0) FIN_CUDA(cudaEventRecord(em, 0));
-    launch_pipeline(view_, (const uint8_t*)d_seqs, n_bases, d_read_offsets, n_reads, dev_packed_.p, dev_out_offsets_.p,
-                    dev_scan_tmp_.p, tmp, d_out, hit_bytes, (SearchTotals*)dev_totals_.p, count_accesses, 2, 0, em);
-    FIN_CUDA(cudaEventRecord(e1, 0));
-    SearchTotals t;
-    FIN_CUDA(cudaMemcpy(&t, dev_totals_.p, sizeof t, cudaMemcpyDeviceToHost));
-    FIN_CUDA(cudaEventSynchronize(e1));
-    float ms = 0;
-    FIN_CUDA(cudaEventElapsedTime(&ms, e0, e1));
-    last_timing.pipeline_ms = ms;
-    FIN_CUDA(cudaEventElapsedTime(&last_timing.prepare_ms, e0, em));
-    FIN_CUDA(cudaEventElapsedTime(&last_timing.search_kernel_ms, em, e1));
-    cudaEventDestroy(e0);
-    cudaEventDestroy(e1);
-    cudaEventDestroy(em);
-    if (kernel_ms) *kernel_ms = ms;
-    check_flags(t.error_flags);
-    fin_search_counts c{};
-    last_access = fin_access_counters{};
-    accumulate(t, c, last_access);
-    if (counts) *counts = c;
+    EventTimer t;
+    FIN_CUDA(cudaEventRecord(t.e0, 0));
+    const uint64_t total = prepare_device_batch(d_seqs, d_read_offsets, n_reads, n_bases);
+    if (total > total_kmers) throw arg_error("total_kmers (the capacity of d_out) is smaller than the number of k-mer positions of the batch");
+    FIN_CUDA(cudaEventRecord(t.em, 0));
+    PipelineOut po;
+    po.hit_bytes = hit_bytes;
+    po.d_hits = d_out;
+    po.d_fmask = dev_fmask_.p;
+    launch_search(view_, dev_packed_.p, d_read_offsets, n_reads, dev_out_offsets_.p, po, (SearchTotals*)dev_totals_.p, count_accesses, 2, 0);
+    SearchTotals tot;
+    finish_device_batch(t, counts, kernel_ms, tot);
+}
+
+uint64_t DeviceIndex::search_device_runs(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases,
+                                         uint64_t* d_run_offsets, fin_run* d_runs, uint64_t runs_capacity, fin_search_counts* counts,
+                                         float* kernel_ms) {
+    static_assert(sizeof(fin_run) == sizeof(RunRec), "fin_run and RunRec are the same record");
+    FIN_CUDA(cudaSetDevice(device_));
+    EventTimer t;
+    FIN_CUDA(cudaEventRecord(t.e0, 0));
+    prepare_device_batch(d_seqs, d_read_offsets, n_reads, n_bases);
+    dev_keys_a_.ensure(runs_capacity + 1);
+    dev_keys_b_.ensure(runs_capacity + 1);
+    dev_recs_a_.ensure((runs_capacity + 1) * sizeof(RunRec));
+    FIN_CUDA(cudaEventRecord(t.em, 0));
+    PipelineOut po;
+    po.hit_bytes = 0;
+    po.d_fmask = dev_fmask_.p;
+    SearchTotals* dt = (SearchTotals*)dev_totals_.p;
+    po.sink = RunSink{dev_keys_a_.p, (RunRec*)dev_recs_a_.p, &dt->n_runs, runs_capacity};
+    launch_search(view_, dev_packed_.p, d_read_offsets, n_reads, dev_out_offsets_.p, po, dt, count_accesses, 2, 0);
+    uint64_t n_runs = 0;
+    FIN_CUDA(cudaMemcpy(&n_runs, &dt->n_runs, 8, cudaMemcpyDeviceToHost));
+    if (n_runs <= runs_capacity) {
+        const size_t tmp = sort_tmp_bytes_for(n_runs);
+        dev_sort_tmp_.ensure(tmp);
+        launch_run_sort(dev_keys_a_.p, dev_keys_b_.p, (const RunRec*)dev_recs_a_.p, (RunRec*)d_runs, n_runs, n_reads, 0, d_run_offsets,
+                        dev_sort_tmp_.p, tmp, 0);
+    }
+    SearchTotals tot;
+    finish_device_batch(t, counts, kernel_ms, tot);
+    return n_runs;
 }
 
 // -------------------------------------------------------------------------------------------------------
@@ -250,6 +351,88 @@ static constexpr uint64_t kSubBases = 48ull << 20;  // bases per sub-batch
 static constexpr uint64_t kSubReads = 1ull << 19;   // reads per sub-batch
 static constexpr int kSlots = 3;
 
+void DeviceIndex::ensure_slots() {
+    if (slots_.empty()) {
+        for (int i = 0; i < kSlots; i++) {
+            std::unique_ptr<SearchSlot> s(new SearchSlot());
+            FIN_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+            FIN_CUDA(cudaEventCreateWithFlags(&s->counted, cudaEventDisableTiming));
+            FIN_CUDA(cudaEventCreateWithFlags(&s->done, cudaEventDisableTiming));
+            FIN_CUDA(cudaHostAlloc((void**)&s->h_totals, sizeof(SearchTotals), cudaHostAllocDefault));
+            s->totals.alloc(sizeof(SearchTotals));
+            slots_.push_back(std::move(s));
+        }
+    }
+    // a previous call that ended with an exception may have left sub-batches in flight: let them finish and forget them,
+    // so that their copies no longer write into the caller's buffers and their totals never reach this call's counters
+    for (auto& s : slots_) {
+        if (s->busy) cudaStreamSynchronize(s->stream);
+        s->busy = false;
+    }
+}
+
+// drains the pipeline when a call leaves with an exception (the caller's buffers must not be written after the return)
+struct SlotDrain {
+    std::vector<std::unique_ptr<SearchSlot>>& slots;
+    bool armed = true;
+    ~SlotDrain() {
+        if (!armed) return;
+        for (auto& s : slots) {
+            if (s->busy) cudaStreamSynchronize(s->stream);
+            s->busy = false;
+        }
+    }
+};
+
+// sub-batch [r0, r1): at most kSubReads reads and kSubBases bases (always at least one read); validates the offsets
+// of the sub-batch and counts its k-mer positions
+static uint64_t cut_sub_batch(const uint64_t* read_offsets, uint64_t n_reads, uint64_t r0, int k, uint64_t& nkm, uint64_t& max_len) {
+    uint64_t r1 = std::min(n_reads, r0 + kSubReads);
+    const uint64_t base0 = read_offsets[r0];
+    if (read_offsets[r1] >= base0 && read_offsets[r1] - base0 > kSubBases) {
+        const uint64_t* lo = read_offsets + r0 + 1;
+        const uint64_t* hi = read_offsets + r1 + 1;
+        const uint64_t* p = std::upper_bound(lo, hi, base0 + kSubBases);  // first offset beyond the cap
+        r1 = std::max<uint64_t>(r0 + 1, (uint64_t)(p - read_offsets) - 1);
+    }
+    nkm = 0;
+    bool ordered = true;
+    for (uint64_t i = r0; i < r1; i++) {
+        ordered &= read_offsets[i + 1] >= read_offsets[i];
+        const uint64_t len = read_offsets[i + 1] - read_offsets[i];
+        max_len = std::max(max_len, len);
+        nkm += len >= (uint64_t)k ? len - (uint64_t)k + 1 : 0;
+    }
+    if (!ordered) throw arg_error("read_offsets must be non-decreasing");
+    return r1;
+}
+
+// H2D of a sub-batch and its preparation kernels on the slot's stream
+static void stage_sub_batch(const IndexView& v, SearchSlot& s, const char* seqs, const uint64_t* read_offsets, uint64_t r0, uint64_t r1,
+                            uint64_t nkm) {
+    const uint64_t base0 = read_offsets[r0];
+    const uint64_t nr = r1 - r0, nb = read_offsets[r1] - base0;
+    s.r0 = r0; s.nr = nr; s.nb = nb; s.nkm = nkm; s.base0 = base0;
+    s.ascii.ensure(nb + 64);
+    s.packed.ensure((nb + 31) / 32 + 2);
+    s.offsets.ensure(nr + 1);
+    s.out_offsets.ensure(nr + 2);
+    s.fmask.ensure(fmask_words(nr, nkm));
+    const size_t tmp = scan_tmp_bytes_for(nr + 1);
+    s.scan_tmp.ensure(tmp);
+    if (s.h_offsets_cap < nr + 1) {
+        if (s.h_offsets_pinned) cudaFreeHost(s.h_offsets_pinned);
+        s.h_offsets_pinned = nullptr;
+        s.h_offsets_cap = std::max<uint64_t>(nr + 1, kSubReads + 1);
+        FIN_CUDA(cudaHostAlloc((void**)&s.h_offsets_pinned, s.h_offsets_cap * 8, cudaHostAllocDefault));
+    }
+    for (uint64_t i = 0; i <= nr; i++) s.h_offsets_pinned[i] = read_offsets[r0 + i] - base0;
+    FIN_CUDA(cudaMemsetAsync(s.totals.p, 0, sizeof(SearchTotals), s.stream));
+    FIN_CUDA(cudaMemcpyAsync(s.ascii.p, seqs + base0, nb, cudaMemcpyHostToDevice, s.stream));
+    FIN_CUDA(cudaMemcpyAsync(s.offsets.p, s.h_offsets_pinned, (nr + 1) * 8, cudaMemcpyHostToDevice, s.stream));
+    launch_prepare(v, s.ascii.p, nb, s.offsets.p, nr, s.packed.p, s.out_offsets.p, s.scan_tmp.p, tmp, (SearchTotals*)s.totals.p, s.stream);
+}
+
 template <class HitT>
 void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, uint64_t n_reads, HitT* out_pairs,
                               uint64_t out_capacity, fin_search_counts* counts, int n_strands) {
@@ -258,17 +441,8 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
     const int k = view_.k;
     // the offsets are validated and the k-mer positions counted sub-batch by sub-batch while the GPU already works on
     // the previous ones: no pass over the whole batch stands between the call and the first copy
-
-    if (slots_.empty()) {
-        for (int i = 0; i < kSlots; i++) {
-            std::unique_ptr<SearchSlot> s(new SearchSlot());
-            FIN_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-            FIN_CUDA(cudaEventCreateWithFlags(&s->done, cudaEventDisableTiming));
-            FIN_CUDA(cudaHostAlloc((void**)&s->h_totals, sizeof(SearchTotals), cudaHostAllocDefault));
-            s->totals.alloc(sizeof(SearchTotals));
-            slots_.push_back(std::move(s));
-        }
-    }
+    ensure_slots();
+    SlotDrain drain{slots_};
     fin_search_counts c{};
     last_access = fin_access_counters{};
     unsigned flags = 0;
@@ -281,58 +455,22 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
         s.busy = false;
     };
 
-    uint64_t r0 = 0, out_pos = 0;
+    uint64_t r0 = 0, out_pos = 0, max_len = 0;
     int turn = 0;
     while (r0 < n_reads) {
-        // sub-batch [r0, r1): at most kSubReads reads and kSubBases bases (always at least one read)
-        uint64_t r1 = std::min(n_reads, r0 + kSubReads);
-        const uint64_t base0 = read_offsets[r0];
-        if (read_offsets[r1] - base0 > kSubBases) {
-            const uint64_t* lo = read_offsets + r0 + 1;
-            const uint64_t* hi = read_offsets + r1 + 1;
-            const uint64_t* p = std::upper_bound(lo, hi, base0 + kSubBases);  // first offset beyond the cap
-            r1 = std::max<uint64_t>(r0 + 1, (uint64_t)(p - read_offsets) - 1);
-        }
-        const uint64_t nr = r1 - r0, nb = read_offsets[r1] - base0;
         uint64_t nkm = 0;
-        bool ordered = true;
-        for (uint64_t i = r0; i < r1; i++) {
-            ordered &= read_offsets[i + 1] >= read_offsets[i];
-            const uint64_t len = read_offsets[i + 1] - read_offsets[i];
-            nkm += len >= (uint64_t)k ? len - (uint64_t)k + 1 : 0;
-        }
-        if (!ordered || out_pos + nkm > out_capacity) {
-            for (auto& sl : slots_) {  // let the sub-batches in flight finish before reporting
-                if (sl->busy) cudaEventSynchronize(sl->done);
-                sl->busy = false;
-            }
-            if (!ordered) throw arg_error("read_offsets must be non-decreasing");
-            throw arg_error("out_capacity is smaller than the number of k-mer positions of the batch");
-        }
-
+        const uint64_t r1 = cut_sub_batch(read_offsets, n_reads, r0, k, nkm, max_len);
+        if (out_pos + nkm > out_capacity) throw arg_error("out_capacity is smaller than the number of k-mer positions of the batch");
         SearchSlot& s = *slots_[turn % kSlots];
         turn++;
         retire(s);
-        s.ascii.ensure(nb + 64);
-        s.packed.ensure((nb + 31) / 32 + 2);
-        s.offsets.ensure(nr + 1);
-        s.out_offsets.ensure(nr + 1);
-        const size_t tmp = scan_tmp_bytes_for(nr);
-        s.scan_tmp.ensure(tmp);
         s.hits.ensure(std::max<uint64_t>(nkm, 1) * 2 * sizeof(HitT));
-        if (s.h_offsets_cap < nr + 1) {
-            if (s.h_offsets_pinned) cudaFreeHost(s.h_offsets_pinned);
-            s.h_offsets_pinned = nullptr;
-            s.h_offsets_cap = std::max<uint64_t>(nr + 1, kSubReads + 1);
-            FIN_CUDA(cudaHostAlloc((void**)&s.h_offsets_pinned, s.h_offsets_cap * 8, cudaHostAllocDefault));
-        }
-        for (uint64_t i = 0; i <= nr; i++) s.h_offsets_pinned[i] = read_offsets[r0 + i] - base0;
-
-        FIN_CUDA(cudaMemsetAsync(s.totals.p, 0, sizeof(SearchTotals), s.stream));
-        FIN_CUDA(cudaMemcpyAsync(s.ascii.p, seqs + base0, nb, cudaMemcpyHostToDevice, s.stream));
-        FIN_CUDA(cudaMemcpyAsync(s.offsets.p, s.h_offsets_pinned, (nr + 1) * 8, cudaMemcpyHostToDevice, s.stream));
-        launch_pipeline(view_, s.ascii.p, nb, s.offsets.p, nr, s.packed.p, s.out_offsets.p, s.scan_tmp.p, tmp, s.hits.p,
-                        (int)sizeof(HitT), (SearchTotals*)s.totals.p, count_accesses, n_strands, s.stream);
+        stage_sub_batch(view_, s, seqs, read_offsets, r0, r1, nkm);
+        PipelineOut po;
+        po.hit_bytes = (int)sizeof(HitT);
+        po.d_hits = s.hits.p;
+        po.d_fmask = s.fmask.p;
+        launch_search(view_, s.packed.p, s.offsets.p, s.nr, s.out_offsets.p, po, (SearchTotals*)s.totals.p, count_accesses, n_strands, s.stream);
         if (nkm)
             FIN_CUDA(cudaMemcpyAsync(out_pairs + 2 * out_pos, s.hits.p, nkm * 2 * sizeof(HitT), cudaMemcpyDeviceToHost, s.stream));
         FIN_CUDA(cudaMemcpyAsync(s.h_totals, s.totals.p, sizeof(SearchTotals), cudaMemcpyDeviceToHost, s.stream));
@@ -342,11 +480,99 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
         r0 = r1;
     }
     for (auto& s : slots_) retire(*s);
+    drain.armed = false;
     check_flags(flags);
     if (counts) *counts = c;
 }
 
 template void DeviceIndex::search_host<int32_t>(const char*, const uint64_t*, uint64_t, int32_t*, uint64_t, fin_search_counts*, int);
 template void DeviceIndex::search_host<int64_t>(const char*, const uint64_t*, uint64_t, int64_t*, uint64_t, fin_search_counts*, int);
+
+// -------------------------------------------------------------------------------------------------------
+// host batch, answers as runs.  Per sub-batch: (A) copy in, pack, search -> appended records + their count;
+// (B) once the count is on the host: sort by (read, first k-mer), CSR offsets, copy out.  B of sub-batch i is
+// issued after A of sub-batch i+1, so the GPU always has the next search queued while the host waits for a count.
+// -------------------------------------------------------------------------------------------------------
+uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_offsets, uint64_t n_reads, uint64_t* run_offsets,
+                                       fin_run* runs, uint64_t runs_capacity, fin_search_counts* counts) {
+    FIN_CUDA(cudaSetDevice(device_));
+    const int k = view_.k;
+    ensure_slots();
+    SlotDrain drain{slots_};
+    fin_search_counts c{};
+    last_access = fin_access_counters{};
+    unsigned flags = 0;
+    uint64_t run_pos = 0;
+
+    auto launch_a = [&](SearchSlot& s) {
+        PipelineOut po;
+        po.hit_bytes = 0;
+        po.d_fmask = s.fmask.p;
+        SearchTotals* dt = (SearchTotals*)s.totals.p;
+        po.sink = RunSink{s.keys_a.p, s.recs_a.p, &dt->n_runs, std::min<uint64_t>(s.keys_a.n, s.recs_a.n)};
+        launch_search(view_, s.packed.p, s.offsets.p, s.nr, s.out_offsets.p, po, dt, count_accesses, 2, s.stream);
+        FIN_CUDA(cudaMemcpyAsync(s.h_totals, s.totals.p, sizeof(SearchTotals), cudaMemcpyDeviceToHost, s.stream));
+        FIN_CUDA(cudaEventRecord(s.counted, s.stream));
+    };
+    auto ensure_runs = [&](SearchSlot& s, uint64_t n) {
+        s.keys_a.ensure(n);
+        s.keys_b.ensure(n);
+        s.recs_a.ensure(n);
+        s.recs_b.ensure(n);
+    };
+    auto phase_b = [&](SearchSlot& s) {
+        FIN_CUDA(cudaEventSynchronize(s.counted));
+        uint64_t n = s.h_totals->n_runs;
+        if (n > std::min<uint64_t>(s.keys_a.n, s.recs_a.n)) {  // more runs than the slot had room for: search again with enough
+            flags |= s.h_totals->error_flags;
+            FIN_CUDA(cudaStreamSynchronize(s.stream));
+            ensure_runs(s, n + n / 8 + 1024);
+            FIN_CUDA(cudaMemsetAsync(s.totals.p, 0, sizeof(SearchTotals), s.stream));
+            launch_a(s);
+            FIN_CUDA(cudaEventSynchronize(s.counted));
+            n = s.h_totals->n_runs;
+        }
+        flags |= s.h_totals->error_flags;
+        accumulate(*s.h_totals, c, last_access);
+        const size_t tmp = sort_tmp_bytes_for(n);
+        s.sort_tmp.ensure(tmp);
+        s.run_offsets.ensure(s.nr + 2);
+        launch_run_sort(s.keys_a.p, s.keys_b.p, s.recs_a.p, s.recs_b.p, n, s.nr, run_pos, s.run_offsets.p, s.sort_tmp.p, tmp, s.stream);
+        FIN_CUDA(cudaMemcpyAsync(run_offsets + s.r0, s.run_offsets.p, (s.nr + 1) * 8, cudaMemcpyDeviceToHost, s.stream));
+        if (n && run_pos + n <= runs_capacity)
+            FIN_CUDA(cudaMemcpyAsync(runs + run_pos, s.recs_b.p, n * sizeof(RunRec), cudaMemcpyDeviceToHost, s.stream));
+        FIN_CUDA(cudaEventRecord(s.done, s.stream));
+        run_pos += n;
+    };
+
+    if (n_reads == 0) run_offsets[0] = 0;
+    uint64_t r0 = 0, max_len = 0;
+    int turn = 0;
+    SearchSlot* prev = nullptr;
+    while (r0 < n_reads) {
+        uint64_t nkm = 0;
+        const uint64_t r1 = cut_sub_batch(read_offsets, n_reads, r0, k, nkm, max_len);
+        SearchSlot& s = *slots_[turn % kSlots];
+        turn++;
+        if (s.busy) FIN_CUDA(cudaEventSynchronize(s.done));  // its phase B was issued two turns ago
+        s.busy = false;
+        ensure_runs(s, nkm / 16 + 4096);
+        stage_sub_batch(view_, s, seqs, read_offsets, r0, r1, nkm);
+        launch_a(s);
+        s.busy = true;
+        if (prev) phase_b(*prev);
+        prev = &s;
+        r0 = r1;
+    }
+    if (prev) phase_b(*prev);
+    for (auto& s : slots_) {
+        if (s->busy) FIN_CUDA(cudaEventSynchronize(s->done));
+        s->busy = false;
+    }
+    drain.armed = false;
+    check_flags(flags);
+    if (counts) *counts = c;
+    return run_pos;
+}
 
 }  // namespace fin

@@ -20,9 +20,10 @@ struct SearchTotals {  // device-side accumulators of one launch
     unsigned int error_flags;  // bit 0: non-ACGT base; bit 1: candidate window underflow; bit 2: lookup out of range
     unsigned int pad;
     unsigned long long next_read;  // work counter of the persistent search kernel
+    unsigned long long n_runs;     // runs mode: records appended (RunSink::count)
 };
 
-enum : unsigned { kErrBadBase = 1u, kErrWindowUnderflow = 2u, kErrLookupRange = 4u, kErrReadTooLong = 8u };
+enum : unsigned { kErrBadBase = 1u, kErrWindowUnderflow = 2u, kErrLookupRange = 4u, kErrReadTooLong = 8u, kErrBadOffsets = 16u };
 
 struct ReadCounters {  // per-thread tallies, reduced per warp at the end of the kernel
     unsigned found[2] = {0, 0}, positive = 0, n_q = 0, err = 0;
@@ -72,11 +73,24 @@ static __global__ void pack_reads_kernel(const uint8_t* __restrict__ ascii, uint
     if (bad) atomicOr(&totals->error_flags, kErrBadBase);
 }
 
-static __global__ void kmer_counts_kernel(const uint64_t* __restrict__ read_offsets, uint64_t n_reads, int k,
-                                   uint64_t* __restrict__ counts) {
+// k-mer positions per read (counts[n_reads] = 0 so that the exclusive scan ends with the total); also checks that the
+// offsets are non-decreasing and end at n_bases (the device entry points cannot trust their caller's arrays).
+static __global__ void kmer_counts_kernel(const uint64_t* __restrict__ read_offsets, uint64_t n_reads, uint64_t n_bases, int k,
+                                   uint64_t* __restrict__ counts, SearchTotals* __restrict__ totals) {
     const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n_reads) return;
-    const uint64_t len = read_offsets[r + 1] - read_offsets[r];
+    if (r > n_reads) return;
+    if (r == n_reads) {
+        counts[r] = 0;
+        if (read_offsets[r] != n_bases) atomicOr(&totals->error_flags, kErrBadOffsets);
+        return;
+    }
+    const uint64_t a = read_offsets[r], b = read_offsets[r + 1];
+    if (b < a || b > n_bases) {
+        atomicOr(&totals->error_flags, kErrBadOffsets);
+        counts[r] = 0;
+        return;
+    }
+    const uint64_t len = b - a;
     counts[r] = len >= (uint64_t)k ? len - (uint64_t)k + 1 : 0;
 }
 
@@ -167,22 +181,8 @@ FIN_D Ival drop_first_char(const IndexView& ix, const int new_len, Ival I, unsig
     return I;
 }
 
-template <class HitT> struct alignas(2 * sizeof(HitT)) HitPair { HitT unitig, pos; };
 
-// Hits are written once and never read again by the kernel (except the reverse strand's look at its own read's slots):
-// with FIN_STREAM_STORES they are stored evict-first so that 8 bytes per k-mer of output do not push the index out of the L2.
-template <class HitT> FIN_D void store_hit(HitPair<HitT>* dst, const HitPair<HitT> h) {
-#if defined(FIN_STREAM_STORES) && !defined(FIN_EMU)
-    if (sizeof(HitT) == 4) {
-        __stcs(reinterpret_cast<int2*>(dst), make_int2((int)h.unitig, (int)h.pos));
-    } else {
-        __stcs(reinterpret_cast<long long*>(dst), (long long)h.unitig);
-        __stcs(reinterpret_cast<long long*>(dst) + 1, (long long)h.pos);
-    }
-#else
-    *dst = h;
-#endif
-}
+template <class HitT> struct alignas(2 * sizeof(HitT)) HitPair { HitT unitig, pos; };
 
 // Candidate finimizers are packed into one u64 so that the unsigned order equals the reference's tuple
 // order (freq, len, colex, end) with freq == 1 throughout (common.hh:84,147): len:8 | colex:32 | end:24.
@@ -195,6 +195,56 @@ FIN_D int cand_end(uint64_t c) { return (int)(c & 0xFFFFFFu); }
 FIN_D int cand_start(uint64_t c) { return cand_end(c) - cand_len(c) + 1; }
 
 constexpr int kMaxReadLen = (1 << 24) - 1;
+
+// ---- run-length hits ------------------------------------------------------------------------------------------
+// 98 % of the found k-mers of a read are produced by walk_in_unitigs (FinimizerIndex.hh:47-102): consecutive k-mer
+// positions that map to consecutive offsets of one unitig.  A run record says exactly that for a maximal stretch the
+// search produced in one go: merged k-mer positions [i0, i0 + len) of the read map to `unitig`, position i0 + d at
+// offset pos0 + d (forward strand) or pos0 - d (reverse-complement strand: the merged position runs against the
+// strand's own direction, search_fmin.hh:54-60).  Runs of one read never overlap (the reverse strand only reports
+// positions the forward strand missed), every position outside a run is (-1,-1).  Same layout as fin_run in
+// include/finito_b200.h.
+struct RunRec {
+    uint32_t i0, len_rc /* len | rc << 31 */, unitig, pos0;
+};
+constexpr uint32_t kRunRc = 0x80000000u;
+constexpr int kRunKeyPosBits = 24;  // sort key of a record: read << 24 | i0  (i0 <= kMaxReadLen)
+
+// where the search kernel appends its records: struct of arrays (cub sorts keys + values), one counter
+struct RunSink {
+    uint64_t* keys;
+    RunRec* recs;
+    unsigned long long* count;  // records produced (keeps counting past the capacity: the caller retries)
+    uint64_t capacity;
+};
+
+// Appends one record per lane that has one.  Called by every lane of the warp at the same point (converged).
+FIN_D void run_append(const RunSink& sink, const bool want, const uint64_t key, const RunRec rec) {
+#ifdef FIN_EMU
+    if (want) {
+        const uint64_t t = (*sink.count)++;
+        if (t < sink.capacity) {
+            sink.keys[t] = key;
+            sink.recs[t] = rec;
+        }
+    }
+#else
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, want);
+    if (m == 0) return;
+    const unsigned lane = threadIdx.x & 31u;
+    const int leader = __ffs((int)m) - 1;
+    unsigned long long base = 0;
+    if ((int)lane == leader) base = atomicAdd(sink.count, (unsigned long long)__popc(m));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (want) {
+        const uint64_t t = base + (uint64_t)__popc(m & ((1u << lane) - 1u));
+        if (t < sink.capacity) {
+            sink.keys[t] = key;
+            *reinterpret_cast<uint4*>(sink.recs + t) = make_uint4(rec.i0, rec.len_rc, rec.unitig, rec.pos0);
+        }
+    }
+#endif
+}
 
 // ---- one chain = one read, both strands, as a flattened state machine ------------------------------------------
 // The reference's loop nest (per character: contract-and-retry loops for the finimizer interval and the k-mer
@@ -212,7 +262,7 @@ constexpr int kMaxReadLen = (1 << 24) - 1;
 // Every lane of the warp calls step() in every iteration, so the phases can be fenced with warp barriers: they keep
 // the compiler from threading a phase into the branches of the one before it (which would execute it once per
 // incoming path, each time for a few lanes).
-#if defined(FIN_EMU) || defined(FIN_NO_FENCE)
+#if defined(FIN_EMU)
 #define FIN_PHASE_FENCE() do {} while (0)
 #else
 #define FIN_PHASE_FENCE() __syncwarp()
@@ -220,23 +270,29 @@ constexpr int kMaxReadLen = (1 << 24) - 1;
 
 enum : int { ST_EXT = 0, ST_EXTK = 1, ST_POST = 2, ST_SHRINK = 3, ST_EMIT = 4, ST_IDLE = 5 };
 
-// FIN_DQ_SHARED: for k <= 32 the candidate ring lives in shared memory, slot i of thread t at [i * blockDim + t] (no bank
-// conflicts when the lanes touch the same slot); otherwise it is a thread-local array (stride 1).
-#if defined(FIN_DQ_SHARED) && !defined(FIN_EMU)
-#define FIN_DQ_STRIDE(KCAP) ((KCAP) == 32 ? FIN_SEARCH_THREADS : 1)
-#else
-#define FIN_DQ_STRIDE(KCAP) 1
-#endif
 #ifndef FIN_SEARCH_THREADS
 #define FIN_SEARCH_THREADS 128
 #endif
 
-template <int KCAP, class HitT, bool COUNT> struct Chain {
+// Where a chain's answers go.  Dense: one HitPair per k-mer position (out + out_offsets[read]).  Runs: RunSink.
+// Both: `fmask`, one bit per k-mer position = "the forward strand found it", so that the reverse strand can apply
+// the merge rule (search_fmin.hh:54-60) without reading the forward strand's hits back.  The current 64-bit word
+// lives in a register; words are only spilled to `fmask` for reads with more than 64 k-mer positions.
+template <class HitT> struct SearchOut {
+    HitPair<HitT>* hits;        // dense mode (RUNS == false)
+    const uint64_t* out_offsets;
+    uint64_t* fmask;            // (total_kmers >> 6) + n_reads + 1 words; read r starts at (out_offsets[r] >> 6) + r
+    RunSink sink;               // runs mode
+};
+
+template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
     static constexpr bool WIDE = KCAP > 128;
-    static constexpr int DQS = FIN_DQ_STRIDE(KCAP);
     // the read
     uint64_t b0 = 0;
-    HitPair<HitT>* o = nullptr;
+    HitPair<HitT>* o = nullptr;  // dense mode: the read's slots
+    uint32_t rid = 0;            // runs mode: the read's index in the batch
+    uint32_t fmw = 0;            // first word of the read in SearchOut::fmask
+    uint64_t fm = 0;             // current word of the forward strand's found mask
     int len = 0, nk = 0, strand = 0;
     // stream state (common.hh:80-103)
     int st = ST_IDLE, end = 0, c = 0;
@@ -256,51 +312,33 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
     uint32_t walk_uid = 0;
     uint64_t tword = 0;
     int walk_j = 0;
-#ifdef FIN_BASE_WORD_CACHE
-    uint32_t bw = 0;          // the 16 packed bases around the current position
-#endif
+    int run_len = 0;          // runs mode: length of the open run (it ends at the previous k-mer position)
     uint64_t fr = 0, bk = 0;  // front and back of the candidate window, cached in registers
-#ifdef FIN_BK2
-    uint64_t bk2 = 0;         // the entry below the back, or 0 when not cached
-#endif
 
-    FIN_D void begin_strand(const IndexView& ix, const uint64_t* __restrict__ packed) {
+    FIN_D void begin_strand(const IndexView& ix) {
         start = kmer_start = 0;
         I.l = 0; I.r = ix.n_nodes - 1;
         Ik = I;
         dq_head = dq_n = 0;
-#ifdef FIN_BK2
-        bk2 = 0;
-#endif
         bestU_pos = -1;
         walking = false;
         pendI = pendK = 0;
         end = 0;
         fresh = true;
+        run_len = 0;
         st = ST_EXT;
     }
 
     // 2-bit code of the character at `end` of the current strand (reverse complement: read backwards, complemented)
     FIN_D void fetch_base(const uint64_t* __restrict__ packed) {
         const uint64_t b = b0 + (uint64_t)(strand ? len - 1 - end : end);
-#if defined(FIN_BASES_NO_L1) && !defined(FIN_EMU)
-        uint32_t w;  // streamed once: do not spend L1 lines on the reads, the index lines live there
-        asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(w) : "l"(reinterpret_cast<const uint32_t*>(packed) + (b >> 4)));
-#else
-#ifdef FIN_BASE_WORD_CACHE
-        // 16 bases per 32-bit word: reload only when the position enters a new word (or a strand begins)
-        if (end == 0 || (b & 15) == (strand ? 15u : 0u)) bw = __ldg(reinterpret_cast<const uint32_t*>(packed) + (b >> 4));
-        const uint32_t w = bw;
-#else
         const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(packed) + (b >> 4));
-#endif
-#endif
         c = (int)((w >> (2 * (b & 15))) & 3u) ^ (strand ? 3 : 0);
     }
 
     // takes a new read; returns false (and stays idle) when the read has no k-mer
-    FIN_D bool begin_read(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t base, const uint64_t len64,
-                          HitPair<HitT>* out, ReadCounters& rc) {
+    FIN_D bool begin_read(const IndexView& ix, const uint64_t base, const uint64_t len64, const uint64_t read,
+                          const SearchOut<HitT>& out, ReadCounters& rc) {
         st = ST_IDLE;
         if (len64 > (uint64_t)kMaxReadLen) {
             rc.err |= kErrReadTooLong;
@@ -311,9 +349,13 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
         len = (int)len64;
         nk = len - ix.k + 1;
         rc.n_q += (unsigned)nk;
-        o = out;
+        const uint64_t oo = __ldg(out.out_offsets + read);
+        if (!RUNS) o = out.hits + oo;
+        rid = (uint32_t)read;
+        fmw = (uint32_t)((oo >> 6) + read);
+        fm = 0;
         strand = 0;
-        begin_strand(ix, packed);
+        begin_strand(ix);
         return true;
     }
 
@@ -321,12 +363,13 @@ template <int KCAP, class HitT, bool COUNT> struct Chain {
     FIN_D void set_drop_K(const int new_len) { lenK = new_len; pendK = kDropLeft | kDropRight; }
 
     // dq: the KCAP slots of the candidate window, a separate array so that the scalar state stays in registers
-    FIN_D void step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc, const int n_strands, uint64_t* dq);
+    FIN_D void step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc, const int n_strands, uint64_t* dq,
+                    const SearchOut<HitT>& out);
 };
 
-template <int KCAP, class HitT, bool COUNT>
-FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc,
-                                          const int n_strands, uint64_t* dq) {
+template <int KCAP, class HitT, bool COUNT, bool RUNS>
+FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc,
+                                                const int n_strands, uint64_t* dq, const SearchOut<HitT>& out) {
     const int k = ix.k;
     const idx_t N = ix.n_nodes;
 
@@ -407,11 +450,11 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         const idx_t il = I.l, ir = I.r + 1, kl = Ik.l, kr = Ik.r + 1;
         uint32_t uw = 0;
         uint64_t w_il = 0, w_ir = 0, w_kl = 0, w_kr = 0;
-        if (single) uw = ldg_line_u32(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
-        if (pendI & kDropLeft) w_il = ldg_line_u64(lw + lcs_word_index(il));
-        if (pendI & kDropRight) w_ir = ldg_line_u64(lw + lcs_word_index(ir));
-        if (pendK & kDropLeft) w_kl = ldg_line_u64(lw + lcs_word_index(kl));
-        if (pendK & kDropRight) w_kr = ldg_line_u64(lw + lcs_word_index(kr));
+        if (single) uw = __ldg(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
+        if (pendI & kDropLeft) w_il = __ldg(lw + lcs_word_index(il));
+        if (pendI & kDropRight) w_ir = __ldg(lw + lcs_word_index(ir));
+        if (pendK & kDropLeft) w_kl = __ldg(lw + lcs_word_index(kl));
+        if (pendK & kDropRight) w_kr = __ldg(lw + lcs_word_index(kr));
         if (single) {
             if (COUNT) rc.c_ustart++;
             if ((uw >> (ucol & 31)) & 1u) {
@@ -419,32 +462,23 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                 bestU_col = ucol;
             }
         }
-#ifdef FIN_BRANCHY_DROPS
-        if (pendI & kDropLeft) drop_left<WIDE, COUNT>(w_il, I, lenI, pendI, rc.c_lcs);
-        if (pendI & kDropRight) drop_right<WIDE, COUNT>(w_ir, I, lenI, pendI, N, rc.c_lcs);
-        if (pendK & kDropLeft) drop_left<WIDE, COUNT>(w_kl, Ik, lenK, pendK, rc.c_lcs);
-        if (pendK & kDropRight) drop_right<WIDE, COUNT>(w_kr, Ik, lenK, pendK, N, rc.c_lcs);
-#else
         // all four word steps computed by every lane, committed by select: no divergent regions in this phase
-        {
-            bool f_il, f_ir, f_kl, f_kr;
-            const idx_t n_il = drop_left_word<WIDE>(w_il, I.l, lenI, f_il), n_ir = drop_right_word<WIDE>(w_ir, I.r, lenI, f_ir);
-            const idx_t n_kl = drop_left_word<WIDE>(w_kl, Ik.l, lenK, f_kl), n_kr = drop_right_word<WIDE>(w_kr, Ik.r, lenK, f_kr);
-            const bool d_il = pendI & kDropLeft, d_ir = pendI & kDropRight, d_kl = pendK & kDropLeft, d_kr = pendK & kDropRight;
-            if (COUNT) {
-                if (d_il) rc.c_lcs += (I.l - n_il) + (f_il && n_il > 0 ? 1u : 0u);
-                if (d_ir) rc.c_lcs += (n_ir - I.r) + (f_ir && n_ir < N - 1 ? 1u : 0u);
-                if (d_kl) rc.c_lcs += (Ik.l - n_kl) + (f_kl && n_kl > 0 ? 1u : 0u);
-                if (d_kr) rc.c_lcs += (n_kr - Ik.r) + (f_kr && n_kr < N - 1 ? 1u : 0u);
-            }
-            I.l = d_il ? n_il : I.l;
-            I.r = d_ir ? n_ir : I.r;
-            Ik.l = d_kl ? n_kl : Ik.l;
-            Ik.r = d_kr ? n_kr : Ik.r;
-            pendI &= ~((d_il && f_il ? kDropLeft : 0u) | (d_ir && f_ir ? kDropRight : 0u));
-            pendK &= ~((d_kl && f_kl ? kDropLeft : 0u) | (d_kr && f_kr ? kDropRight : 0u));
+        bool f_il, f_ir, f_kl, f_kr;
+        const idx_t n_il = drop_left_word<WIDE>(w_il, I.l, lenI, f_il), n_ir = drop_right_word<WIDE>(w_ir, I.r, lenI, f_ir);
+        const idx_t n_kl = drop_left_word<WIDE>(w_kl, Ik.l, lenK, f_kl), n_kr = drop_right_word<WIDE>(w_kr, Ik.r, lenK, f_kr);
+        const bool d_il = pendI & kDropLeft, d_ir = pendI & kDropRight, d_kl = pendK & kDropLeft, d_kr = pendK & kDropRight;
+        if (COUNT) {
+            if (d_il) rc.c_lcs += (I.l - n_il) + (f_il && n_il > 0 ? 1u : 0u);
+            if (d_ir) rc.c_lcs += (n_ir - I.r) + (f_ir && n_ir < N - 1 ? 1u : 0u);
+            if (d_kl) rc.c_lcs += (Ik.l - n_kl) + (f_kl && n_kl > 0 ? 1u : 0u);
+            if (d_kr) rc.c_lcs += (n_kr - Ik.r) + (f_kr && n_kr < N - 1 ? 1u : 0u);
         }
-#endif
+        I.l = d_il ? n_il : I.l;
+        I.r = d_ir ? n_ir : I.r;
+        Ik.l = d_kl ? n_kl : Ik.l;
+        Ik.r = d_kr ? n_kr : Ik.r;
+        pendI &= ~((d_il && f_il ? kDropLeft : 0u) | (d_ir && f_ir ? kDropRight : 0u));
+        pendK &= ~((d_kl && f_kl ? kDropLeft : 0u) | (d_kr && f_kr ? kDropRight : 0u));
     }
     FIN_PHASE_FENCE();
 
@@ -457,32 +491,18 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         } else {
             // monotone window: drop the candidates that are larger than the new one, then append it.  Front and
             // back live in registers, so only a pop touches the slots.
-#ifdef FIN_BK2
-            // the entry below the back is usually known (it was the back before the last push): the first pop then
-            // needs no load from the ring.  bk2 == 0 means "not cached" (a candidate is never 0: its length is >= 1).
-            if (dq_n > 0 && bk > cur) {
-                dq_n--;
-                if (dq_n > 0) {
-                    if (bk2 == 0) bk2 = dq[((dq_head + dq_n - 1) & (KCAP - 1)) * DQS];
-                    bk = bk2;
-                }
-                bk2 = 0;
-            }
-#endif
             while (dq_n > 0 && bk > cur) {
                 dq_n--;
-                if (dq_n > 0) bk = dq[((dq_head + dq_n - 1) & (KCAP - 1)) * DQS];
+                if (dq_n > 0) bk = dq[(dq_head + dq_n - 1) & (KCAP - 1)];
             }
-#ifndef FIN_DQ_NO_RESET
             // an empty ring restarts at slot 0: the live entries then stay in the first few slots instead of rotating
             // through all KCAP of them, which keeps the thread-local footprint (and its share of the L1) small
             if (dq_n == 0) dq_head = 0;
-#endif
             if (dq_n == KCAP) {  // only entries that left the window can fill the ring: expire them now
                 while (dq_n > 0 && cand_start(fr) < kmer_start) {
                     dq_head = (dq_head + 1) & (KCAP - 1);
                     dq_n--;
-                    if (dq_n > 0) fr = dq[dq_head * DQS];
+                    if (dq_n > 0) fr = dq[dq_head];
                 }
                 if (dq_n == KCAP) {  // cannot happen for live entries; keeps memory safe out of domain
                     rc.err |= kErrWindowUnderflow;
@@ -490,10 +510,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                     bk = 0;
                 }
             }
-            dq[((dq_head + dq_n) & (KCAP - 1)) * DQS] = cur;
-#ifdef FIN_BK2
-            bk2 = dq_n > 0 ? bk : 0;
-#endif
+            dq[(dq_head + dq_n) & (KCAP - 1)] = cur;
             dq_n++;
             bk = cur;
             if (dq_n == 1) fr = cur;
@@ -503,6 +520,8 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
 
     FIN_PHASE_FENCE();
     // ---- E: emission (:170-182), resolve (FinimizerIndex.hh:148-183), next character
+    bool rec_want = false, strand_done = false;  // runs mode: a run was closed by this position / the strand ends here
+    RunRec rec{0, 0, 0, 0};
     if (st == ST_EMIT && (pendI | pendK) == 0) {
         if (COUNT) rc.c_bases++;
         bool present = false;
@@ -512,14 +531,9 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         while (dq_n > 0 && cand_start(fr) < kmer_start) {
             dq_head = (dq_head + 1) & (KCAP - 1);
             dq_n--;
-            if (dq_n > 0) fr = dq[dq_head * DQS];
+            if (dq_n > 0) fr = dq[dq_head];
         }
-#ifndef FIN_DQ_NO_RESET
         if (dq_n == 0) dq_head = 0;
-#endif
-#ifdef FIN_BK2
-        if (dq_n < 2) bk2 = 0;
-#endif
         if (emit) {
             present = true;
             if (dq_n > 0) {
@@ -532,7 +546,10 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
         }
         if (end >= k - 1) {
             if (COUNT) rc.c_kmers++;
-            bool hit = false;
+            // the previous position's answer (meaningful while a run is open)
+            const uint32_t p_uid = walk_uid;
+            const idx_t p_pos = walk_g - (idx_t)(k - 1) - walk_ustart;
+            bool hit = false, walked = false;
             if (walking) {  // walk_in_unitigs: next query base against the next text base
                 const idx_t tp = walk_g + 1;
                 bool match = false;
@@ -544,7 +561,7 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                 if (match) {
                     walk_g = tp;
                     walk_j++;
-                    hit = true;
+                    hit = walked = true;
                 } else {
                     walking = false;
                 }
@@ -581,65 +598,86 @@ FIN_D void Chain<KCAP, HitT, COUNT>::step(const IndexView& ix, const uint64_t* _
                     if (walking && g + 1 < walk_uend) tword = __ldg(ix.text + ((g + 1) >> 5));
                 }
             }
+            // merge (search_fmin.hh:54-60): the forward answer wins; the reverse strand reports position
+            // i = nk - 1 - j only where the forward strand's found mask has no bit
             const int j = end - (k - 1);
+            const int i = strand ? nk - 1 - j : j;
+            bool take = hit;
             if (strand == 0) {
+                fm |= (uint64_t)hit << (j & 63);
+                if ((j & 63) == 63 && j != nk - 1) {  // the last word stays in the register for the reverse strand
+                    out.fmask[fmw + (uint32_t)(j >> 6)] = fm;
+                    fm = 0;
+                }
+            } else {
+                take = hit && !((fm >> (i & 63)) & 1u);
+                if ((i & 63) == 0 && i > 0) fm = out.fmask[fmw + (uint32_t)(i >> 6) - 1u];
+            }
+            rc.found[0] += hit && strand == 0 ? 1u : 0u;
+            rc.found[1] += hit && strand != 0 ? 1u : 0u;
+            rc.positive += take ? 1u : 0u;
+            const idx_t pos = walk_g - (idx_t)(k - 1) - walk_ustart;
+            if (!RUNS) {
                 HitPair<HitT> h;
-                h.unitig = hit ? (HitT)walk_uid : (HitT)-1;
-                h.pos = hit ? (HitT)(walk_g - (idx_t)(k - 1) - walk_ustart) : (HitT)-1;
-                store_hit(o + j, h);
-                if (hit) {
-                    rc.found[0]++;
-                    rc.positive++;
+                h.unitig = take ? (HitT)walk_uid : (HitT)-1;
+                h.pos = take ? (HitT)pos : (HitT)-1;
+                if (strand == 0 || take) o[i] = h;
+            } else {
+                const bool cont = take && walked && run_len > 0;
+                if (run_len > 0 && !cont) {  // the open run ended at the previous position j - 1
+                    rec_want = true;
+                    rec.len_rc = (uint32_t)run_len | (strand ? kRunRc : 0u);
+                    rec.unitig = p_uid;
+                    rec.i0 = strand ? (uint32_t)(i + 1) : (uint32_t)(j - run_len);
+                    rec.pos0 = strand ? (uint32_t)p_pos : (uint32_t)p_pos - (uint32_t)(run_len - 1);
                 }
-            } else if (hit) {  // merge: the forward answer wins (search_fmin.hh:54-60)
-                rc.found[1]++;
-                const int i = nk - 1 - j;
-                if (o[i].unitig == (HitT)-1) {
-                    HitPair<HitT> h;
-                    h.unitig = (HitT)walk_uid;
-                    h.pos = (HitT)(walk_g - (idx_t)(k - 1) - walk_ustart);
-                    store_hit(o + i, h);
-                    rc.positive++;
-                }
+                run_len = take ? (cont ? run_len + 1 : 1) : 0;
             }
         }
         end++;
         if (end == len) {
-            strand++;
-            if (strand < n_strands) begin_strand(ix, packed);
-            else st = ST_IDLE;
+            strand_done = true;
         } else {
             fresh = true;
             st = ST_EXT;
         }
+    }
+    if (RUNS) {
+        FIN_PHASE_FENCE();
+        run_append(out.sink, rec_want, ((uint64_t)rid << kRunKeyPosBits) | rec.i0, rec);
+        // the run that is still open when the strand ends (its last position is the strand's last k-mer)
+        const bool tail = strand_done && run_len > 0;
+        if (tail) {
+            const uint32_t pos = walk_g - (idx_t)(k - 1) - walk_ustart;
+            rec.len_rc = (uint32_t)run_len | (strand ? kRunRc : 0u);
+            rec.unitig = walk_uid;
+            rec.i0 = strand ? 0u : (uint32_t)(nk - run_len);
+            rec.pos0 = strand ? pos : pos - (uint32_t)(run_len - 1);
+        }
+        run_append(out.sink, tail, ((uint64_t)rid << kRunKeyPosBits) | rec.i0, rec);
+    }
+    if (strand_done) {
+        strand++;
+        if (strand < n_strands) begin_strand(ix);
+        else st = ST_IDLE;
     }
 }
 
 #ifdef __CUDACC__
 // Persistent warps: a lane that finishes its read takes the next one from a global counter (one atomic per
 // group of lanes that run dry in the same iteration), so no lane idles while reads remain.
-#ifndef FIN_SEARCH_THREADS
-#define FIN_SEARCH_THREADS 128
-#endif
 #ifndef FIN_SEARCH_MIN_BLOCKS
 #define FIN_SEARCH_MIN_BLOCKS 8  // 64 registers; 10 and 12 blocks spill and lose 4-30 % (profiles/r1_sweep_occupancy.log)
 #endif
-template <int KCAP, class HitT, bool COUNT>
+template <int KCAP, class HitT, bool COUNT, bool RUNS>
 __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) search_reads_kernel(const IndexView ix, const uint64_t* __restrict__ packed,
                                                            const uint64_t* __restrict__ read_offsets, const uint64_t n_reads,
-                                                           const uint64_t* __restrict__ out_offsets,
-                                                           HitPair<HitT>* __restrict__ out, SearchTotals* __restrict__ totals,
+                                                           const SearchOut<HitT> out, SearchTotals* __restrict__ totals,
                                                            const int n_strands) {
     const unsigned full = 0xFFFFFFFFu;
     const unsigned lane = threadIdx.x & 31u;
-    Chain<KCAP, HitT, COUNT> ch;
-#if defined(FIN_DQ_SHARED)
-    extern __shared__ uint64_t dq_shared[];
-    uint64_t dq_local[KCAP == 32 ? 1 : KCAP];
-    uint64_t* dq = KCAP == 32 ? dq_shared + threadIdx.x : dq_local;
-#else
+    Chain<KCAP, HitT, COUNT, RUNS> ch;
     uint64_t dq[KCAP];
-#endif
     ReadCounters rc;
     bool dry = false;  // the counter ran past the last read
     while (true) {
@@ -655,7 +693,7 @@ __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) sea
                 if (rid < n_reads) {
                     const uint64_t b0 = __ldg(read_offsets + rid);
                     const uint64_t len64 = __ldg(read_offsets + rid + 1) - b0;
-                    ch.begin_read(ix, packed, b0, len64, out + __ldg(out_offsets + rid), rc);
+                    ch.begin_read(ix, b0, len64, rid, out, rc);
                 } else {
                     dry = true;
                 }
@@ -665,7 +703,7 @@ __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) sea
             if (__all_sync(full, dry)) break;
             continue;
         }
-        ch.step(ix, packed, rc, n_strands, dq);
+        ch.step(ix, packed, rc, n_strands, dq, out);
     }
 
     // ---- per-warp reduction of the counters, one atomic per warp and counter
@@ -695,6 +733,35 @@ __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) sea
             for (int s = 16; s > 0; s >>= 1) v += __shfl_down_sync(full, v, s);
             if (lane == 0 && v) atomicAdd(dst + i, v);
         }
+    }
+}
+
+// ---- after the sort by (read, i0): CSR offsets of the runs per read --------------------------------------------
+// run_offsets[r] = base + index of the first record of a read >= r; run_offsets[n_reads] = base + n_runs.
+static __global__ void run_bounds_kernel(const uint64_t* __restrict__ keys, const uint64_t n_runs, const uint64_t n_reads,
+                                         const uint64_t base, uint64_t* __restrict__ run_offsets) {
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t > n_runs) return;
+    const uint64_t lo = t == 0 ? 0 : (keys[t - 1] >> kRunKeyPosBits) + 1;       // first read not yet covered
+    const uint64_t hi = t == n_runs ? n_reads : (keys[t] >> kRunKeyPosBits);   // this record's read (or the end)
+    for (uint64_t r = lo; r <= hi; r++) run_offsets[r] = base + t;
+}
+
+// ---- runs -> dense table on the device (fin_search_device callers that want the table, tests) -------------------
+template <class HitT>
+static __global__ void expand_runs_kernel(const uint64_t* __restrict__ keys, const RunRec* __restrict__ recs, const uint64_t n_runs,
+                                          const uint64_t* __restrict__ out_offsets, HitPair<HitT>* __restrict__ out) {
+    const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_runs) return;
+    const RunRec r = recs[t];
+    HitPair<HitT>* o = out + out_offsets[keys[t] >> kRunKeyPosBits] + r.i0;
+    const uint32_t len = r.len_rc & ~kRunRc;
+    const bool rcs = r.len_rc & kRunRc;
+    for (uint32_t d = 0; d < len; d++) {
+        HitPair<HitT> h;
+        h.unitig = (HitT)r.unitig;
+        h.pos = (HitT)(rcs ? r.pos0 - d : r.pos0 + d);
+        o[d] = h;
     }
 }
 #endif  // __CUDACC__

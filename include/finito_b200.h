@@ -110,6 +110,42 @@ fin_status fin_search_device(fin_index* index, const void* d_seqs, const uint64_
                              uint64_t n_bases, uint64_t total_kmers, void* d_out, int hit_bytes,
                              fin_search_counts* counts, float* kernel_ms);
 
+/* ---- run-length hits -----------------------------------------------------------------------------
+ * 98 % of the found k-mers of a read come out of walk_in_unitigs (include/FinimizerIndex.hh:47-102): consecutive
+ * k-mer positions at consecutive offsets of one unitig.  A run says that for one maximal stretch the search produced in
+ * one go: merged k-mer positions [first_kmer, first_kmer + len) of its read map to `unitig`; position first_kmer + d
+ * has offset first_offset + d, or first_offset - d when FIN_RUN_RC is set (a reverse-complement hit: the unitig runs
+ * against the read, include/search_fmin.hh:54-60).  The runs of a read are sorted by first_kmer and never overlap;
+ * every position outside a run is (-1,-1).  fin_expand_runs turns them back into the table fin_search_batch* fills,
+ * bit for bit; at 150 bp / 1 % error a read has ~3 runs (48 bytes) instead of 120 pairs (960 bytes). */
+typedef struct fin_run {
+    uint32_t first_kmer;   /* merged k-mer position of the run's first entry within its read */
+    uint32_t len_rc;       /* length | FIN_RUN_RC */
+    uint32_t unitig;
+    uint32_t first_offset; /* offset of position first_kmer in the unitig */
+} fin_run;
+#define FIN_RUN_RC 0x80000000u
+
+/* fin_search_batch32 with the answer as runs.  run_offsets (n_reads + 1 entries): the runs of read i are
+ * runs[run_offsets[i] .. run_offsets[i+1]).  *n_runs receives the number of runs of the batch; if it exceeds
+ * runs_capacity the call returns FIN_ERR_ARG, `runs` is incomplete and *n_runs says how much room a retry needs
+ * (fin_count_kmers() always suffices: a run holds at least one k-mer position). */
+fin_status fin_search_batch_runs(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
+                                 uint64_t* run_offsets, fin_run* runs, uint64_t runs_capacity, uint64_t* n_runs,
+                                 fin_search_counts* counts);
+
+/* Same on DEVICE buffers (d_seqs, d_read_offsets as for fin_search_device; d_run_offsets: n_reads + 1 u64;
+ * d_runs: runs_capacity records).  Synchronous. */
+fin_status fin_search_device_runs(fin_index* index, const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads,
+                                  uint64_t n_bases, uint64_t* d_run_offsets, fin_run* d_runs, uint64_t runs_capacity,
+                                  uint64_t* n_runs, fin_search_counts* counts, float* kernel_ms);
+
+/* Runs -> the (unitig, offset) table of fin_search_batch (hit_bytes 8) / fin_search_batch32 (hit_bytes 4) on the
+ * HOST, with n_threads worker threads (<= 1: the calling thread only).  Pure host arithmetic over the caller's
+ * arrays: no device, no handle. */
+fin_status fin_expand_runs(const uint64_t* read_offsets, uint64_t n_reads, int64_t k, const uint64_t* run_offsets,
+                           const fin_run* runs, void* out_pairs, uint64_t out_capacity, int hit_bytes, int n_threads);
+
 /* Access counters of the last search call on this handle, the ones SURVEY.md section 8(d) builds the
  * algorithmic-bytes figure from.  They are only tallied while counting is enabled (fin_search_set_counting,
  * or FIN_COUNTERS=1 in the environment at load time): the counting kernel variant is slower. */

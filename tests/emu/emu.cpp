@@ -20,6 +20,7 @@ using std::min;
 
 #define FIN_EMU 1
 #include "../../finito_b200/csrc/build_kernels.cuh"
+#include "../../finito_b200/csrc/runs_host.hpp"
 
 using namespace fin;
 
@@ -45,23 +46,23 @@ static IndexView view_of(const HostLayout& L) {
     return v;
 }
 
-template <int KCAP, class HitT, bool COUNT>
-static void run_chain(const IndexView& v, const uint64_t* packed, uint64_t b0, uint64_t len, HitPair<HitT>* o, ReadCounters& rc,
-                      int n_strands) {
-    Chain<KCAP, HitT, COUNT> ch;
+template <int KCAP, class HitT, bool COUNT, bool RUNS>
+static void run_chain(const IndexView& v, const uint64_t* packed, uint64_t b0, uint64_t len, uint64_t read, const SearchOut<HitT>& out,
+                      ReadCounters& rc, int n_strands) {
+    Chain<KCAP, HitT, COUNT, RUNS> ch;
     uint64_t dq[KCAP];
-    if (!ch.begin_read(v, packed, b0, len, o, rc)) return;
-    while (ch.st != ST_IDLE) ch.step(v, packed, rc, n_strands, dq);
+    if (!ch.begin_read(v, b0, len, read, out, rc)) return;
+    while (ch.st != ST_IDLE) ch.step(v, packed, rc, n_strands, dq, out);
 }
 
-template <class HitT, bool COUNT>
-static void run_read(const IndexView& v, const uint64_t* packed, uint64_t b0, uint64_t len, HitPair<HitT>* o, ReadCounters& rc,
-                     int n_strands) {
+template <class HitT, bool COUNT, bool RUNS>
+static void run_read(const IndexView& v, const uint64_t* packed, uint64_t b0, uint64_t len, uint64_t read, const SearchOut<HitT>& out,
+                     ReadCounters& rc, int n_strands) {
     const int k = v.k;
-    if (k <= 32) run_chain<32, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
-    else if (k <= 64) run_chain<64, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
-    else if (k <= 128) run_chain<128, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
-    else run_chain<256, HitT, COUNT>(v, packed, b0, len, o, rc, n_strands);
+    if (k <= 32) run_chain<32, HitT, COUNT, RUNS>(v, packed, b0, len, read, out, rc, n_strands);
+    else if (k <= 64) run_chain<64, HitT, COUNT, RUNS>(v, packed, b0, len, read, out, rc, n_strands);
+    else if (k <= 128) run_chain<128, HitT, COUNT, RUNS>(v, packed, b0, len, read, out, rc, n_strands);
+    else run_chain<256, HitT, COUNT, RUNS>(v, packed, b0, len, read, out, rc, n_strands);
 }
 
 static std::vector<uint8_t> emu_lcs_bytes(const SbwtHost& s) {
@@ -99,7 +100,7 @@ const char* emu_last_error() { return g_err.c_str(); }
 
 // counts4: found_fwd, found_rc, positive, n_queries; access8: the eight access counters; flags: error bits
 int emu_search(const char* prefix, const char* seqs, const uint64_t* offs, uint64_t n_reads, int64_t* out, int64_t* counts4,
-               int64_t* access8, uint32_t* flags, int n_strands) {
+               int64_t* access8, uint32_t* flags, int n_strands, int runs_mode, uint64_t* n_runs_out) {
     return guarded([&] {
         IndexHost h = load_index_files(prefix);
         HostLayout L = build_host_layout(h);
@@ -112,18 +113,46 @@ int emu_search(const char* prefix, const char* seqs, const uint64_t* offs, uint6
             if (!(ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T')) *flags |= kErrBadBase;
             packed[i >> 5] |= (uint64_t)(((ch >> 1) ^ (ch >> 2)) & 3u) << (2 * (i & 31));
         }
-        uint64_t o = 0;
         for (int i = 0; i < 4; i++) counts4[i] = 0;
         for (int i = 0; i < 8; i++) access8[i] = 0;
+        // what the device pipeline prepares: output offsets (exclusive scan of the k-mer counts) and the found-mask scratch
+        std::vector<uint64_t> out_offsets(n_reads + 1, 0);
+        for (uint64_t r = 0; r < n_reads; r++) {
+            const uint64_t len = offs[r + 1] - offs[r];
+            out_offsets[r + 1] = out_offsets[r] + (len >= (uint64_t)v.k ? len - v.k + 1 : 0);
+        }
+        const uint64_t total = out_offsets[n_reads];
+        std::vector<uint64_t> fmask((total >> 6) + n_reads + 2, 0xDEADBEEFDEADBEEFull);
+        std::vector<uint64_t> keys(total + 1);
+        std::vector<RunRec> recs(total + 1);
+        unsigned long long n_runs = 0;
+        SearchOut<int64_t> so{reinterpret_cast<HitPair<int64_t>*>(out), out_offsets.data(), fmask.data(),
+                              RunSink{keys.data(), recs.data(), &n_runs, total}};
         for (uint64_t r = 0; r < n_reads; r++) {
             ReadCounters rc;
             const uint64_t len = offs[r + 1] - offs[r];
-            run_read<int64_t, true>(v, packed.data(), offs[r], len, reinterpret_cast<HitPair<int64_t>*>(out) + o, rc, n_strands);
-            if (len >= (uint64_t)v.k) o += len - v.k + 1;
+            if (runs_mode) run_read<int64_t, true, true>(v, packed.data(), offs[r], len, r, so, rc, n_strands);
+            else run_read<int64_t, true, false>(v, packed.data(), offs[r], len, r, so, rc, n_strands);
             counts4[0] += rc.found[0]; counts4[1] += rc.found[1]; counts4[2] += rc.positive; counts4[3] += rc.n_q;
             const unsigned a[8] = {rc.c_rank, rc.c_lcs, rc.c_ustart, rc.c_anchor, rc.c_branch, rc.c_walk, rc.c_bases, rc.c_kmers};
             for (int i = 0; i < 8; i++) access8[i] += a[i];
             *flags |= rc.err;
+        }
+        if (runs_mode) {  // the device pipeline's sort by (read, first k-mer) and CSR offsets, then the product's host expander
+            if (n_runs > total) throw arg_error("more runs than k-mer positions");
+            std::vector<uint64_t> order(n_runs);
+            for (uint64_t t = 0; t < n_runs; t++) order[t] = t;
+            std::sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b) { return keys[a] < keys[b]; });
+            std::vector<fin_run> sorted(n_runs);
+            std::vector<uint64_t> run_offsets(n_reads + 1, 0);
+            for (uint64_t t = 0; t < n_runs; t++) {
+                const RunRec& q = recs[order[t]];
+                sorted[t] = fin_run{q.i0, q.len_rc, q.unitig, q.pos0};
+                run_offsets[(keys[order[t]] >> kRunKeyPosBits) + 1]++;
+            }
+            for (uint64_t r = 0; r < n_reads; r++) run_offsets[r + 1] += run_offsets[r];
+            expand_runs_host(offs, n_reads, v.k, run_offsets.data(), sorted.data(), out, total, 8, 3);
+            if (n_runs_out) *n_runs_out = n_runs;
         }
     });
 }

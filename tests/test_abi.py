@@ -25,13 +25,33 @@ def test_library_exports_every_symbol():
     lib = fb.lib()
     for name in header_functions():
         assert hasattr(lib, name), name
-    assert lib.fin_abi_version() == 1
+    assert lib.fin_abi_version() == 2
 
 
 def test_count_kmers_is_host_arithmetic():
     offs = np.array([0, 10, 10, 40, 45, 200], dtype=np.uint64)
     assert fb.lib().fin_count_kmers(offs.ctypes.data, 5, 31) == 0 + 0 + 0 + 0 + 125
     assert fb.lib().fin_count_kmers(offs.ctypes.data, 5, 4) == 7 + 0 + 27 + 2 + 152
+
+
+def test_expand_runs_is_host_arithmetic():
+    """fin_expand_runs needs no device: two reads, a forward run, a reverse-complement run and the gaps between them."""
+    offs = np.array([0, 10, 17], dtype=np.uint64)  # k = 4: 7 and 4 k-mer positions
+    runs = np.array([(1, 3, 5, 10), (5, 2 | fb.RUN_RC, 9, 7), (0, 4 | fb.RUN_RC, 2, 3)], dtype=fb.RUN_DTYPE)
+    ro = np.array([0, 2, 3], dtype=np.uint64)
+    want = [[-1, -1], [5, 10], [5, 11], [5, 12], [-1, -1], [9, 7], [9, 6], [2, 3], [2, 2], [2, 1], [2, 0]]
+    for bits in (64, 32):
+        for threads in (1, 4):
+            assert fb.expand_runs(offs, 4, ro, runs, hit_bits=bits, threads=threads).tolist() == want
+    bad = runs.copy()
+    bad[1]["first_kmer"] = 2  # overlaps the first run
+    with pytest.raises(fb.FinitoError) as e:
+        fb.expand_runs(offs, 4, ro, bad)
+    assert e.value.status == fb.FIN_ERR_ARG
+    bad = runs.copy()
+    bad[2]["first_offset"] = 2  # a reverse run that would go below offset 0
+    with pytest.raises(fb.FinitoError):
+        fb.expand_runs(offs, 4, ro, bad)
 
 
 def test_no_cpu_fallback_without_device():

@@ -12,11 +12,12 @@ from fin_datasets import make_dataset
 
 
 @pytest.mark.parametrize("case", golden_cases())
-def test_search_bodies_match_reference_output(case):
+@pytest.mark.parametrize("runs", [False, True], ids=["dense", "runs"])
+def test_search_bodies_match_reference_output(case, runs):
     d = os.path.join(H.GOLDEN, case)
     reads = H.read_fasta(os.path.join(d, "queries.fna"))
     seqs, offs = H.batch_of(reads)
-    got, counts, _, flags = H.emu_search(os.path.join(d, "ref"), seqs, offs)
+    got, counts, _, flags = H.emu_search(os.path.join(d, "ref"), seqs, offs, runs=runs)
     assert flags == 0
     want = H.parse_output(os.path.join(d, "ref_out.txt"))
     assert np.array_equal(got, want)
@@ -49,10 +50,44 @@ def test_search_and_build_bodies_match_oracle_on_synthetic(k, genome_len, tmp_pa
     got, gc, acc, flags = H.emu_search(orc_prefix, seqs, offs)
     assert flags == 0 and oc["n_deque_underflow"] == 0 and oc["n_out_of_domain"] == 0
     assert np.array_equal(got, want) and np.array_equal(gc, wc)
+    got_r, gc_r, _, flags_r = H.emu_search(orc_prefix, seqs, offs, runs=True)  # run records -> fin_expand_runs
+    assert flags_r == 0 and np.array_equal(got_r, want) and np.array_equal(gc_r, wc)
     # the access counters behind the algorithmic-bytes figure agree between the oracle and the kernel bodies
     for name in ("n_rank", "n_lcs_reads", "n_ustart_reads", "n_anchor", "n_anchor_branch", "n_walk_words", "n_bases", "n_kmers"):
         assert acc[name] == oc[name], name
     assert 0.5 < wc[2] / wc[3] < 0.95  # most k-mers of 1 %-error reads are found
+
+
+@pytest.mark.parametrize("runs", [False, True], ids=["dense", "runs"])
+def test_search_bodies_long_reads_cross_found_mask_words(runs, tmp_path):
+    """Reads of 40..700 bases with errors on either strand: the forward strand's found mask spans up to 11 words, runs
+    get cut by the merge rule in the middle of a walk (search_fmin.hh:54-60)."""
+    k = 31
+    ds = make_dataset("cpu", genome_len=150_000, k=k, n_reads=400, read_len=150, seed=k)
+    orc_prefix = str(tmp_path / "orc")
+    H.oracle_build(ds["sbwt"], ds["unitigs"], orc_prefix)
+    genome = "".join(H.read_fasta(ds["genome"]))
+    unitigs = H.read_fasta(ds["unitigs"])
+    rng = np.random.default_rng(7)
+    comp = str.maketrans("ACGT", "TGCA")
+    reads = []
+    for i in range(300):
+        n = int(rng.integers(40, 700))
+        p = int(rng.integers(0, len(genome) - n))
+        r = list(genome[p:p + n])
+        for j in np.nonzero(rng.random(n) < 0.01)[0]:
+            r[j] = "ACGT"[("ACGT".index(r[j]) + 1 + int(rng.integers(0, 3))) % 4]
+        r = "".join(r)
+        reads.append(r if rng.random() < 0.5 else r[::-1].translate(comp))
+    # chimeras: a forward piece of one unitig glued to the reverse complement of another (both strands hit in one read)
+    long_u = sorted(unitigs, key=len)[-12:]
+    for a, b in zip(long_u[::2], long_u[1::2]):
+        reads.append(a[:200] + b[:200][::-1].translate(comp) + a[100:260])
+    seqs, offs = H.batch_of(reads)
+    want, wc = H.Oracle(orc_prefix).search_reads(seqs, offs)
+    got, gc, _, flags = H.emu_search(orc_prefix, seqs, offs, runs=runs)
+    assert flags == 0 and np.array_equal(got, want) and np.array_equal(gc, wc)
+    assert wc[0] > 0 and wc[1] > 0
 
 
 def stats_modes():
