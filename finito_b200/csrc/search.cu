@@ -24,7 +24,8 @@ struct SearchSlot {
     cudaStream_t stream = nullptr;
     cudaEvent_t counted = nullptr, done = nullptr;  // kernels + totals copy finished / everything finished
     DevBuf<uint8_t> ascii, scan_tmp, sort_tmp;
-    DevBuf<uint64_t> packed, offsets, out_offsets, fmask;
+    DevBuf<uint64_t> packed, offsets, out_offsets;
+    DevBuf<uint32_t> fmask;
     DevBuf<uint8_t> hits;
     DevBuf<uint64_t> keys_a, keys_b, run_offsets;  // runs mode: appended / sorted keys, CSR offsets
     DevBuf<RunRec> recs_a, recs_b;
@@ -139,13 +140,13 @@ static void launch_search_t(const IndexView& v, const uint64_t* packed, const ui
 }
 
 // words of the forward strand's found mask for a batch (SearchOut::fmask)
-static uint64_t fmask_words(uint64_t n_reads, uint64_t total_kmers) { return (total_kmers >> 6) + n_reads + 2; }
+static uint64_t fmask_words(uint64_t n_reads, uint64_t total_kmers) { return (total_kmers >> 5) + n_reads + 2; }
 
 // what the pipeline writes: dense hits (hit_bytes 4 / 8, d_hits) or runs (hit_bytes 0, sink)
 struct PipelineOut {
     int hit_bytes = 4;
     void* d_hits = nullptr;
-    uint64_t* d_fmask = nullptr;
+    uint32_t* d_fmask = nullptr;
     RunSink sink{nullptr, nullptr, nullptr, 0};
 };
 
@@ -271,7 +272,7 @@ uint64_t DeviceIndex::prepare_device_batch(const void* d_seqs, const uint64_t* d
     FIN_CUDA(cudaMemcpyAsync(&flags, &((SearchTotals*)dev_totals_.p)->error_flags, 4, cudaMemcpyDeviceToHost, 0));
     FIN_CUDA(cudaStreamSynchronize(0));
     check_flags(flags & kErrBadOffsets);
-    if ((total >> 6) + n_reads >= 0xFFFFFFF0ull) throw limit_error("batch too large for one call: split it");
+    if ((total >> 5) + n_reads >= 0xFFFFFFF0ull) throw limit_error("batch too large for one call: split it");
     dev_fmask_.ensure(fmask_words(n_reads, total));
     return total;
 }
@@ -347,8 +348,20 @@ uint64_t DeviceIndex::search_device_runs(const void* d_seqs, const uint64_t* d_r
 // host batch: sub-batches round-robin over three streams, so that the H2D copy of sub-batch i+1 and the
 // D2H copy of sub-batch i-1 overlap the kernels of sub-batch i.
 // -------------------------------------------------------------------------------------------------------
-static constexpr uint64_t kSubBases = 48ull << 20;  // bases per sub-batch
-static constexpr uint64_t kSubReads = 1ull << 19;   // reads per sub-batch
+// Dense hits: 8 bytes per k-mer leave over PCIe, so small sub-batches (the copies of one hide behind the kernels of
+// the next).  Runs: the copies are small and what counts is the tail of every persistent kernel (a lane owns a read
+// for ~2.5 ms at 150 bp), so few, large sub-batches.  FIN_SUB_READS / FIN_SUB_MBASES override both (experiments).
+struct SubBatchLimits {
+    uint64_t reads, bases;
+};
+static SubBatchLimits sub_batch_limits(bool runs, uint64_t n_reads) {
+    // runs: at least four sub-batches per call so that the first copy-in stays short
+    SubBatchLimits l = runs ? SubBatchLimits{std::min<uint64_t>(1ull << 21, std::max<uint64_t>(1ull << 18, n_reads / 4)), 384ull << 20}
+                            : SubBatchLimits{1ull << 19, 48ull << 20};
+    if (const char* e = getenv("FIN_SUB_READS")) if (atoll(e) > 0) l.reads = (uint64_t)atoll(e);
+    if (const char* e = getenv("FIN_SUB_MBASES")) if (atoll(e) > 0) l.bases = (uint64_t)atoll(e) << 20;
+    return l;
+}
 static constexpr int kSlots = 3;
 
 void DeviceIndex::ensure_slots() {
@@ -386,8 +399,10 @@ struct SlotDrain {
 
 // sub-batch [r0, r1): at most kSubReads reads and kSubBases bases (always at least one read); validates the offsets
 // of the sub-batch and counts its k-mer positions
-static uint64_t cut_sub_batch(const uint64_t* read_offsets, uint64_t n_reads, uint64_t r0, int k, uint64_t& nkm, uint64_t& max_len) {
-    uint64_t r1 = std::min(n_reads, r0 + kSubReads);
+static uint64_t cut_sub_batch(const uint64_t* read_offsets, uint64_t n_reads, uint64_t r0, int k, const SubBatchLimits lim, uint64_t& nkm,
+                              uint64_t& max_len) {
+    const uint64_t kSubBases = lim.bases;
+    uint64_t r1 = std::min(n_reads, r0 + lim.reads);
     const uint64_t base0 = read_offsets[r0];
     if (read_offsets[r1] >= base0 && read_offsets[r1] - base0 > kSubBases) {
         const uint64_t* lo = read_offsets + r0 + 1;
@@ -423,7 +438,7 @@ static void stage_sub_batch(const IndexView& v, SearchSlot& s, const char* seqs,
     if (s.h_offsets_cap < nr + 1) {
         if (s.h_offsets_pinned) cudaFreeHost(s.h_offsets_pinned);
         s.h_offsets_pinned = nullptr;
-        s.h_offsets_cap = std::max<uint64_t>(nr + 1, kSubReads + 1);
+        s.h_offsets_cap = nr + 1 + nr / 4;
         FIN_CUDA(cudaHostAlloc((void**)&s.h_offsets_pinned, s.h_offsets_cap * 8, cudaHostAllocDefault));
     }
     for (uint64_t i = 0; i <= nr; i++) s.h_offsets_pinned[i] = read_offsets[r0 + i] - base0;
@@ -457,9 +472,10 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
 
     uint64_t r0 = 0, out_pos = 0, max_len = 0;
     int turn = 0;
+    const SubBatchLimits lim = sub_batch_limits(false, n_reads);
     while (r0 < n_reads) {
         uint64_t nkm = 0;
-        const uint64_t r1 = cut_sub_batch(read_offsets, n_reads, r0, k, nkm, max_len);
+        const uint64_t r1 = cut_sub_batch(read_offsets, n_reads, r0, k, lim, nkm, max_len);
         if (out_pos + nkm > out_capacity) throw arg_error("out_capacity is smaller than the number of k-mer positions of the batch");
         SearchSlot& s = *slots_[turn % kSlots];
         turn++;
@@ -549,9 +565,10 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
     uint64_t r0 = 0, max_len = 0;
     int turn = 0;
     SearchSlot* prev = nullptr;
+    const SubBatchLimits lim = sub_batch_limits(true, n_reads);
     while (r0 < n_reads) {
         uint64_t nkm = 0;
-        const uint64_t r1 = cut_sub_batch(read_offsets, n_reads, r0, k, nkm, max_len);
+        const uint64_t r1 = cut_sub_batch(read_offsets, n_reads, r0, k, lim, nkm, max_len);
         SearchSlot& s = *slots_[turn % kSlots];
         turn++;
         if (s.busy) FIN_CUDA(cudaEventSynchronize(s.done));  // its phase B was issued two turns ago

@@ -218,6 +218,15 @@ struct RunSink {
     uint64_t capacity;
 };
 
+// does any lane of the (converged) warp want to append?
+FIN_D bool run_any(const bool want) {
+#ifdef FIN_EMU
+    return want;
+#else
+    return __any_sync(0xFFFFFFFFu, want);
+#endif
+}
+
 // Appends one record per lane that has one.  Called by every lane of the warp at the same point (converged).
 FIN_D void run_append(const RunSink& sink, const bool want, const uint64_t key, const RunRec rec) {
 #ifdef FIN_EMU
@@ -276,12 +285,12 @@ enum : int { ST_EXT = 0, ST_EXTK = 1, ST_POST = 2, ST_SHRINK = 3, ST_EMIT = 4, S
 
 // Where a chain's answers go.  Dense: one HitPair per k-mer position (out + out_offsets[read]).  Runs: RunSink.
 // Both: `fmask`, one bit per k-mer position = "the forward strand found it", so that the reverse strand can apply
-// the merge rule (search_fmin.hh:54-60) without reading the forward strand's hits back.  The current 64-bit word
-// lives in a register; words are only spilled to `fmask` for reads with more than 64 k-mer positions.
+// the merge rule (search_fmin.hh:54-60) without reading the forward strand's hits back.  The current 32-bit word
+// lives in a register; words are only spilled to `fmask` for reads with more than 32 k-mer positions.
 template <class HitT> struct SearchOut {
     HitPair<HitT>* hits;        // dense mode (RUNS == false)
     const uint64_t* out_offsets;
-    uint64_t* fmask;            // (total_kmers >> 6) + n_reads + 1 words; read r starts at (out_offsets[r] >> 6) + r
+    uint32_t* fmask;            // (total_kmers >> 5) + n_reads + 1 words; read r starts at (out_offsets[r] >> 5) + r
     RunSink sink;               // runs mode
 };
 
@@ -292,7 +301,7 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
     HitPair<HitT>* o = nullptr;  // dense mode: the read's slots
     uint32_t rid = 0;            // runs mode: the read's index in the batch
     uint32_t fmw = 0;            // first word of the read in SearchOut::fmask
-    uint64_t fm = 0;             // current word of the forward strand's found mask
+    uint32_t fm = 0;             // current word of the forward strand's found mask
     int len = 0, nk = 0, strand = 0;
     // stream state (common.hh:80-103)
     int st = ST_IDLE, end = 0, c = 0;
@@ -352,7 +361,7 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
         const uint64_t oo = __ldg(out.out_offsets + read);
         if (!RUNS) o = out.hits + oo;
         rid = (uint32_t)read;
-        fmw = (uint32_t)((oo >> 6) + read);
+        fmw = (uint32_t)((oo >> 5) + read);
         fm = 0;
         strand = 0;
         begin_strand(ix);
@@ -604,14 +613,14 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
             const int i = strand ? nk - 1 - j : j;
             bool take = hit;
             if (strand == 0) {
-                fm |= (uint64_t)hit << (j & 63);
-                if ((j & 63) == 63 && j != nk - 1) {  // the last word stays in the register for the reverse strand
-                    out.fmask[fmw + (uint32_t)(j >> 6)] = fm;
+                fm |= (uint32_t)hit << (j & 31);
+                if ((j & 31) == 31 && j != nk - 1) {  // the last word stays in the register for the reverse strand
+                    out.fmask[fmw + (uint32_t)(j >> 5)] = fm;
                     fm = 0;
                 }
             } else {
-                take = hit && !((fm >> (i & 63)) & 1u);
-                if ((i & 63) == 0 && i > 0) fm = out.fmask[fmw + (uint32_t)(i >> 6) - 1u];
+                take = hit && !((fm >> (i & 31)) & 1u);
+                if ((i & 31) == 0 && i > 0) fm = out.fmask[fmw + (uint32_t)(i >> 5) - 1u];
             }
             rc.found[0] += hit && strand == 0 ? 1u : 0u;
             rc.found[1] += hit && strand != 0 ? 1u : 0u;
@@ -644,17 +653,19 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
     }
     if (RUNS) {
         FIN_PHASE_FENCE();
-        run_append(out.sink, rec_want, ((uint64_t)rid << kRunKeyPosBits) | rec.i0, rec);
         // the run that is still open when the strand ends (its last position is the strand's last k-mer)
         const bool tail = strand_done && run_len > 0;
-        if (tail) {
-            const uint32_t pos = walk_g - (idx_t)(k - 1) - walk_ustart;
-            rec.len_rc = (uint32_t)run_len | (strand ? kRunRc : 0u);
-            rec.unitig = walk_uid;
-            rec.i0 = strand ? 0u : (uint32_t)(nk - run_len);
-            rec.pos0 = strand ? pos : pos - (uint32_t)(run_len - 1);
+        if (run_any(rec_want || tail)) {  // rare: ~2 records per read
+            run_append(out.sink, rec_want, ((uint64_t)rid << kRunKeyPosBits) | rec.i0, rec);
+            if (tail) {
+                const uint32_t pos = walk_g - (idx_t)(k - 1) - walk_ustart;
+                rec.len_rc = (uint32_t)run_len | (strand ? kRunRc : 0u);
+                rec.unitig = walk_uid;
+                rec.i0 = strand ? 0u : (uint32_t)(nk - run_len);
+                rec.pos0 = strand ? pos : pos - (uint32_t)(run_len - 1);
+            }
+            run_append(out.sink, tail, ((uint64_t)rid << kRunKeyPosBits) | rec.i0, rec);
         }
-        run_append(out.sink, tail, ((uint64_t)rid << kRunKeyPosBits) | rec.i0, rec);
     }
     if (strand_done) {
         strand++;

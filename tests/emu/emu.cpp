@@ -122,7 +122,7 @@ int emu_search(const char* prefix, const char* seqs, const uint64_t* offs, uint6
             out_offsets[r + 1] = out_offsets[r] + (len >= (uint64_t)v.k ? len - v.k + 1 : 0);
         }
         const uint64_t total = out_offsets[n_reads];
-        std::vector<uint64_t> fmask((total >> 6) + n_reads + 2, 0xDEADBEEFDEADBEEFull);
+        std::vector<uint32_t> fmask((total >> 5) + n_reads + 2, 0xDEADBEEFu);
         std::vector<uint64_t> keys(total + 1);
         std::vector<RunRec> recs(total + 1);
         unsigned long long n_runs = 0;
