@@ -20,6 +20,9 @@
 //   offsets — u32 per finimizer, in column order       (global_offsets, FinimizerIndex.hh:113)
 //   ends    — u32 exclusive end of every unitig        (unitigs.ends, PackedStrings.hh:29)
 //   text    — 2 bits per base, 32 bases per u64, same bit order as sdsl::int_vector<2> (PackedStrings.hh:28)
+//   smer    — 4^s bits: which s-mers (s ~ log4(text length) + 1, <= 16) occur in the text.  Not part of the reference:
+//             a k-mer of the index has all its s-mers in the text, so a read strand without k - s + 1 consecutive
+//             present s-mers cannot hold a k-mer of the index and its streaming search is skipped (all (-1,-1))
 #pragma once
 #include <cstdint>
 #ifndef FIN_EMU
@@ -55,6 +58,10 @@ struct IndexView {
     uint32_t n_unitigs;
     uint32_t n_fmin;
     int32_t k;
+    // strand prefilter (search_kernels.cuh): bit c of `smer` is set iff the s-mer with code c occurs in `text`;
+    // nullptr = no prefilter
+    const uint32_t* __restrict__ smer;
+    int32_t smer_s;
 };
 
 #if defined(__CUDACC__) || defined(FIN_EMU)

@@ -87,11 +87,12 @@ class DeviceIndex {
     fin_index_info info_{};
     bool fits32_ = true;
     DevBuf<uint64_t> lines_, ustart_, fmin_, tstart_, text_;
-    DevBuf<uint32_t> offsets_, ends_;
+    DevBuf<uint32_t> offsets_, ends_, smer_;
     std::vector<std::unique_ptr<SearchSlot>> slots_;
     // scratch of search_device
     DevBuf<uint64_t> dev_packed_, dev_out_offsets_, dev_keys_a_, dev_keys_b_;
     DevBuf<uint32_t> dev_fmask_;
+    DevBuf<uint8_t> dev_strand_flags_;
     DevBuf<uint8_t> dev_scan_tmp_, dev_sort_tmp_, dev_recs_a_;
     DevBuf<uint8_t> dev_totals_;
 };

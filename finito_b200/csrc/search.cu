@@ -23,7 +23,7 @@ thread_local uint64_t g_launches = 0;
 struct SearchSlot {
     cudaStream_t stream = nullptr;
     cudaEvent_t counted = nullptr, done = nullptr;  // kernels + totals copy finished / everything finished
-    DevBuf<uint8_t> ascii, scan_tmp, sort_tmp;
+    DevBuf<uint8_t> ascii, scan_tmp, sort_tmp, strand_flags;
     DevBuf<uint64_t> packed, offsets, out_offsets;
     DevBuf<uint32_t> fmask;
     DevBuf<uint8_t> hits;
@@ -78,6 +78,29 @@ DeviceIndex::DeviceIndex(const IndexHost& h, int device) : device_(device) {
     view_.n_unitigs = (uint32_t)L.n_unitigs;
     view_.n_fmin = (uint32_t)L.n_fmin;
     view_.k = (int32_t)L.k;
+    view_.smer = nullptr;
+    view_.smer_s = 0;
+    {   // strand prefilter table: s ~ log4(text length) + 1 (a few percent of the 4^s codes occur), at most 16 and at most k
+        const char* off = getenv("FIN_NO_PREFILTER");
+        if (!(off && *off && *off != '0')) {
+            int s = 1;
+            while (s < 16 && (1ull << (2 * s)) < L.text_len) s++;
+            s = std::min<int>(std::min(16, s + 1), (int)L.k);
+            if (const char* e = getenv("FIN_PREFILTER_S")) if (atoi(e) >= 4 && atoi(e) <= 16) s = std::min<int>(atoi(e), (int)L.k);
+            const uint64_t words = std::max<uint64_t>(1, (1ull << (2 * s)) / 32);
+            smer_.alloc(words);
+            FIN_CUDA(cudaMemset(smer_.p, 0, words * 4));
+            if (L.text_len >= (uint64_t)s) {
+                const unsigned threads = 256;
+                smer_table_kernel<<<(unsigned)((L.text_len + threads - 1) / threads), threads>>>(text_.p, L.text_len, s, smer_.p);
+                g_launches++;
+                FIN_CUDA(cudaGetLastError());
+                FIN_CUDA(cudaDeviceSynchronize());
+            }
+            view_.smer = smer_.p;
+            view_.smer_s = s;
+        }
+    }
     fits32_ = L.n_unitigs < 0x7FFFFFFFull && L.max_unitig_len < 0x7FFFFFFFull;
 
     info_.k = L.k;
@@ -88,7 +111,7 @@ DeviceIndex::DeviceIndex(const IndexHost& h, int device) : device_(device) {
     info_.n_finimizers = (int64_t)L.n_fmin;
     info_.device = device;
     info_.device_bytes = (int64_t)(lines_.bytes() + ustart_.bytes() + fmin_.bytes() + tstart_.bytes() +
-                                   offsets_.bytes() + ends_.bytes() + text_.bytes());
+                                   offsets_.bytes() + ends_.bytes() + text_.bytes() + smer_.bytes());
     const char* e = getenv("FIN_COUNTERS");
     count_accesses = e && *e && *e != '0';
 }
@@ -147,6 +170,7 @@ struct PipelineOut {
     int hit_bytes = 4;
     void* d_hits = nullptr;
     uint32_t* d_fmask = nullptr;
+    uint8_t* d_strand_flags = nullptr;  // n_reads bytes when the index has a strand prefilter
     RunSink sink{nullptr, nullptr, nullptr, 0};
 };
 
@@ -170,13 +194,24 @@ static void launch_search(const IndexView& v, const uint64_t* d_packed, const ui
                           const uint64_t* d_out_offsets, const PipelineOut& po, SearchTotals* d_totals, bool count, int n_strands,
                           cudaStream_t st) {
     if (n_reads == 0) return;
+    const uint8_t* sf = v.smer ? po.d_strand_flags : nullptr;
+    const unsigned ft = 128, fb = (unsigned)((n_reads + ft - 1) / ft);
     if (po.hit_bytes == 8) {
-        SearchOut<int64_t> out{reinterpret_cast<HitPair<int64_t>*>(po.d_hits), d_out_offsets, po.d_fmask, po.sink};
+        SearchOut<int64_t> out{reinterpret_cast<HitPair<int64_t>*>(po.d_hits), d_out_offsets, po.d_fmask, po.sink, sf};
+        if (sf) {
+            strand_filter_kernel<int64_t><<<fb, ft, 0, st>>>(v, d_packed, d_offsets, n_reads, n_strands, po.d_strand_flags, d_out_offsets, out.hits);
+            g_launches++;
+        }
         if (count) launch_search_t<int64_t, true, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
         else launch_search_t<int64_t, false, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
         return;
     }
-    SearchOut<int32_t> out{reinterpret_cast<HitPair<int32_t>*>(po.d_hits), d_out_offsets, po.d_fmask, po.sink};
+    SearchOut<int32_t> out{reinterpret_cast<HitPair<int32_t>*>(po.d_hits), d_out_offsets, po.d_fmask, po.sink, sf};
+    if (sf) {
+        strand_filter_kernel<int32_t><<<fb, ft, 0, st>>>(v, d_packed, d_offsets, n_reads, n_strands, po.d_strand_flags, d_out_offsets,
+                                                         po.hit_bytes == 4 ? out.hits : nullptr);
+        g_launches++;
+    }
     if (po.hit_bytes == 4) {
         if (count) launch_search_t<int32_t, true, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
         else launch_search_t<int32_t, false, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
@@ -274,6 +309,7 @@ uint64_t DeviceIndex::prepare_device_batch(const void* d_seqs, const uint64_t* d
     check_flags(flags & kErrBadOffsets);
     if ((total >> 5) + n_reads >= 0xFFFFFFF0ull) throw limit_error("batch too large for one call: split it");
     dev_fmask_.ensure(fmask_words(n_reads, total));
+    dev_strand_flags_.ensure(n_reads + 1);
     return total;
 }
 
@@ -308,6 +344,7 @@ void DeviceIndex::search_device(const void* d_seqs, const uint64_t* d_read_offse
     po.hit_bytes = hit_bytes;
     po.d_hits = d_out;
     po.d_fmask = dev_fmask_.p;
+    po.d_strand_flags = dev_strand_flags_.p;
     launch_search(view_, dev_packed_.p, d_read_offsets, n_reads, dev_out_offsets_.p, po, (SearchTotals*)dev_totals_.p, count_accesses, 2, 0);
     SearchTotals tot;
     finish_device_batch(t, counts, kernel_ms, tot);
@@ -328,6 +365,7 @@ uint64_t DeviceIndex::search_device_runs(const void* d_seqs, const uint64_t* d_r
     PipelineOut po;
     po.hit_bytes = 0;
     po.d_fmask = dev_fmask_.p;
+    po.d_strand_flags = dev_strand_flags_.p;
     SearchTotals* dt = (SearchTotals*)dev_totals_.p;
     po.sink = RunSink{dev_keys_a_.p, (RunRec*)dev_recs_a_.p, &dt->n_runs, runs_capacity};
     launch_search(view_, dev_packed_.p, d_read_offsets, n_reads, dev_out_offsets_.p, po, dt, count_accesses, 2, 0);
@@ -433,6 +471,7 @@ static void stage_sub_batch(const IndexView& v, SearchSlot& s, const char* seqs,
     s.offsets.ensure(nr + 1);
     s.out_offsets.ensure(nr + 2);
     s.fmask.ensure(fmask_words(nr, nkm));
+    s.strand_flags.ensure(nr + 1);
     const size_t tmp = scan_tmp_bytes_for(nr + 1);
     s.scan_tmp.ensure(tmp);
     if (s.h_offsets_cap < nr + 1) {
@@ -486,6 +525,7 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
         po.hit_bytes = (int)sizeof(HitT);
         po.d_hits = s.hits.p;
         po.d_fmask = s.fmask.p;
+        po.d_strand_flags = s.strand_flags.p;
         launch_search(view_, s.packed.p, s.offsets.p, s.nr, s.out_offsets.p, po, (SearchTotals*)s.totals.p, count_accesses, n_strands, s.stream);
         if (nkm)
             FIN_CUDA(cudaMemcpyAsync(out_pairs + 2 * out_pos, s.hits.p, nkm * 2 * sizeof(HitT), cudaMemcpyDeviceToHost, s.stream));
@@ -524,6 +564,7 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
         PipelineOut po;
         po.hit_bytes = 0;
         po.d_fmask = s.fmask.p;
+        po.d_strand_flags = s.strand_flags.p;
         SearchTotals* dt = (SearchTotals*)s.totals.p;
         po.sink = RunSink{s.keys_a.p, s.recs_a.p, &dt->n_runs, std::min<uint64_t>(s.keys_a.n, s.recs_a.n)};
         launch_search(view_, s.packed.p, s.offsets.p, s.nr, s.out_offsets.p, po, dt, count_accesses, 2, s.stream);

@@ -94,8 +94,58 @@ static __global__ void kmer_counts_kernel(const uint64_t* __restrict__ read_offs
     counts[r] = len >= (uint64_t)k ? len - (uint64_t)k + 1 : 0;
 }
 
+// the s-mers of the text: one thread per text position (windows that span two unitigs only add bits: harmless)
+static __global__ void smer_table_kernel(const uint64_t* __restrict__ text, const uint64_t text_len, const int s, uint32_t* __restrict__ bits) {
+    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p + (uint64_t)s > text_len) return;
+    const uint64_t w0 = text[p >> 5], w1 = text[(p >> 5) + 1];  // the text array is padded by one word
+    const int sh = 2 * (int)(p & 31);
+    const uint64_t v = sh ? (w0 >> sh) | (w1 << (64 - sh)) : w0;
+    const uint32_t code = (uint32_t)v & (s >= 16 ? 0xFFFFFFFFu : ((1u << (2 * s)) - 1u));
+    atomicOr(bits + (code >> 5), 1u << (code & 31));
+}
 #endif  // __CUDACC__
 
+// ---- strand prefilter ---------------------------------------------------------------------------------------------
+// Every k-mer of the index is a substring of the unitig text, so all of its k - s + 1 s-mers are set in IndexView::smer.
+// A strand of a read that nowhere has k - s + 1 consecutive present s-mers therefore holds no k-mer of the index:
+// the reference would answer (-1,-1) for every position of that strand (FinimizerIndex.hh:150-152) after streaming
+// through all of it; here the strand is not streamed at all.  No false negatives by construction, false positives only
+// cost time.  In the benchmark workload a read matches the index on one strand, so about half of the streaming work
+// (the more expensive half: a non-matching strand contracts at every character) disappears.
+// s-mer code = sum base[i] << 2i, the bit order of the packed text and of the packed reads.
+enum : unsigned { kStrandFwd = 1u, kStrandRc = 2u };
+
+FIN_D uint32_t smer_mask(const int s) { return s >= 16 ? 0xFFFFFFFFu : ((1u << (2 * s)) - 1u); }
+FIN_D bool smer_present(const uint32_t* __restrict__ bits, const uint32_t code) { return (__ldg(bits + (code >> 5)) >> (code & 31)) & 1u; }
+
+// which strands of the read at bases [b0, b0 + len) of `packed` can hold a k-mer of the index
+FIN_D unsigned strand_candidates(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t b0, const uint64_t len) {
+    const int s = ix.smer_s, k = ix.k;
+    if (ix.smer == nullptr) return kStrandFwd | kStrandRc;
+    if (len < (uint64_t)k) return 0;
+    const uint32_t mask = smer_mask(s);
+    const int need = k - s + 1;
+    const uint32_t* __restrict__ p32 = reinterpret_cast<const uint32_t*>(packed);
+    uint32_t f = 0, r = 0, w = 0;
+    int run_f = 0, run_r = 0;
+    unsigned flags = 0;
+    for (uint64_t q = 0; q < len; q++) {
+        const uint64_t b = b0 + q;
+        if (q == 0 || (b & 15) == 0) w = __ldg(p32 + (b >> 4));
+        const uint32_t c = (w >> (2 * (b & 15))) & 3u;
+        f = (f >> 2) | (c << (2 * (s - 1)));   // window [q - s + 1, q] of the read, first base in the low bits
+        r = ((r << 2) | (3u - c)) & mask;      // its reverse complement
+        if (q + 1 >= (uint64_t)s) {
+            run_f = smer_present(ix.smer, f) ? run_f + 1 : 0;
+            run_r = smer_present(ix.smer, r) ? run_r + 1 : 0;
+            if (run_f >= need) flags |= kStrandFwd;
+            if (run_r >= need) flags |= kStrandRc;
+            if (flags == (kStrandFwd | kStrandRc)) break;
+        }
+    }
+    return flags;
+}
 
 // ---- drop_first_char (common.hh:38-48), word-parallel ------------------------------------------------------
 // The reference widens l downwards while LCS[l] >= new_len and r upwards while LCS[r+1] >= new_len, one element
@@ -292,6 +342,7 @@ template <class HitT> struct SearchOut {
     const uint64_t* out_offsets;
     uint32_t* fmask;            // (total_kmers >> 5) + n_reads + 1 words; read r starts at (out_offsets[r] >> 5) + r
     RunSink sink;               // runs mode
+    const uint8_t* strand_flags;  // per read kStrandFwd | kStrandRc from strand_filter_kernel; nullptr = stream every strand
 };
 
 template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
@@ -303,6 +354,7 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
     uint32_t fmw = 0;            // first word of the read in SearchOut::fmask
     uint32_t fm = 0;             // current word of the forward strand's found mask
     int len = 0, nk = 0, strand = 0;
+    unsigned sflags = 0;         // strands of this read that are streamed (strand prefilter)
     // stream state (common.hh:80-103)
     int st = ST_IDLE, end = 0, c = 0;
     int start = 0, kmer_start = 0;
@@ -347,7 +399,7 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
 
     // takes a new read; returns false (and stays idle) when the read has no k-mer
     FIN_D bool begin_read(const IndexView& ix, const uint64_t base, const uint64_t len64, const uint64_t read,
-                          const SearchOut<HitT>& out, ReadCounters& rc) {
+                          const SearchOut<HitT>& out, ReadCounters& rc, const int n_strands) {
         st = ST_IDLE;
         if (len64 > (uint64_t)kMaxReadLen) {
             rc.err |= kErrReadTooLong;
@@ -358,12 +410,15 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
         len = (int)len64;
         nk = len - ix.k + 1;
         rc.n_q += (unsigned)nk;
+        sflags = out.strand_flags ? (unsigned)__ldg(out.strand_flags + read) : (kStrandFwd | kStrandRc);
+        if (n_strands < 2) sflags &= kStrandFwd;
+        if (sflags == 0) return false;  // no strand can hold a k-mer of the index: every answer is (-1,-1)
         const uint64_t oo = __ldg(out.out_offsets + read);
         if (!RUNS) o = out.hits + oo;
         rid = (uint32_t)read;
         fmw = (uint32_t)((oo >> 5) + read);
         fm = 0;
-        strand = 0;
+        strand = (sflags & kStrandFwd) ? 0 : 1;
         begin_strand(ix);
         return true;
     }
@@ -612,6 +667,11 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
             const int j = end - (k - 1);
             const int i = strand ? nk - 1 - j : j;
             bool take = hit;
+#ifdef FIN_DENSE_READBACK  // experiment: the round-1 merge (read the forward strand's hit back) in dense mode
+            if (!RUNS) {
+                if (strand) take = hit && o[i].unitig == (HitT)-1;
+            } else
+#endif
             if (strand == 0) {
                 fm |= (uint32_t)hit << (j & 31);
                 if ((j & 31) == 31 && j != nk - 1) {  // the last word stays in the register for the reverse strand
@@ -620,7 +680,7 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
                 }
             } else {
                 take = hit && !((fm >> (i & 31)) & 1u);
-                if ((i & 31) == 0 && i > 0) fm = out.fmask[fmw + (uint32_t)(i >> 5) - 1u];
+                if ((i & 31) == 0 && i > 0 && (sflags & kStrandFwd)) fm = out.fmask[fmw + (uint32_t)(i >> 5) - 1u];
             }
             rc.found[0] += hit && strand == 0 ? 1u : 0u;
             rc.found[1] += hit && strand != 0 ? 1u : 0u;
@@ -630,7 +690,8 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
                 HitPair<HitT> h;
                 h.unitig = take ? (HitT)walk_uid : (HitT)-1;
                 h.pos = take ? (HitT)pos : (HitT)-1;
-                if (strand == 0 || take) o[i] = h;
+                // the first streamed strand writes every position, the reverse strand after a forward one only its own hits
+                if (strand == 0 || take || !(sflags & kStrandFwd)) o[i] = h;
             } else {
                 const bool cont = take && walked && run_len > 0;
                 if (run_len > 0 && !cont) {  // the open run ended at the previous position j - 1
@@ -669,7 +730,7 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
     }
     if (strand_done) {
         strand++;
-        if (strand < n_strands) begin_strand(ix);
+        if (strand < n_strands && (sflags & kStrandRc)) begin_strand(ix);
         else st = ST_IDLE;
     }
 }
@@ -704,7 +765,7 @@ __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) sea
                 if (rid < n_reads) {
                     const uint64_t b0 = __ldg(read_offsets + rid);
                     const uint64_t len64 = __ldg(read_offsets + rid + 1) - b0;
-                    ch.begin_read(ix, b0, len64, rid, out, rc);
+                    ch.begin_read(ix, b0, len64, rid, out, rc, n_strands);
                 } else {
                     dry = true;
                 }
@@ -744,6 +805,24 @@ __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) sea
             for (int s = 16; s > 0; s >>= 1) v += __shfl_down_sync(full, v, s);
             if (lane == 0 && v) atomicAdd(dst + i, v);
         }
+    }
+}
+
+// ---- strand prefilter: one thread per read; dense mode also answers the reads no strand of which is streamed ------
+template <class HitT>
+static __global__ void strand_filter_kernel(const IndexView ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ read_offsets,
+                                            const uint64_t n_reads, const int n_strands, uint8_t* __restrict__ flags,
+                                            const uint64_t* __restrict__ out_offsets, HitPair<HitT>* __restrict__ hits) {
+    const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_reads) return;
+    const uint64_t b0 = read_offsets[r], len = read_offsets[r + 1] - b0;
+    unsigned f = strand_candidates(ix, packed, b0, len);
+    if (n_strands < 2) f &= kStrandFwd;
+    flags[r] = (uint8_t)f;
+    if (hits != nullptr && f == 0) {
+        HitPair<HitT> none;
+        none.unitig = none.pos = (HitT)-1;
+        for (uint64_t i = out_offsets[r]; i < out_offsets[r + 1]; i++) hits[i] = none;
     }
 }
 

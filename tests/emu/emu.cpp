@@ -51,7 +51,7 @@ static void run_chain(const IndexView& v, const uint64_t* packed, uint64_t b0, u
                       ReadCounters& rc, int n_strands) {
     Chain<KCAP, HitT, COUNT, RUNS> ch;
     uint64_t dq[KCAP];
-    if (!ch.begin_read(v, b0, len, read, out, rc)) return;
+    if (!ch.begin_read(v, b0, len, read, out, rc, n_strands)) return;
     while (ch.st != ST_IDLE) ch.step(v, packed, rc, n_strands, dq, out);
 }
 
@@ -100,7 +100,8 @@ const char* emu_last_error() { return g_err.c_str(); }
 
 // counts4: found_fwd, found_rc, positive, n_queries; access8: the eight access counters; flags: error bits
 int emu_search(const char* prefix, const char* seqs, const uint64_t* offs, uint64_t n_reads, int64_t* out, int64_t* counts4,
-               int64_t* access8, uint32_t* flags, int n_strands, int runs_mode, uint64_t* n_runs_out) {
+               int64_t* access8, uint32_t* flags, int n_strands, int runs_mode, uint64_t* n_runs_out, int prefilter_s,
+               uint64_t* strands_streamed) {
     return guarded([&] {
         IndexHost h = load_index_files(prefix);
         HostLayout L = build_host_layout(h);
@@ -126,8 +127,32 @@ int emu_search(const char* prefix, const char* seqs, const uint64_t* offs, uint6
         std::vector<uint64_t> keys(total + 1);
         std::vector<RunRec> recs(total + 1);
         unsigned long long n_runs = 0;
+        // strand prefilter (DeviceIndex's constructor + strand_filter_kernel): s-mer table of the text, flags per read
+        std::vector<uint32_t> smer;
+        std::vector<uint8_t> sflags(n_reads + 1, 0);
+        if (prefilter_s > 0) {
+            const int s = std::min<int>(prefilter_s, (int)v.k);
+            smer.assign(std::max<uint64_t>(1, (1ull << (2 * s)) / 32), 0);
+            for (uint64_t p = 0; p + (uint64_t)s <= L.text_len; p++) {
+                const uint64_t w0 = L.text[p >> 5], w1 = L.text[(p >> 5) + 1];
+                const int sh = 2 * (int)(p & 31);
+                const uint64_t x = sh ? (w0 >> sh) | (w1 << (64 - sh)) : w0;
+                const uint32_t code = (uint32_t)x & smer_mask(s);
+                smer[code >> 5] |= 1u << (code & 31);
+            }
+            v.smer = smer.data();
+            v.smer_s = s;
+            for (uint64_t r = 0; r < n_reads; r++) {
+                unsigned f = strand_candidates(v, packed.data(), offs[r], offs[r + 1] - offs[r]);
+                if (n_strands < 2) f &= kStrandFwd;
+                sflags[r] = (uint8_t)f;
+                if (strands_streamed) *strands_streamed += (f & 1) + ((f >> 1) & 1);
+                if (!runs_mode && f == 0)
+                    for (uint64_t i = out_offsets[r]; i < out_offsets[r + 1]; i++) out[2 * i] = out[2 * i + 1] = -1;
+            }
+        }
         SearchOut<int64_t> so{reinterpret_cast<HitPair<int64_t>*>(out), out_offsets.data(), fmask.data(),
-                              RunSink{keys.data(), recs.data(), &n_runs, total}};
+                              RunSink{keys.data(), recs.data(), &n_runs, total}, prefilter_s > 0 ? sflags.data() : nullptr};
         for (uint64_t r = 0; r < n_reads; r++) {
             ReadCounters rc;
             const uint64_t len = offs[r + 1] - offs[r];

@@ -128,7 +128,7 @@ def emu_lib() -> C.CDLL:
     lib = C.CDLL(so)
     lib.emu_last_error.restype = C.c_char_p
     lib.emu_search.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
-                               C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+                               C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
     lib.emu_lcs.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_uint64]
     lib.emu_build.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]
     lib.emu_builder_open.restype = C.c_void_p
@@ -144,7 +144,9 @@ def emu_lib() -> C.CDLL:
     return lib
 
 
-def emu_search(prefix, seqs, offs, n_strands=2, runs=False):
+def emu_search(prefix, seqs, offs, n_strands=2, runs=False, prefilter_s=0, streamed=None):
+    """prefilter_s > 0: with the strand prefilter on s-mers (DeviceIndex builds it at load); `streamed`: a one-element
+    uint64 array that receives the number of strands that were streamed"""
     lib = emu_lib()
     offs = np.ascontiguousarray(offs, dtype=np.uint64)
     seqs = np.ascontiguousarray(seqs, dtype=np.uint8)
@@ -157,7 +159,8 @@ def emu_search(prefix, seqs, offs, n_strands=2, runs=False):
     access = np.zeros(8, dtype=np.int64)
     flags = np.zeros(1, dtype=np.uint32)
     if lib.emu_search(os.fsencode(prefix), seqs.ctypes.data, offs.ctypes.data, n, out.ctypes.data, counts.ctypes.data,
-                      access.ctypes.data, flags.ctypes.data, n_strands, int(runs), None):
+                      access.ctypes.data, flags.ctypes.data, n_strands, int(runs), None, prefilter_s,
+                      streamed.ctypes.data if streamed is not None else None):
         raise RuntimeError("emu: " + lib.emu_last_error().decode())
     return out, counts, dict(zip(COUNTER_NAMES[:8], (int(x) for x in access))), int(flags[0])
 

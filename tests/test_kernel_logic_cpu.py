@@ -13,11 +13,12 @@ from fin_datasets import make_dataset
 
 @pytest.mark.parametrize("case", golden_cases())
 @pytest.mark.parametrize("runs", [False, True], ids=["dense", "runs"])
-def test_search_bodies_match_reference_output(case, runs):
+@pytest.mark.parametrize("prefilter_s", [0, 3, 8], ids=["nofilter", "s3", "s8"])
+def test_search_bodies_match_reference_output(case, runs, prefilter_s):
     d = os.path.join(H.GOLDEN, case)
     reads = H.read_fasta(os.path.join(d, "queries.fna"))
     seqs, offs = H.batch_of(reads)
-    got, counts, _, flags = H.emu_search(os.path.join(d, "ref"), seqs, offs, runs=runs)
+    got, counts, _, flags = H.emu_search(os.path.join(d, "ref"), seqs, offs, runs=runs, prefilter_s=prefilter_s)
     assert flags == 0
     want = H.parse_output(os.path.join(d, "ref_out.txt"))
     assert np.array_equal(got, want)
@@ -52,6 +53,12 @@ def test_search_and_build_bodies_match_oracle_on_synthetic(k, genome_len, tmp_pa
     assert np.array_equal(got, want) and np.array_equal(gc, wc)
     got_r, gc_r, _, flags_r = H.emu_search(orc_prefix, seqs, offs, runs=True)  # run records -> fin_expand_runs
     assert flags_r == 0 and np.array_equal(got_r, want) and np.array_equal(gc_r, wc)
+    # strand prefilter: same answers and counters although about half of the strands are never streamed
+    for runs in (False, True):
+        streamed = np.zeros(1, dtype=np.uint64)
+        got_f, gc_f, acc_f, flags_f = H.emu_search(orc_prefix, seqs, offs, runs=runs, prefilter_s=10, streamed=streamed)
+        assert flags_f == 0 and np.array_equal(got_f, want) and np.array_equal(gc_f, wc)
+        assert int(streamed[0]) < 0.7 * 2 * (len(offs) - 1) and acc_f["n_rank"] < 0.7 * acc["n_rank"]
     # the access counters behind the algorithmic-bytes figure agree between the oracle and the kernel bodies
     for name in ("n_rank", "n_lcs_reads", "n_ustart_reads", "n_anchor", "n_anchor_branch", "n_walk_words", "n_bases", "n_kmers"):
         assert acc[name] == oc[name], name
@@ -86,6 +93,8 @@ def test_search_bodies_long_reads_cross_found_mask_words(runs, tmp_path):
     seqs, offs = H.batch_of(reads)
     want, wc = H.Oracle(orc_prefix).search_reads(seqs, offs)
     got, gc, _, flags = H.emu_search(orc_prefix, seqs, offs, runs=runs)
+    assert flags == 0 and np.array_equal(got, want) and np.array_equal(gc, wc)
+    got, gc, _, flags = H.emu_search(orc_prefix, seqs, offs, runs=runs, prefilter_s=10)
     assert flags == 0 and np.array_equal(got, want) and np.array_equal(gc, wc)
     assert wc[0] > 0 and wc[1] > 0
 
