@@ -55,6 +55,11 @@ class _BuilderInfo(C.Structure):
                [("rank", C.c_int32), ("world", C.c_int32), ("stream_ms", C.c_float)]
 
 
+class _SbwtTiming(C.Structure):
+    _fields_ = [(n, C.c_float) for n in ("read_ms", "keys_ms", "sort_ms", "nodes_ms", "write_ms", "total_ms")] + \
+               [(n, C.c_int64) for n in ("bases", "n_nodes", "n_kmers")]
+
+
 class _BuildTiming(C.Structure):
     _fields_ = [(n, C.c_float) for n in ("load_sbwt_ms", "lcs_ms", "read_unitigs_ms", "prepare_ms", "stream_merge_ms",
                                          "stream_kernel_ms", "write_ms", "total_ms")] + [("unitig_bases", C.c_int64)]
@@ -91,6 +96,8 @@ ABI = {
     "fin_probe_random_sectors": (C.c_int, [C.c_int, C.c_uint64, C.c_int, C.c_int, C.POINTER(C.c_double)]),
     "fin_host_alloc": (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
     "fin_host_free": (None, [C.c_void_p]),
+    "fin_sbwt_build": (C.c_int, [C.c_char_p, C.c_int64, C.c_char_p, C.c_int64, C.c_int]),
+    "fin_sbwt_build_last_timing": (C.c_int, [C.POINTER(_SbwtTiming)]),
     "fin_build": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int, C.c_char_p,
                             C.c_size_t]),
     "fin_build_last_timing": (C.c_int, [C.POINTER(_BuildTiming)]),
@@ -289,6 +296,14 @@ def build_fmin(sbwt_path: str, unitig_path: str, out_prefix: str, type: str = "r
     _check(lib().fin_build(os.fsencode(sbwt_path), os.fsencode(unitig_path), os.fsencode(out_prefix), type.encode(), t,
                            os.fsencode(lcs_path) if lcs_path else None, device, buf, len(buf)))
     return buf.value.decode()
+
+
+def sbwt_build(unitig_path: str, k: int, out_path: str, precalc_k: int = 8, device: int = 0) -> dict:
+    """`sbwt build --variant plain-matrix -k K` on the device (fin_sbwt_build); returns the stage timings."""
+    _check(lib().fin_sbwt_build(os.fsencode(unitig_path), k, os.fsencode(out_path), precalc_k, device))
+    t = _SbwtTiming()
+    _check(lib().fin_sbwt_build_last_timing(C.byref(t)))
+    return {n: (int if n in ("bases", "n_nodes", "n_kmers") else float)(getattr(t, n)) for n, _ in _SbwtTiming._fields_}
 
 
 class ShardedBuilder:

@@ -149,6 +149,20 @@ fin_status fin_expand_runs(const uint64_t* read_offsets, uint64_t n_reads, int64
     });
 }
 
+fin_status fin_sbwt_build(const char* unitig_path, int64_t k, const char* out_sbwt_path, int64_t precalc_k, int device) {
+    return guarded([&] {
+        require(unitig_path && out_sbwt_path, "fin_sbwt_build: null argument");
+        fin::sbwt_build_device(unitig_path, k, out_sbwt_path, precalc_k, device);
+    });
+}
+
+fin_status fin_sbwt_build_last_timing(fin_sbwt_build_timing* out) {
+    return guarded([&] {
+        require(out != nullptr, "fin_sbwt_build_last_timing: null argument");
+        *out = fin::last_sbwt_build_timing();
+    });
+}
+
 fin_status fin_search_access_counters(const fin_index* index, fin_access_counters* out) {
     return guarded([&] {
         require(index && out, "fin_search_access_counters: null argument");

@@ -105,6 +105,10 @@ fin_build_timing last_build_timing();
 DevBuf<uint64_t> index_lines_device(const IndexHost& h);  // build.cu: the 128-byte lines of a loaded index, built on the device
 double probe_random_sectors(int device, uint64_t table_bytes, int repeats, int bytes_per_access);  // probe.cu
 
+// plain-matrix SBWT construction on the device (sbwt_build.cu)
+void sbwt_build_device(const std::string& unitig_path, int64_t k, const std::string& out_path, int64_t precalc_k, int device);
+fin_sbwt_build_timing last_sbwt_build_timing();
+
 // staged build-fmin --type rarest, shardable over GPUs (build.cu)
 class RarestBuilder;
 RarestBuilder* builder_open(const std::string& sbwt_path, const std::string& unitig_path, const std::string& lcs_path,

@@ -206,6 +206,22 @@ fin_status fin_lcs(const char* sbwt_path, int with_variant_header, int device, u
                    uint64_t* n_nodes);
 
 /* ------------------------------------------------------------------------------------------------
+ * sbwt build (the producer of build-fmin's input): the plain-matrix SBWT of the k-mers of a
+ * FASTA/FASTQ(.gz) file (or .txt list of files), constructed on the device and written in the format
+ * `sbwt build --variant plain-matrix` writes (SBWT/src/CLI/sbwt_build.cpp:30-160, SBWT/include/sbwt/SBWT.hh:395-424):
+ * same node set and order as the reference constructors (SBWT/include/sbwt/NodeBOSSInMemoryConstructor.hh:98-188,
+ * kmc_construct.hh:42-238), no reverse complements added, k-mer prefix precalc table of precalc_k characters
+ * (the tool's default is 8; clamped to k).  2 <= k <= 64 in this build (FIN_ERR_LIMIT above). */
+fin_status fin_sbwt_build(const char* unitig_path, int64_t k, const char* out_sbwt_path, int64_t precalc_k, int device);
+
+/* Wall-clock stages of the last fin_sbwt_build call on this thread (milliseconds). */
+typedef struct fin_sbwt_build_timing {
+    float read_ms, keys_ms, sort_ms, nodes_ms, write_ms, total_ms;
+    int64_t bases, n_nodes, n_kmers;
+} fin_sbwt_build_timing;
+fin_status fin_sbwt_build_last_timing(fin_sbwt_build_timing* out);
+
+/* ------------------------------------------------------------------------------------------------
  * build-fmin --type rarest sharded over GPUs: one process (or thread) per GPU, every rank opens the same
  * inputs.  Replaces the single loop over the permuted unitigs of FinimizerIndexBuilder's constructor
  * (include/FinimizerIndex.hh:292-299) by `world` partial streams whose (finimizer column, overwrite-rule key)
