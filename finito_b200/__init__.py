@@ -60,6 +60,10 @@ class _SbwtTiming(C.Structure):
                [(n, C.c_int64) for n in ("bases", "n_nodes", "n_kmers")]
 
 
+class _SpssInfo(C.Structure):
+    _fields_ = [(n, C.c_int64) for n in ("n_strings", "bases", "n_kmers", "input_bases")]
+
+
 class _BuildTiming(C.Structure):
     _fields_ = [(n, C.c_float) for n in ("load_sbwt_ms", "lcs_ms", "read_unitigs_ms", "prepare_ms", "stream_merge_ms",
                                          "stream_kernel_ms", "write_ms", "total_ms")] + [("unitig_bases", C.c_int64)]
@@ -98,6 +102,7 @@ ABI = {
     "fin_host_free": (None, [C.c_void_p]),
     "fin_sbwt_build": (C.c_int, [C.c_char_p, C.c_int64, C.c_char_p, C.c_int64, C.c_int]),
     "fin_sbwt_build_last_timing": (C.c_int, [C.POINTER(_SbwtTiming)]),
+    "fin_spss_build": (C.c_int, [C.c_char_p, C.c_int64, C.c_char_p, C.c_int, C.c_uint64, C.c_int, C.POINTER(_SpssInfo)]),
     "fin_build": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_char_p, C.c_int, C.c_char_p,
                             C.c_size_t]),
     "fin_build_last_timing": (C.c_int, [C.POINTER(_BuildTiming)]),
@@ -304,6 +309,13 @@ def sbwt_build(unitig_path: str, k: int, out_path: str, precalc_k: int = 8, devi
     t = _SbwtTiming()
     _check(lib().fin_sbwt_build_last_timing(C.byref(t)))
     return {n: (int if n in ("bases", "n_nodes", "n_kmers") else float)(getattr(t, n)) for n, _ in _SbwtTiming._fields_}
+
+
+def spss_build(in_path: str, k: int, out_path: str, flip: bool = True, seed: int = 1, device: int = 0) -> dict:
+    """Disjoint SPSS of the canonical k-mers of a FASTA file (fin_spss_build): the stand-in for ggcat + unitig_flipper."""
+    i = _SpssInfo()
+    _check(lib().fin_spss_build(os.fsencode(in_path), k, os.fsencode(out_path), int(flip), seed, device, C.byref(i)))
+    return {n: int(getattr(i, n)) for n, _ in _SpssInfo._fields_}
 
 
 class ShardedBuilder:

@@ -156,6 +156,15 @@ fin_status fin_sbwt_build(const char* unitig_path, int64_t k, const char* out_sb
     });
 }
 
+fin_status fin_spss_build(const char* in_path, int64_t k, const char* out_fasta_path, int flip, uint64_t seed, int device,
+                          fin_spss_info* info) {
+    return guarded([&] {
+        require(in_path && out_fasta_path, "fin_spss_build: null argument");
+        const fin_spss_info i = fin::spss_build_device(in_path, k, out_fasta_path, flip, seed, device);
+        if (info) *info = i;
+    });
+}
+
 fin_status fin_sbwt_build_last_timing(fin_sbwt_build_timing* out) {
     return guarded([&] {
         require(out != nullptr, "fin_sbwt_build_last_timing: null argument");

@@ -108,6 +108,7 @@ double probe_random_sectors(int device, uint64_t table_bytes, int repeats, int b
 // plain-matrix SBWT construction on the device (sbwt_build.cu)
 void sbwt_build_device(const std::string& unitig_path, int64_t k, const std::string& out_path, int64_t precalc_k, int device);
 fin_sbwt_build_timing last_sbwt_build_timing();
+fin_spss_info spss_build_device(const std::string& in_path, int64_t k, const std::string& out_path, int flip, uint64_t seed, int device);
 
 // staged build-fmin --type rarest, shardable over GPUs (build.cu)
 class RarestBuilder;

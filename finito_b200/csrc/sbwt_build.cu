@@ -24,6 +24,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_select.cuh>
+#include <cub/iterator/counting_input_iterator.cuh>
 
 #include "engine.hpp"
 #include "seqio.hpp"
@@ -278,22 +279,43 @@ struct SbwtRows {  // the result of the device part, on the host
     uint64_t row_words = 0, n_nodes = 0, n_kmers = 0;
 };
 
-template <class Key>
-static SbwtRows build_rows_device(const SeqBatch& seqs, int k) {
-    using clock = std::chrono::steady_clock;
-    auto ms_since = [](clock::time_point t0) { return (float)std::chrono::duration<double, std::milli>(clock::now() - t0).count(); };
+// reverse complement of a k-mer key (first base in the low bits): reverse the 2-bit groups, complement
+__device__ __forceinline__ uint64_t rev_groups64(uint64_t x) {
+    x = ((x >> 2) & 0x3333333333333333ULL) | ((x & 0x3333333333333333ULL) << 2);
+    x = ((x >> 4) & 0x0F0F0F0F0F0F0F0FULL) | ((x & 0x0F0F0F0F0F0F0F0FULL) << 4);
+    x = ((x >> 8) & 0x00FF00FF00FF00FFULL) | ((x & 0x00FF00FF00FF00FFULL) << 8);
+    x = ((x >> 16) & 0x0000FFFF0000FFFFULL) | ((x & 0x0000FFFF0000FFFFULL) << 16);
+    return (x >> 32) | (x << 32);
+}
+__device__ __forceinline__ uint64_t revcomp_key(uint64_t x, int k) { return (~rev_groups64(x)) >> (64 - 2 * k); }
+__device__ __forceinline__ u128 revcomp_key(u128 x, int k) {
+    const u128 r = ((u128)rev_groups64((uint64_t)x) << 64) | (u128)rev_groups64((uint64_t)(x >> 64));
+    return (~r) >> (128 - 2 * k);
+}
+template <class Key> static __global__ void canonical_keys_kernel(Key* __restrict__ keys, uint64_t n, int k) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const Key x = keys[i], r = revcomp_key(x, k);
+    keys[i] = r < x ? r : x;
+}
+
+// the k-mers of a batch of sequences as keys on the device, in input order
+template <class Key> struct KmerKeys {
+    DevBuf<Key> keys;
+    std::vector<uint64_t> kstart;  // index of the first k-mer of every sequence; kstart[n_seqs] = n_pos
+    uint64_t n_pos = 0;
+};
+template <class Key> static KmerKeys<Key> make_kmer_keys(const SeqBatch& seqs, int k, bool canonical) {
+    KmerKeys<Key> K;
     const uint64_t n_seqs = seqs.size(), text_len = seqs.seqs.size();
     // k-mer positions per sequence (sequences shorter than k hold none, NodeBOSSInMemoryConstructor.hh:104)
-    std::vector<uint64_t> kstart(n_seqs + 1, 0);
+    K.kstart.assign(n_seqs + 1, 0);
     for (uint64_t u = 0; u < n_seqs; u++) {
         const uint64_t len = seqs.offsets[u + 1] - seqs.offsets[u];
-        kstart[u + 1] = kstart[u] + (len >= (uint64_t)k ? len - (uint64_t)k + 1 : 0);
+        K.kstart[u + 1] = K.kstart[u] + (len >= (uint64_t)k ? len - (uint64_t)k + 1 : 0);
     }
-    const uint64_t n_pos = kstart[n_seqs];
+    const uint64_t n_pos = K.n_pos = K.kstart[n_seqs];
     if (n_pos == 0) throw domain_error("the input holds no k-mer");
-
-    auto t0 = clock::now();
-    DevBuf<uint8_t> tmp;
     DevBuf<uint64_t> d_text((text_len + 31) / 32 + 3);
     {
         DevBuf<uint8_t> d_ascii(text_len + 1);
@@ -308,16 +330,30 @@ static SbwtRows build_rows_device(const SeqBatch& seqs, int k) {
         FIN_CUDA(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
         if (bad) throw domain_error("a sequence holds a character other than A, C, G, T (outside the parity domain)");
     }
-    DevBuf<Key> a(n_pos), b(n_pos);
-    {
-        DevBuf<uint64_t> d_starts(n_seqs + 1), d_kstart(n_seqs + 1);
-        FIN_CUDA(cudaMemcpy(d_starts.p, seqs.offsets.data(), (n_seqs + 1) * 8, cudaMemcpyHostToDevice));
-        FIN_CUDA(cudaMemcpy(d_kstart.p, kstart.data(), (n_seqs + 1) * 8, cudaMemcpyHostToDevice));
-        kmer_keys_kernel<Key><<<grid_for(n_pos), 256>>>(d_text.p, d_starts.p, d_kstart.p, n_seqs, n_pos, k, a.p);
+    K.keys.alloc(n_pos);
+    DevBuf<uint64_t> d_starts(n_seqs + 1), d_kstart(n_seqs + 1);
+    FIN_CUDA(cudaMemcpy(d_starts.p, seqs.offsets.data(), (n_seqs + 1) * 8, cudaMemcpyHostToDevice));
+    FIN_CUDA(cudaMemcpy(d_kstart.p, K.kstart.data(), (n_seqs + 1) * 8, cudaMemcpyHostToDevice));
+    kmer_keys_kernel<Key><<<grid_for(n_pos), 256>>>(d_text.p, d_starts.p, d_kstart.p, n_seqs, n_pos, k, K.keys.p);
+    g_launches++;
+    if (canonical) {
+        canonical_keys_kernel<Key><<<grid_for(n_pos), 256>>>(K.keys.p, n_pos, k);
         g_launches++;
-        FIN_CUDA(cudaGetLastError());
-        FIN_CUDA(cudaDeviceSynchronize());
     }
+    FIN_CUDA(cudaGetLastError());
+    FIN_CUDA(cudaDeviceSynchronize());
+    return K;
+}
+
+template <class Key>
+static SbwtRows build_rows_device(const SeqBatch& seqs, int k) {
+    using clock = std::chrono::steady_clock;
+    auto ms_since = [](clock::time_point t0) { return (float)std::chrono::duration<double, std::milli>(clock::now() - t0).count(); };
+    auto t0 = clock::now();
+    DevBuf<uint8_t> tmp;
+    KmerKeys<Key> K = make_kmer_keys<Key>(seqs, k, false);
+    const uint64_t n_pos = K.n_pos;
+    DevBuf<Key> a = std::move(K.keys), b(n_pos);
     g_sbwt_timing.keys_ms = ms_since(t0);
 
     // ---- 2. the k-mer nodes: sort, unique
@@ -517,6 +553,156 @@ void sbwt_build_device(const std::string& unitig_path, int64_t k, const std::str
     g_sbwt_timing.total_ms = ms_since(t_all);
     g_sbwt_timing.n_nodes = (int64_t)N;
     g_sbwt_timing.n_kmers = (int64_t)R.n_kmers;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Disjoint spectrum-preserving string set on the device: the stand-in for the unitig tools
+// the reference's README chains in front of `sbwt build` (ggcat + unitig_flipper).  Every canonical k-mer (a k-mer and
+// its reverse complement count as one, as in ggcat) is kept at its first occurrence in the input; the output strings
+// are the maximal stretches of consecutive kept k-mers ("pieces", each >= k long, every k-mer exactly once in either
+// orientation), optionally reverse-complemented at random ("flipped").  Not maximal unitigs - FinimizerIndex only
+// needs a disjoint SPSS.
+// ---------------------------------------------------------------------------------------------------------------
+static __global__ void first_occurrence_kernel_u32(const uint32_t* __restrict__ pos, uint64_t n, uint8_t* __restrict__ keep, const void* keys,
+                                                   int key_bytes) {
+    const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    bool head = i == 0;
+    if (!head) {
+        if (key_bytes == 8) head = ((const uint64_t*)keys)[i] != ((const uint64_t*)keys)[i - 1];
+        else head = ((const u128*)keys)[i] != ((const u128*)keys)[i - 1];
+    }
+    keep[pos[i]] = head ? 1 : 0;  // the sort is stable: the head of a run of equal keys has the smallest input position
+}
+static __global__ void mark_sequence_bounds_kernel(const uint64_t* __restrict__ kstart, uint64_t n_seqs, uint8_t* __restrict__ keep) {
+    const uint64_t u = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= n_seqs || kstart[u + 1] == kstart[u]) return;
+    keep[kstart[u]] |= 2;          // first k-mer of its sequence
+    keep[kstart[u + 1] - 1] |= 4;  // last k-mer of its sequence
+}
+// 1 = a piece starts at k-mer j, 2 = a piece ends at k-mer j
+static __global__ void piece_bounds_kernel(const uint8_t* __restrict__ keep, uint64_t n, uint8_t* __restrict__ is_start, uint8_t* __restrict__ is_end) {
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const unsigned f = keep[j];
+    const bool kept = f & 1;
+    is_start[j] = kept && ((f & 2) || !(keep[j - 1] & 1));  // j > 0 whenever bit 2 is clear
+    is_end[j] = kept && ((f & 4) || !(keep[j + 1] & 1));    // j + 1 < n whenever bit 4 is clear
+}
+
+template <class Key>
+static void spss_pieces_device(const SeqBatch& seqs, int k, std::vector<uint64_t>& starts, std::vector<uint64_t>& ends) {
+    KmerKeys<Key> K = make_kmer_keys<Key>(seqs, k, true);
+    const uint64_t n = K.n_pos, n_seqs = seqs.size();
+    if (n >= 0xFFFFFFF0ull) throw limit_error("too many k-mer positions for this build");
+    DevBuf<uint8_t> tmp, keep(n + 1);
+    {
+        DevBuf<Key> sorted(n);
+        DevBuf<uint32_t> pos(n), pos_sorted(n);
+        iota_kernel<<<grid_for(n), 256>>>(pos.p, n);
+        g_launches++;
+        sort_pairs<Key, uint32_t>(tmp, K.keys.p, sorted.p, pos.p, pos_sorted.p, n, 2 * k);
+        K.keys.release();
+        first_occurrence_kernel_u32<<<grid_for(n), 256>>>(pos_sorted.p, n, keep.p, sorted.p, (int)sizeof(Key));
+        g_launches++;
+        FIN_CUDA(cudaGetLastError());
+        FIN_CUDA(cudaDeviceSynchronize());
+    }
+    tmp.release();
+    DevBuf<uint64_t> d_kstart(n_seqs + 1);
+    FIN_CUDA(cudaMemcpy(d_kstart.p, K.kstart.data(), (n_seqs + 1) * 8, cudaMemcpyHostToDevice));
+    mark_sequence_bounds_kernel<<<grid_for(n_seqs), 256>>>(d_kstart.p, n_seqs, keep.p);
+    DevBuf<uint8_t> is_start(n), is_end(n);
+    piece_bounds_kernel<<<grid_for(n), 256>>>(keep.p, n, is_start.p, is_end.p);
+    g_launches += 2;
+    DevBuf<uint32_t> sel(n);
+    DevBuf<uint64_t> d_count(1);
+    auto select = [&](const uint8_t* flags, std::vector<uint64_t>& out) {
+        size_t bytes = 0;
+        cub::CountingInputIterator<uint32_t> it(0);
+        FIN_CUDA(cub::DeviceSelect::Flagged(nullptr, bytes, it, flags, sel.p, d_count.p, (int64_t)n));
+        tmp.ensure(bytes + 256);
+        FIN_CUDA(cub::DeviceSelect::Flagged(tmp.p, bytes, it, flags, sel.p, d_count.p, (int64_t)n));
+        g_launches += 2;
+        uint64_t c = 0;
+        FIN_CUDA(cudaMemcpy(&c, d_count.p, 8, cudaMemcpyDeviceToHost));
+        std::vector<uint32_t> h(c);
+        if (c) FIN_CUDA(cudaMemcpy(h.data(), sel.p, c * 4, cudaMemcpyDeviceToHost));
+        out.assign(h.begin(), h.end());
+    };
+    select(is_start.p, starts);
+    select(is_end.p, ends);
+    if (starts.size() != ends.size()) throw std::runtime_error("internal error: piece bounds do not pair up");
+    // k-mer index -> text position
+    uint64_t u = 0;
+    for (size_t i = 0; i < starts.size(); i++) {
+        while (K.kstart[u + 1] <= starts[i]) u++;
+        const uint64_t shift = seqs.offsets[u] - K.kstart[u];
+        if (ends[i] < starts[i] || ends[i] >= K.kstart[u + 1]) throw std::runtime_error("internal error: a piece leaves its sequence");
+        starts[i] += shift;
+        ends[i] += shift + (uint64_t)k;  // exclusive end in bases
+    }
+}
+
+static uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+
+fin_spss_info spss_build_device(const std::string& in_path, int64_t k, const std::string& out_path, int flip, uint64_t seed, int device) {
+    if (k < 2 || k > 64) throw limit_error("fin_spss_build supports 2 <= k <= 64");
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) throw cuda_error("no CUDA device is visible");
+    if (device < 0 || device >= n_dev) throw arg_error("CUDA device ordinal out of range");
+    FIN_CUDA(cudaSetDevice(device));
+    SeqBatch seqs;
+    for (const std::string& f : has_suffix(in_path, ".txt") ? read_lines(in_path) : std::vector<std::string>{in_path}) append_sequences(f, seqs);
+    if (seqs.seqs.size() >= kIndexLimit32) throw limit_error("input too large for the 32-bit positions of this build");
+    std::vector<uint64_t> starts, ends;
+    if (k <= 32) spss_pieces_device<uint64_t>(seqs, (int)k, starts, ends);
+    else spss_pieces_device<u128>(seqs, (int)k, starts, ends);
+    FILE* f = fopen(out_path.c_str(), "wb");
+    if (!f) throw io_error("cannot write " + out_path);
+    fin_spss_info info{};
+    try {
+        static const char comp[4] = {'T', 'G', 'C', 'A'};
+        std::vector<char> buf;
+        buf.reserve(1 << 24);
+        for (size_t i = 0; i < starts.size(); i++) {
+            char head[32];
+            const int hl = snprintf(head, sizeof head, ">%zu\n", i);
+            buf.insert(buf.end(), head, head + hl);
+            const char* src = seqs.seqs.data() + starts[i];
+            const uint64_t len = ends[i] - starts[i];
+            const size_t at = buf.size();
+            buf.resize(at + len + 1);
+            if (flip && (splitmix64(seed ^ (uint64_t)i) & 1)) {
+                for (uint64_t q = 0; q < len; q++) {
+                    const unsigned ch = (unsigned char)src[len - 1 - q];
+                    buf[at + q] = comp[((ch >> 1) ^ (ch >> 2)) & 3u];
+                }
+            } else {
+                memcpy(&buf[at], src, len);
+            }
+            buf[at + len] = '\n';
+            info.bases += (int64_t)len;
+            if (buf.size() > (1u << 24) - 4096 || len > (1u << 22)) {
+                write_all(f, buf.data(), buf.size(), out_path);
+                buf.clear();
+            }
+        }
+        write_all(f, buf.data(), buf.size(), out_path);
+    } catch (...) {
+        fclose(f);
+        throw;
+    }
+    if (fclose(f) != 0) throw io_error("cannot close " + out_path);
+    info.n_strings = (int64_t)starts.size();
+    info.n_kmers = info.bases - info.n_strings * (k - 1);
+    info.input_bases = (int64_t)seqs.seqs.size();
+    return info;
 }
 
 }  // namespace fin

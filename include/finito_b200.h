@@ -221,6 +221,17 @@ typedef struct fin_sbwt_build_timing {
 } fin_sbwt_build_timing;
 fin_status fin_sbwt_build_last_timing(fin_sbwt_build_timing* out);
 
+/* Disjoint spectrum-preserving string set of the k-mers of a FASTA/FASTQ(.gz) file, built on the device: the stand-in
+ * for the unitig tools the reference's README runs in front of `sbwt build` (ggcat, unitig_flipper; README.md:22-40).
+ * Every canonical k-mer (a k-mer and its reverse complement are one) is kept at its first occurrence; the output FASTA
+ * holds the maximal stretches of consecutive kept k-mers, each >= k long, reverse-complemented at random when flip != 0.
+ * Valid input for fin_sbwt_build + fin_build (every k-mer exactly once); not maximal unitigs. */
+typedef struct fin_spss_info {
+    int64_t n_strings, bases, n_kmers, input_bases;
+} fin_spss_info;
+fin_status fin_spss_build(const char* in_path, int64_t k, const char* out_fasta_path, int flip, uint64_t seed, int device,
+                          fin_spss_info* info);
+
 /* ------------------------------------------------------------------------------------------------
  * build-fmin --type rarest sharded over GPUs: one process (or thread) per GPU, every rank opens the same
  * inputs.  Replaces the single loop over the permuted unitigs of FinimizerIndexBuilder's constructor

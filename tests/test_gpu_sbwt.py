@@ -74,7 +74,7 @@ def test_sbwt_then_build_fmin_then_search_end_to_end(gpu_lib, tmp_path):
 
     fb = gpu_lib
     ds = make_dataset("gpusbwt", genome_len=300_000, k=31, n_reads=3000, read_len=150, seed=9)
-    sb = str(tmp_path / "gpu.sbwt")
+    sb = str(tmp_path / "input.sbwt")
     fb.sbwt_build(ds["unitigs"], 31, sb, 8)
     gp, op = str(tmp_path / "gpu"), str(tmp_path / "orc")
     fb.build_fmin(sb, ds["unitigs"], gp)
@@ -86,3 +86,60 @@ def test_sbwt_then_build_fmin_then_search_end_to_end(gpu_lib, tmp_path):
     with fb.FinimizerIndex.load(gp) as ix:
         got, _ = ix.search_batch((seqs, offs))
     assert np.array_equal(got, want)
+
+
+def _canon(s):
+    r = s[::-1].translate(str.maketrans("ACGT", "TGCA"))
+    return min(s, r)
+
+
+@pytest.mark.parametrize("k,flip", [(31, True), (21, False), (33, True)])
+def test_spss_is_a_disjoint_cover_of_the_canonical_kmers(k, flip, gpu_lib, tmp_path):
+    fb = gpu_lib
+    ds = make_dataset("gpusbwt", genome_len=120_000, k=21, n_reads=100, read_len=150, seed=78)
+    genome = H.read_fasta(ds["genome"])[0]
+    comp = str.maketrans("ACGT", "TGCA")
+    fa = str(tmp_path / "in.fna")
+    with open(fa, "w") as f:  # two records, the second holds a reverse-complemented stretch of the first and a short one
+        f.write(">a\n" + genome + "\n>b\n" + genome[2000:9000][::-1].translate(comp) + genome[50_000:50_300] + "\n>short\nACGT\n")
+    out = str(tmp_path / "spss.fna")
+    info = fb.spss_build(fa, k, out, flip=flip, seed=5)
+    pieces = H.read_fasta(out)
+    assert info["n_strings"] == len(pieces) and info["bases"] == sum(len(p) for p in pieces)
+    assert all(len(p) >= k for p in pieces)
+    want = set()
+    for s in H.read_fasta(fa):
+        want.update(_canon(s[i:i + k]) for i in range(len(s) - k + 1))
+    got = [_canon(p[i:i + k]) for p in pieces for i in range(len(p) - k + 1)]
+    assert len(got) == len(set(got)) == info["n_kmers"]  # every canonical k-mer once
+    assert set(got) == want
+    if flip:
+        assert any(p in genome for p in pieces if len(p) > 100) and any(p not in genome for p in pieces if len(p) > 100)
+
+
+def test_spss_sbwt_build_search_chain_matches_oracle(gpu_lib, tmp_path):
+    """genome -> fin_spss_build -> fin_sbwt_build -> fin_build -> search, the oracle (and, where shipped, the reference
+    binary) on the same files."""
+    import numpy as np
+
+    fb = gpu_lib
+    ds = make_dataset("gpusbwt", genome_len=400_000, k=31, n_reads=4000, read_len=150, seed=10)
+    spss, sb = str(tmp_path / "spss.fna"), str(tmp_path / "input.sbwt")  # not gpu.sbwt: build-fmin writes <prefix>.sbwt
+    fb.spss_build(ds["genome"], 31, spss, flip=True, seed=3)
+    fb.sbwt_build(spss, 31, sb, 8)
+    gp, op = str(tmp_path / "gpu"), str(tmp_path / "orc")
+    fb.build_fmin(sb, spss, gp)
+    H.oracle_build(sb, spss, op)
+    for suf in H.INDEX_SUFFIXES:
+        assert H.files_equal(gp + suf, op + suf), suf
+    if H.have_ref():
+        r = H.ref_run("build-fmin", "-o", str(tmp_path / "ref"), "-i", sb, "-u", spss)
+        assert r.returncode == 0, r.stderr
+        for suf in H.INDEX_SUFFIXES:
+            assert H.files_equal(gp + suf, str(tmp_path / "ref") + suf), suf
+    seqs, offs = ds["reads"]
+    want, wc = H.Oracle(op).search_reads(seqs, offs)
+    with fb.FinimizerIndex.load(gp) as ix:
+        got, c = ix.search_batch((seqs, offs))
+    assert np.array_equal(got, want) and c.positive == int(wc[2])
+    assert 0.6 < c.positive / c.n_queries < 0.8

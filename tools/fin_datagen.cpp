@@ -1,6 +1,10 @@
 // fin_datagen — synthetic inputs for tests and bench.py (not part of the product path, not the oracle).
 //
 //   fin_datagen genome  <out.fna> <length> <seed> [families copies replen divergence]
+//   fin_datagen bigenome <out.fna> <length> <seed> [chromosomes=24 repeat_fraction=0.45 families=2000 min_div=0.05 max_div=0.20]
+//                                                              large genomes: iid bases generated
+//                                                              in parallel, repeat families of 300 bp - 6 kb with Zipf copy numbers
+//                                                              and per-copy divergence, cut into `chromosomes` records
 //   fin_datagen unitigs <genome.fna> <k> <out.fna> <seed>      maximal non-branching paths of the node-centric
 //                                                              de Bruijn graph of the forward k-mers, each unitig
 //                                                              reverse-complemented with probability 1/2
@@ -105,6 +109,79 @@ static int cmd_genome(int argc, char** argv) {
     }
     std::ofstream o(out);
     o << ">genome\n" << g << "\n";
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ bigenome
+static uint64_t mix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ULL;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBULL;
+    return x ^ (x >> 31);
+}
+
+static int cmd_bigenome(int argc, char** argv) {
+    if (argc < 5) return 2;
+    const std::string out = argv[2];
+    const uint64_t len = std::stoull(argv[3]);
+    const uint64_t seed = std::stoull(argv[4]);
+    const int chromosomes = argc > 5 ? atoi(argv[5]) : 24;
+    const double rep_frac = argc > 6 ? atof(argv[6]) : 0.45;
+    const int families = argc > 7 ? atoi(argv[7]) : 2000;
+    const double min_div = argc > 8 ? atof(argv[8]) : 0.05, max_div = argc > 9 ? atof(argv[9]) : 0.20;
+    std::string g(len, 'A');
+    const uint64_t block = 1 << 20;
+#pragma omp parallel for schedule(dynamic, 4)
+    for (uint64_t b = 0; b < (len + block - 1) / block; b++) {
+        uint64_t x = mix64(seed ^ (b * 0xD1342543DE82EF95ULL));
+        const uint64_t end = std::min(len, (b + 1) * block);
+        for (uint64_t i = b * block; i < end; i += 32) {
+            x = mix64(x);
+            uint64_t v = x;
+            for (uint64_t j = i; j < std::min(end, i + 32); j++, v >>= 2) g[j] = "ACGT"[v & 3];
+        }
+    }
+    // repeat families: copy number ~ 1 / rank (Zipf), total repeat bases = rep_frac * len; planted one after the other
+    // (later copies may overwrite earlier ones, as transposons do)
+    if (rep_frac > 0 && families > 0) {
+        std::mt19937_64 rng(seed + 17);
+        double harmonic = 0;
+        for (int f = 1; f <= families; f++) harmonic += 1.0 / f;
+        uint64_t planted = 0, n_copies = 0;
+        for (int f = 1; f <= families; f++) {
+            const uint64_t L = 300 + rng() % 5701;
+            if (L * 4 > len) continue;
+            std::string rep(L, 'A');
+            for (char& c : rep) c = "ACGT"[rng() & 3];
+            const double share = rep_frac * (double)len / harmonic / f;  // bases of this family
+            const uint64_t copies = std::max<uint64_t>(2, (uint64_t)(share / (double)L));
+            for (uint64_t c = 0; c < copies; c++) {
+                const double div = min_div + (max_div - min_div) * ((double)(rng() >> 11) / 9007199254740992.0);
+                const uint64_t thr = (uint64_t)(div * 4294967296.0);
+                const uint64_t pos = rng() % (len - L);
+                for (uint64_t i = 0; i < L; i++) {
+                    char ch = rep[i];
+                    const uint64_t r = rng();
+                    if ((r & 0xFFFFFFFFull) < thr) ch = "ACGT"[(code_of(ch) + 1 + (int)((r >> 32) % 3)) & 3];
+                    g[pos + i] = ch;
+                }
+                planted += L;
+                n_copies++;
+            }
+        }
+        std::cerr << "bigenome: " << n_copies << " repeat copies, " << planted << " bases planted\n";
+    }
+    FILE* o = fopen(out.c_str(), "wb");
+    if (!o) throw std::runtime_error("cannot write " + out);
+    const uint64_t per = (len + chromosomes - 1) / chromosomes;
+    for (int c = 0; c < chromosomes; c++) {
+        const uint64_t a = (uint64_t)c * per, b = std::min(len, a + per);
+        if (a >= b) break;
+        fprintf(o, ">chr%d\n", c + 1);
+        fwrite(g.data() + a, 1, b - a, o);
+        fputc('\n', o);
+    }
+    fclose(o);
     return 0;
 }
 
@@ -414,10 +491,11 @@ int main(int argc, char** argv) {
         const std::string cmd = argc > 1 ? argv[1] : "";
         int rc = 2;
         if (cmd == "genome") rc = cmd_genome(argc, argv);
+        else if (cmd == "bigenome") rc = cmd_bigenome(argc, argv);
         else if (cmd == "unitigs") rc = cmd_unitigs(argc, argv);
         else if (cmd == "sbwt") rc = cmd_sbwt(argc, argv);
         else if (cmd == "reads") rc = cmd_reads(argc, argv);
-        if (rc == 2) std::cerr << "usage: fin_datagen genome|unitigs|sbwt|reads ... (see the header of tools/fin_datagen.cpp)\n";
+        if (rc == 2) std::cerr << "usage: fin_datagen genome|bigenome|unitigs|sbwt|reads ... (see the header of tools/fin_datagen.cpp)\n";
         return rc;
     } catch (const std::exception& e) {
         std::cerr << "fin_datagen: " << e.what() << "\n";
