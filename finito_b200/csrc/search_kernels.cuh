@@ -119,32 +119,53 @@ enum : unsigned { kStrandFwd = 1u, kStrandRc = 2u };
 FIN_D uint32_t smer_mask(const int s) { return s >= 16 ? 0xFFFFFFFFu : ((1u << (2 * s)) - 1u); }
 FIN_D bool smer_present(const uint32_t* __restrict__ bits, const uint32_t code) { return (__ldg(bits + (code >> 5)) >> (code & 31)) & 1u; }
 
+// s-mer of the read that starts at base q (absolute base index b = b0 + q), first base in the low bits
+FIN_D uint32_t read_smer(const uint64_t* __restrict__ packed, const uint64_t b, const uint32_t mask) {
+    const uint64_t w0 = __ldg(packed + (b >> 5)), w1 = __ldg(packed + (b >> 5) + 1);  // the packed array is padded by a word
+    const int sh = 2 * (int)(b & 31);
+    return (uint32_t)(sh ? (w0 >> sh) | (w1 << (64 - sh)) : w0) & mask;
+}
+FIN_D uint32_t smer_revcomp(uint32_t x, const int s) {  // reverse the 2-bit groups, complement, right-align
+    x = ((x >> 2) & 0x33333333u) | ((x & 0x33333333u) << 2);
+    x = ((x >> 4) & 0x0F0F0F0Fu) | ((x & 0x0F0F0F0Fu) << 4);
+    x = ((x >> 8) & 0x00FF00FFu) | ((x & 0x00FF00FFu) << 8);
+    x = (x >> 16) | (x << 16);
+    return (~x) >> (32 - 2 * s);
+}
+
+// Is there a stretch of `need` consecutive s-mer starts in [0, n_starts) all of which are present?  Checked from the far
+// end of each candidate stretch backwards, so that one absent s-mer rules out `need` stretches at once (Boyer-Moore
+// style): a strand that does not match costs ~n_starts / need lookups instead of n_starts.
+template <bool RC>
+FIN_D bool strand_has_candidate(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t b0, const int n_starts, const int need) {
+    const int s = ix.smer_s;
+    const uint32_t mask = smer_mask(s);
+    int a = 0;             // the stretch under test starts here
+    int known = -1;        // starts in [a, known] are known to be present
+    while (a + need <= n_starts) {
+        int j = a + need - 1;
+        const int stop = known >= a ? known : a - 1;  // everything in (stop, a + need - 1] still has to be looked up
+        while (j > stop) {
+            uint32_t code = read_smer(packed, b0 + (uint64_t)j, mask);
+            if (RC) code = smer_revcomp(code, s);
+            if (!smer_present(ix.smer, code)) break;
+            j--;
+        }
+        if (j <= stop) return true;
+        known = a + need - 1;  // (j, a + need - 1] are present, j is absent
+        a = j + 1;
+    }
+    return false;
+}
+
 // which strands of the read at bases [b0, b0 + len) of `packed` can hold a k-mer of the index
 FIN_D unsigned strand_candidates(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t b0, const uint64_t len) {
     const int s = ix.smer_s, k = ix.k;
     if (ix.smer == nullptr) return kStrandFwd | kStrandRc;
     if (len < (uint64_t)k) return 0;
-    const uint32_t mask = smer_mask(s);
-    const int need = k - s + 1;
-    const uint32_t* __restrict__ p32 = reinterpret_cast<const uint32_t*>(packed);
-    uint32_t f = 0, r = 0, w = 0;
-    int run_f = 0, run_r = 0;
-    unsigned flags = 0;
-    for (uint64_t q = 0; q < len; q++) {
-        const uint64_t b = b0 + q;
-        if (q == 0 || (b & 15) == 0) w = __ldg(p32 + (b >> 4));
-        const uint32_t c = (w >> (2 * (b & 15))) & 3u;
-        f = (f >> 2) | (c << (2 * (s - 1)));   // window [q - s + 1, q] of the read, first base in the low bits
-        r = ((r << 2) | (3u - c)) & mask;      // its reverse complement
-        if (q + 1 >= (uint64_t)s) {
-            run_f = smer_present(ix.smer, f) ? run_f + 1 : 0;
-            run_r = smer_present(ix.smer, r) ? run_r + 1 : 0;
-            if (run_f >= need) flags |= kStrandFwd;
-            if (run_r >= need) flags |= kStrandRc;
-            if (flags == (kStrandFwd | kStrandRc)) break;
-        }
-    }
-    return flags;
+    const int n_starts = (int)len - s + 1, need = k - s + 1;
+    return (strand_has_candidate<false>(ix, packed, b0, n_starts, need) ? kStrandFwd : 0u) |
+           (strand_has_candidate<true>(ix, packed, b0, n_starts, need) ? kStrandRc : 0u);
 }
 
 // ---- drop_first_char (common.hh:38-48), word-parallel ------------------------------------------------------
@@ -357,6 +378,9 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
     unsigned sflags = 0;         // strands of this read that are streamed (strand prefilter)
     // stream state (common.hh:80-103)
     int st = ST_IDLE, end = 0, c = 0;
+#ifdef FIN_PREFETCH_ROWS
+    int cn = 4;
+#endif
     int start = 0, kmer_start = 0;
     Ival I{0, 0}, Ik{0, 0};
     unsigned pendI = 0, pendK = 0;  // sides of the pending drops
@@ -395,6 +419,12 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
         const uint64_t b = b0 + (uint64_t)(strand ? len - 1 - end : end);
         const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(packed) + (b >> 4));
         c = (int)((w >> (2 * (b & 15))) & 3u) ^ (strand ? 3 : 0);
+#ifdef FIN_PREFETCH_ROWS
+        // the character after this one, when it sits in the same 16-base word (15 times out of 16): lets the step prefetch
+        // the rank rows the NEXT extension will read, together with the LCS words of the same line
+        const uint32_t nb = (uint32_t)(b & 15) + (strand ? 0xFFFFFFFFu : 1u);
+        cn = nb < 16u ? (int)((w >> (2 * nb)) & 3u) ^ (strand ? 3 : 0) : 4;
+#endif
     }
 
     // takes a new read; returns false (and stays idle) when the read has no k-mer
@@ -514,6 +544,17 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
         const idx_t il = I.l, ir = I.r + 1, kl = Ik.l, kr = Ik.r + 1;
         uint32_t uw = 0;
         uint64_t w_il = 0, w_ir = 0, w_kl = 0, w_kr = 0;
+#if defined(FIN_PREFETCH_ROWS) && !defined(FIN_EMU)
+        if (post && cn < 4) {  // rows A,C live in the first 32-byte sector of a line, G,T in the second
+            const char* lb = reinterpret_cast<const char*>(ix.lines);
+            const char* p0 = lb + ((size_t)(il >> 6) << 7) + ((cn >> 1) << 5);
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(p0));
+            if ((kl >> 6) != (il >> 6)) {
+                const char* p1 = lb + ((size_t)(kl >> 6) << 7) + ((cn >> 1) << 5);
+                asm volatile("prefetch.global.L1 [%0];" ::"l"(p1));
+            }
+        }
+#endif
         if (single) uw = __ldg(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
         if (pendI & kDropLeft) w_il = __ldg(lw + lcs_word_index(il));
         if (pendI & kDropRight) w_ir = __ldg(lw + lcs_word_index(ir));

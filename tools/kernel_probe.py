@@ -32,13 +32,32 @@ def main():
     import finito_b200 as fb
     from fin_datasets import make_dataset
 
-    ds = make_dataset("bench", genome_len=a.genome, k=a.k, n_reads=a.reads, read_len=a.read_len, seed=20260102,
-                      families=max(1, a.genome // 100_000))
-    prefix = os.path.join(ds["dir"], "fmin")
-    if not os.path.exists(prefix + ".FBV.sdsl"):
-        fb.build_fmin(ds["sbwt"], ds["unitigs"], prefix)
+    if a.genome >= 100_000_000:
+        # large indexes: the device pipeline of tools/big_config.py (bigenome -> fin_spss_build -> fin_sbwt_build -> fin_build)
+        import subprocess
+
+        work = "/dev/shm/finwork" if os.path.isdir("/dev/shm") else os.path.join(ROOT, "_work")
+        d = os.path.join(work, f"probe_g{a.genome}_k{a.k}")
+        os.makedirs(d, exist_ok=True)
+        genome, spss, sbwt, prefix, reads_bin = (os.path.join(d, f) for f in ("genome.fna", "spss.fna", "input.sbwt", "fmin", "reads.bin"))
+        datagen = os.path.join(ROOT, "tools", "fin_datagen")
+        if not os.path.exists(prefix + ".FBV.sdsl"):
+            subprocess.run([datagen, "bigenome", genome, str(a.genome), "7", "1", "0.45", "2000"], check=True, capture_output=True)
+            fb.spss_build(genome, a.k, spss, flip=True, seed=7)
+            fb.sbwt_build(spss, a.k, sbwt, 8)
+            fb.build_fmin(sbwt, spss, prefix)
+        if not os.path.exists(reads_bin):
+            subprocess.run([datagen, "reads", genome, str(a.reads), str(a.read_len), "0.01", "9", reads_bin], check=True, capture_output=True)
+        seqs = np.fromfile(reads_bin, dtype=np.uint8)
+        offs = np.arange(a.reads + 1, dtype=np.uint64) * np.uint64(a.read_len)
+    else:
+        ds = make_dataset("bench", genome_len=a.genome, k=a.k, n_reads=a.reads, read_len=a.read_len, seed=20260102,
+                          families=max(1, a.genome // 100_000))
+        prefix = os.path.join(ds["dir"], "fmin")
+        if not os.path.exists(prefix + ".FBV.sdsl"):
+            fb.build_fmin(ds["sbwt"], ds["unitigs"], prefix)
+        seqs, offs = ds["reads"]
     ix = fb.FinimizerIndex.load(prefix)
-    seqs, offs = ds["reads"]
     n, nb = a.reads, int(offs[-1])
     nk = n * (a.read_len - a.k + 1)
     d_seqs = torch.from_numpy(seqs).cuda()

@@ -10,7 +10,7 @@ for extra in "$@"; do
   for kern in "search_reads_kernelILi32EiLb0ELb0" "search_reads_kernelILi32EiLb0ELb1"; do
     grep -A2 "$kern" finito_b200/build/search.ptxas.log | grep -E "registers|spill" | tr '\n' ' ' >> "$out"; echo >> "$out"
   done
-  for g in ${GENOMES:-5000000 200000000}; do
+  for g in ${GENOMES:-5000000 1000000000}; do
     python tools/kernel_probe.py --genome $g --reads ${READS:-2000000} --tag="$extra" $PROBE_ARGS >> "$out" 2>/tmp/variant_err.log || tail -3 /tmp/variant_err.log >> "$out"
   done
 done
