@@ -46,6 +46,9 @@ def parse_args():
     ap.add_argument("--cpu-sample-reads", type=int, default=0, help="reads of the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-build-arm", action="store_true", help="skip the build-fmin bp/s arm (kernel experiments)")
+    ap.add_argument("--no-hbm-arm", action="store_true", help="skip the second roofline entry (index far beyond the L2)")
+    ap.add_argument("--hbm-genome", type=int, default=1_000_000_000)
+    ap.add_argument("--hbm-reads", type=int, default=4_000_000)
     return ap.parse_args()
 
 
@@ -333,6 +336,196 @@ def bind_to_gpu_numa_node(device):
 
 
 # ---------------------------------------------------------------------------------------------------------
+def search_arms(fb, ix, seqs, offs, k, read_len, n_reads, warmup, steps, barrier, with_e2e=True):
+    """Device-resident dense + runs arms (CUDA events inside the library) and the two end-to-end calls (pinned host buffers)
+    on one workload.  Returns times, counts and the run statistics."""
+    import torch
+
+    n_bases = int(offs[n_reads])
+    kmers = n_reads * (read_len - k + 1)
+    d_seqs = torch.from_numpy(seqs[:n_bases]).cuda()
+    d_offs = torch.from_numpy(offs[: n_reads + 1].astype(np.int64)).cuda()
+    d_out = torch.empty((kmers, 2), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    res = {"kmers": kmers, "n_bases": n_bases}
+    # ---- dense table in HBM (fin_search_device)
+    for _ in range(warmup):
+        ix.search_device(d_seqs.data_ptr(), d_offs.data_ptr(), n_reads, n_bases, kmers, d_out.data_ptr(), 4)
+    barrier()
+    launches0 = fb.launch_count()
+    dense_ms, dense_kernel_ms = [], []
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        counts, ms = ix.search_device(d_seqs.data_ptr(), d_offs.data_ptr(), n_reads, n_bases, kmers, d_out.data_ptr(), 4)
+        dense_ms.append(ms)
+        dense_kernel_ms.append(ix.last_timing()["search_kernel_ms"])
+    barrier()
+    res.update(wall_dense_s=time.perf_counter() - t0, launches_dense=fb.launch_count() - launches0, counts=counts,
+               dense_ms=dense_ms, dense_kernel_ms=dense_kernel_ms)
+    # ---- run-length records in HBM (fin_search_device_runs)
+    runs_cap = 16 * n_reads
+    d_ro = torch.empty(n_reads + 1, dtype=torch.int64, device="cuda")
+    d_runs = torch.empty((runs_cap, 4), dtype=torch.int32, device="cuda")
+    for _ in range(warmup):
+        ix.search_device_runs(d_seqs.data_ptr(), d_offs.data_ptr(), n_reads, n_bases, d_ro.data_ptr(), d_runs.data_ptr(), runs_cap)
+    barrier()
+    launches0 = fb.launch_count()
+    runs_ms, runs_kernel_ms = [], []
+    for _ in range(steps):
+        n_runs, counts_runs, ms = ix.search_device_runs(d_seqs.data_ptr(), d_offs.data_ptr(), n_reads, n_bases, d_ro.data_ptr(),
+                                                        d_runs.data_ptr(), runs_cap)
+        runs_ms.append(ms)
+        runs_kernel_ms.append(ix.last_timing()["search_kernel_ms"])
+    barrier()
+    assert counts_runs == counts
+    res.update(launches_runs=fb.launch_count() - launches0, runs_ms=runs_ms, runs_kernel_ms=runs_kernel_ms, n_runs=n_runs)
+    # ---- access counters of the counting kernel variant on a sample (algorithmic bytes of the roofline)
+    sample = min(n_reads, 1_000_000)
+    ix.set_counting(True)
+    ix.search_device(d_seqs.data_ptr(), d_offs.data_ptr(), sample, sample * read_len, sample * (read_len - k + 1), d_out.data_ptr(), 4)
+    res["access"] = {k_: v * (n_reads / sample) for k_, v in ix.access_counters().items()}
+    ix.set_counting(False)
+    del d_runs, d_ro
+    if not with_e2e:
+        return res
+    # ---- end to end, answers as runs: pinned host buffers through fin_search_batch_runs
+    h_seqs = torch.empty(n_bases, dtype=torch.uint8).pin_memory()
+    h_seqs.numpy()[:] = seqs[:n_bases]
+    h_seqs_np = h_seqs.numpy()
+    offs_n = np.ascontiguousarray(offs[: n_reads + 1])
+    h_runs = torch.empty((int(n_runs * 1.05) + 1024, 4), dtype=torch.int32).pin_memory()
+    h_ro = torch.empty(n_reads + 1, dtype=torch.int64).pin_memory()
+    h_runs_np = h_runs.numpy().view(np.uint32).reshape(-1).view(fb.RUN_DTYPE)
+    h_ro_np = h_ro.numpy().view(np.uint64)
+    for _ in range(min(warmup, 2)):
+        ix.search_batch_runs((h_seqs_np, offs_n), runs=h_runs_np, run_offsets=h_ro_np)
+    barrier()
+    e2e_runs = []
+    for _ in range(steps):
+        t1 = time.perf_counter()
+        _, runs_e, c_e = ix.search_batch_runs((h_seqs_np, offs_n), runs=h_runs_np, run_offsets=h_ro_np)
+        e2e_runs.append(time.perf_counter() - t1)
+    barrier()
+    assert c_e == counts and len(runs_e) == n_runs
+    # what a caller that wants the dense table pays on the host (fin_expand_runs on all host threads), on a sample
+    sample = min(n_reads, 1_000_000)
+    t1 = time.perf_counter()
+    fb.expand_runs(offs_n[: sample + 1], k, h_ro_np[: sample + 1], h_runs_np, hit_bits=32, threads=cpu_threads())
+    res["expand_ms_per_step"] = (time.perf_counter() - t1) / sample * n_reads * 1e3
+    # ---- end to end, dense table: fin_search_batch32 (8 bytes per k-mer over PCIe)
+    h_out = torch.empty((kmers, 2), dtype=torch.int32).pin_memory()
+    h_out_np = h_out.numpy()
+    for _ in range(min(warmup, 2)):
+        ix.search_batch((h_seqs_np, offs_n), hit_bits=32, out=h_out_np)
+    barrier()
+    e2e_dense = []
+    for _ in range(steps):
+        t1 = time.perf_counter()
+        _, c_d = ix.search_batch((h_seqs_np, offs_n), hit_bits=32, out=h_out_np)
+        e2e_dense.append(time.perf_counter() - t1)
+    barrier()
+    assert c_d == counts
+    link = []
+    for _ in range(2):  # what the host link gives for the dense result buffer in one plain copy
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        h_out.copy_(d_out, non_blocking=True)
+        torch.cuda.synchronize()
+        link.append(h_out.numel() * 4 / (time.perf_counter() - t1) / 1e9)
+    res.update(e2e_runs_s=e2e_runs, e2e_dense_s=e2e_dense, d2h_link_gbs=max(link))
+    return res
+
+
+def algorithmic_bytes_breakdown(acc, n_bases_in, out_bytes):
+    """SURVEY.md §8(d) sector model (+ the strand prefilter's table lookups, one sector each)."""
+    parts = {"rank_rows": 32 * acc["n_rank"], "lcs_words": 32 * acc["n_lcs_reads"], "ustart": 32 * acc["n_ustart_reads"],
+             "anchor_lookups": 96 * acc["n_anchor"], "walk_words": 32 * acc["n_walk_words"],
+             "prefilter_lookups": 32 * acc.get("n_filter_lookups", 0), "packed_reads": 0.25 * n_bases_in, "answers": out_bytes}
+    return float(sum(parts.values())), parts
+
+
+def committed_capture(genome, k):
+    """DRAM traffic and issue statistics of the search kernel from the committed ncu capture of this workload (a profiler
+    cannot run inside the timed bench): profiles/search_kernel_traffic.json, one entry per (genome, k)."""
+    t = profiled_traffic()
+    if isinstance(t, dict):
+        t = [t]
+    return next((x for x in t or [] if int(x.get("genome", 5_000_000)) == genome and int(x.get("k", 31)) == k), None)
+
+
+def roofline_entry(fb, res, info, args_k, read_len, n_reads, genome, world, peak, peak_src, random_peaks):
+    kmers = res["kmers"]
+    kernel_s = float(np.mean(res["dense_kernel_ms"])) / 1e3
+    total, parts = algorithmic_bytes_breakdown(res["access"], res["n_bases"], 8 * kmers)
+    achieved = total / kernel_s / 1e9
+    cap = committed_capture(genome, args_k)
+    l2_bytes = 126e6
+    resident = info["device_bytes"] < l2_bytes
+    entry = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+             "traffic": cap["dram_bytes_per_read"] * n_reads if cap else None,
+             "kernel": "strand_filter_kernel + search_reads_kernel (dense)", "kernel_ms": kernel_s * 1e3,
+             "kernel_share_of_step": float(np.sum(res["dense_kernel_ms"]) / np.sum(res["dense_ms"])),
+             "algorithmic_bytes_per_launch": total, "algorithmic_bytes_per_kmer": total / kmers,
+             "algorithmic_bytes_breakdown_per_kmer": {k_: v / kmers for k_, v in parts.items()},
+             "peak_source": peak_src, "index_device_bytes": info["device_bytes"],
+             "regime": ("index L2-resident: the sector model bills every L1/L2 hit as HBM traffic, so `frac` is NOT a DRAM utilisation; "
+                        "the kernel is limited by instruction issue under divergence (see `limiter`)") if resident else
+                       f"index {info['device_bytes'] / l2_bytes:.0f}x the 126 MB L2: random sectors come from HBM"}
+    if cap:
+        dram_gbs = cap["dram_bytes_per_read"] * n_reads / kernel_s / 1e9
+        entry.update(traffic_source=f"{cap['source']} (kernel version {cap['version']}), {cap['reads_in_captured_launch']}-read launch scaled per read",
+                     dram_gbs=dram_gbs, frac_of_copy_peak=dram_gbs / peak, limiter=cap.get("limiter"),
+                     issue_active_pct=cap.get("issue_active_pct"), lanes_per_instruction=cap.get("lanes_per_instruction"),
+                     stall_long_scoreboard_share=cap.get("stall_long_sb_share"), l1_hit_pct=cap.get("l1_hit_pct"), l2_hit_pct=cap.get("l2_hit_pct"))
+        if random_peaks and cap.get("probe_dram_gbs_at_32B"):
+            entry["frac_of_random_access_ceiling"] = dram_gbs / cap["probe_dram_gbs_at_32B"]
+            entry["random_access_ceiling_gbs"] = cap["probe_dram_gbs_at_32B"]
+    return entry
+
+
+def hbm_regime_arm(fb, args, local_rank, barrier, peak, peak_src, random_peaks):
+    """Second roofline entry: the same kernels on an index far beyond the L2 (1 Gbp genome, ~3.8 GB on the device), built
+    in this run by the device pipeline fin_spss_build -> fin_sbwt_build -> fin_build (tools/fin_datagen only makes the genome
+    and the reads).  No end-to-end arm, no CPU baseline: this entry is about the kernel."""
+    G, n_reads = args.hbm_genome, args.hbm_reads
+    work = os.environ.get("FIN_WORK") or ("/dev/shm/finwork" if os.path.isdir("/dev/shm") else os.path.join(ROOT, "_work"))
+    d = os.path.join(work, f"bench_hbm_g{G}_k{args.k}")
+    os.makedirs(d, exist_ok=True)
+    genome, spss, sbwt, prefix, reads_bin = (os.path.join(d, f) for f in ("genome.fna", "spss.fna", "input.sbwt", "fmin", "reads.bin"))
+    datagen = os.path.join(ROOT, "tools", "fin_datagen")
+    t0 = time.perf_counter()
+    timings = {}
+    if not os.path.exists(prefix + ".FBV.sdsl"):
+        subprocess.run([datagen, "bigenome", genome, str(G), "20260104", "1", "0.45", "2000"], check=True, capture_output=True)
+        timings["spss"] = fb.spss_build(genome, args.k, spss, flip=True, seed=7, device=local_rank)
+        timings["sbwt_build"] = fb.sbwt_build(spss, args.k, sbwt, 8, device=local_rank)
+        t1 = time.perf_counter()
+        fb.build_fmin(sbwt, spss, prefix, device=local_rank)
+        timings["build_fmin_s"] = time.perf_counter() - t1
+        timings["build_fmin_bp_per_s"] = timings["spss"]["bases"] / timings["build_fmin_s"]
+        timings["build_fmin_stages"] = fb.build_timing()
+    if not os.path.exists(reads_bin):
+        subprocess.run([datagen, "reads", genome, str(n_reads), str(args.read_len), "0.01", "9", reads_bin], check=True, capture_output=True)
+    seqs = np.fromfile(reads_bin, dtype=np.uint8)
+    offs = np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(args.read_len)
+    ix = fb.FinimizerIndex.load(prefix, device=local_rank)
+    info = ix.info
+    timings["prepare_s"] = time.perf_counter() - t0
+    res = search_arms(fb, ix, seqs, offs, args.k, args.read_len, n_reads, 2, max(2, min(args.steps, 3)), barrier, with_e2e=False)
+    entry = roofline_entry(fb, res, info, args.k, args.read_len, n_reads, G, 1, peak, peak_src, random_peaks)
+    kmers = res["kmers"]
+    entry.update(workload=f"synthetic {G / 1e6:g} Mbp genome (45 % repeats), disjoint SPSS of its canonical k-mers, k={args.k}, {n_reads} simulated "
+                          f"{args.read_len} bp reads at 1% error",
+                 value=kmers / np.mean(res["dense_ms"]) * 1e3, runs_value=kmers / np.mean(res["runs_ms"]) * 1e3, unit_value=UNIT,
+                 found_fraction=res["counts"].positive / res["counts"].n_queries, runs_per_read=res["n_runs"] / n_reads,
+                 index_nodes=info["n_nodes"], pipeline=timings)
+    ix.close()
+    for f in os.listdir(d):
+        os.remove(os.path.join(d, f))
+    os.rmdir(d)
+    return entry
+
+
 def main():
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -372,109 +565,21 @@ def main():
     n_bases = int(offs[-1])
     kmers_per_step = n_reads * (args.read_len - args.k + 1)
 
-    # ---- device-resident arm
-    d_seqs = torch.from_numpy(seqs).cuda()
-    d_offs = torch.from_numpy(offs.astype(np.int64)).cuda()
-    d_out = torch.empty((kmers_per_step, 2), dtype=torch.int32, device="cuda")
-    torch.cuda.synchronize()
-
-    def device_step():
-        c, ms = ix.search_device(d_seqs.data_ptr(), d_offs.data_ptr(), n_reads, n_bases, kmers_per_step, d_out.data_ptr(), 4)
-        return c, ms, ix.last_timing()
-
     def barrier():
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    launches0 = fb.launch_count()
-    for _ in range(args.warmup):
-        device_step()
-    barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    launches1 = fb.launch_count()
-    pipeline_ms, search_ms = [], []
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        counts, ms, tm = device_step()
-        pipeline_ms.append(ms)
-        search_ms.append(tm["search_kernel_ms"])
-    barrier()
-    wall_dev = time.perf_counter() - t0
-    gpu_launches = fb.launch_count() - launches1
-    dev_total_ms = float(sum(pipeline_ms))
-
-    # ---- device-resident arm, answers as run-length records (fin_search_device_runs)
-    runs_cap = 16 * n_reads
-    d_ro = torch.empty(n_reads + 1, dtype=torch.int64, device="cuda")
-    d_runs = torch.empty((runs_cap, 4), dtype=torch.int32, device="cuda")
-    for _ in range(args.warmup):
-        n_runs, counts_runs, _ = ix.search_device_runs(d_seqs.data_ptr(), d_offs.data_ptr(), n_reads, n_bases, d_ro.data_ptr(), d_runs.data_ptr(), runs_cap)
-    barrier()
-    runs_ms, runs_search_ms = [], []
-    for _ in range(args.steps):
-        n_runs, counts_runs, ms = ix.search_device_runs(d_seqs.data_ptr(), d_offs.data_ptr(), n_reads, n_bases, d_ro.data_ptr(), d_runs.data_ptr(), runs_cap)
-        runs_ms.append(ms)
-        runs_search_ms.append(ix.last_timing()["search_kernel_ms"])
-    barrier()
-    assert counts_runs == counts
-    runs_total_ms = float(sum(runs_ms))
-    del d_runs, d_ro
-
-    # ---- end-to-end arm, runs: pinned host buffers through fin_search_batch_runs
-    h_seqs = torch.empty(n_bases, dtype=torch.uint8).pin_memory()
-    h_seqs.numpy()[:] = seqs
-    h_seqs_np = h_seqs.numpy()
-    h_runs = torch.empty((int(n_runs * 1.05) + 1024, 4), dtype=torch.int32).pin_memory()
-    h_ro = torch.empty(n_reads + 1, dtype=torch.int64).pin_memory()
-    h_runs_np = h_runs.numpy().view(np.uint32).reshape(-1).view(fb.RUN_DTYPE)
-    h_ro_np = h_ro.numpy().view(np.uint64)
-    for _ in range(min(args.warmup, 2)):
-        ix.search_batch_runs((h_seqs_np, offs), runs=h_runs_np, run_offsets=h_ro_np)
-    barrier()
-    e2e_runs_times = []
-    for _ in range(args.steps):
-        t1 = time.perf_counter()
-        ro_e, runs_e, c_runs_e2e = ix.search_batch_runs((h_seqs_np, offs), runs=h_runs_np, run_offsets=h_ro_np)
-        e2e_runs_times.append(time.perf_counter() - t1)
-    barrier()
-    assert c_runs_e2e == counts and len(runs_e) == n_runs
-    e2e_runs_total = float(sum(e2e_runs_times))
-    # expand-on-host cost of the dense table from the runs (what a caller that wants the table pays on the CPU)
-    t1 = time.perf_counter()
-    sample_reads = min(n_reads, 1_000_000)
-    fb.expand_runs(offs[: sample_reads + 1], args.k, h_ro_np[: sample_reads + 1], h_runs_np, hit_bits=32, threads=cpu_threads())
-    expand_s_per_read = (time.perf_counter() - t1) / sample_reads
-
-    # ---- end-to-end arm: pinned host buffers through fin_search_batch32
-    h_out = torch.empty((kmers_per_step, 2), dtype=torch.int32).pin_memory()
-    h_out_np = h_out.numpy()
-    for _ in range(min(args.warmup, 2)):
-        ix.search_batch((h_seqs_np, offs), hit_bits=32, out=h_out_np)
-    barrier()
-    e2e_times = []
-    for _ in range(args.steps):
-        t1 = time.perf_counter()
-        _, c_e2e = ix.search_batch((h_seqs_np, offs), hit_bits=32, out=h_out_np)
-        e2e_times.append(time.perf_counter() - t1)
-    barrier()
-    # context for the end-to-end figure: what the host link gives for the same result buffer in one plain copy
-    link = []
-    for _ in range(2):
-        torch.cuda.synchronize()
-        t1 = time.perf_counter()
-        h_out.copy_(d_out, non_blocking=True)
-        torch.cuda.synchronize()
-        link.append(h_out.numel() * 4 / (time.perf_counter() - t1) / 1e9)
-    d2h_link_gbs = max(link)
-    clocks = None
+    res = search_arms(fb, ix, seqs, offs, args.k, args.read_len, n_reads, args.warmup, args.steps, barrier)
     sampler.stop_flag.set()
     sampler.join(timeout=3)
     clocks = sampler.summary()
-    e2e_total = float(sum(e2e_times))
-    assert c_e2e.positive == counts.positive
+    counts = res["counts"]
+    dev_total_ms, runs_total_ms = float(sum(res["dense_ms"])), float(sum(res["runs_ms"]))
+    e2e_total, e2e_dense_total = float(sum(res["e2e_runs_s"])), float(sum(res["e2e_dense_s"]))
 
     # ---- build-fmin arm (every rank builds from rank 0's inputs when sharded)
     build = None
@@ -495,58 +600,43 @@ def main():
             ix0.close()
 
     # ---- max over ranks
+    wall_dev = res["wall_dense_s"]
     if world > 1:
-        t = torch.tensor([dev_total_ms, e2e_total, wall_dev, runs_total_ms, e2e_runs_total], dtype=torch.float64, device="cuda")
+        t = torch.tensor([dev_total_ms, e2e_total, wall_dev, runs_total_ms, e2e_dense_total], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_total_ms, e2e_total, wall_dev, runs_total_ms, e2e_runs_total = (float(x) for x in t.cpu())
-    value = world * kmers_per_step * args.steps / (dev_total_ms / 1e3)
-    e2e_value = world * kmers_per_step * args.steps / e2e_total
+        dev_total_ms, e2e_total, wall_dev, runs_total_ms, e2e_dense_total = (float(x) for x in t.cpu())
+    total_kmers = world * kmers_per_step * args.steps
+    value = total_kmers / (dev_total_ms / 1e3)
 
     if rank == 0:
-        # ---- roofline of the dominant kernel (search_reads_kernel): algorithmic bytes from the access counters
-        sample = min(n_reads, 1_000_000)
-        ix.set_counting(True)
-        ix.search_device(d_seqs.data_ptr(), d_offs.data_ptr(), sample, sample * args.read_len, sample * (args.read_len - args.k + 1),
-                         d_out.data_ptr(), 4)
-        acc = ix.access_counters()
-        ix.set_counting(False)
-        scale = n_reads / sample
-        bytes_per_launch = algorithmic_bytes({k_: v * scale for k_, v in acc.items()}, n_bases, kmers_per_step)
-        avg_search_s = float(np.mean(search_ms)) / 1e3
         peak, peak_src = measured_peak()
-        achieved = bytes_per_launch / avg_search_s / 1e9
-        traffic = profiled_traffic()
-        if isinstance(traffic, dict):
-            traffic = [traffic]
-        traffic = next((t for t in traffic or [] if int(t.get("genome", 5_000_000)) == args.genome and int(t.get("k", 31)) == args.k), None)
-        l2_bytes = 126e6
-        regime = ("L2-resident at this config: the sector model counts every access as HBM traffic" if info["device_bytes"] < l2_bytes
-                  else f"{info['device_bytes'] / l2_bytes:.1f}x the 126 MB L2: random sectors mostly come from HBM")
         try:
             random_peaks = {b: fb.probe_random_sectors(local_rank, 8 << 30, 3, b) for b in (32, 64, 128)}
-            random_peak = random_peaks[32]
         except fb.FinitoError:
-            random_peaks, random_peak = None, None
-        roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": traffic["dram_bytes_per_read"] * n_reads if traffic else None,
-                    "traffic_source": (f"ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of a {traffic['reads_in_captured_launch']}-read launch "
-                                       f"({traffic['version']}), scaled per read to this launch") if traffic else None,
-                    "dram_gbs": traffic["dram_bytes_per_read"] * n_reads / avg_search_s / 1e9 if traffic else None,
-                    "dram_frac": traffic["dram_bytes_per_read"] * n_reads / avg_search_s / 1e9 / peak if traffic else None,
-                    "kernel": "search_reads_kernel", "kernel_ms": avg_search_s * 1e3, "kernel_share_of_step": float(np.sum(search_ms)) / dev_total_ms if world == 1 else None,
-                    "algorithmic_bytes_per_launch": bytes_per_launch, "algorithmic_bytes_per_kmer": bytes_per_launch / kmers_per_step,
-                    "peak_source": peak_src,
-                    "random_access_probe_gbs_by_bytes": random_peaks,
-                    "random_access_probe_note": "fin_probe_random_sectors, measured in this run: REQUESTED bytes/s of data-independent random 32/64/128-byte reads over an 8 GiB table "
-                                                "(no cache reuse at all; ncu shows the DRAM moves ~4x the requested bytes at 32 B: profiles/r1_probe_random_sectors_ncu.txt). "
-                                                "The search kernel's requests mostly hit L1/L2 (two ends of an interval, its LCS words and rank rows share a line), so its sector-model "
-                                                "figure is not bounded by this probe; its DRAM traffic is in `traffic`",
-                    "note": f"index is {info['device_bytes'] / 1e6:.1f} MB ({regime})"}
+            random_peaks = None
+        roofline = roofline_entry(fb, res, info, args.k, args.read_len, n_reads, args.genome, world, peak, peak_src, random_peaks)
+        roofline["random_access_probe_gbs_by_bytes"] = random_peaks
+        roofline["random_access_probe_note"] = ("fin_probe_random_sectors, measured in this run: REQUESTED bytes/s of data-independent random 32/64/128-byte reads "
+                                                "over an 8 GiB table; the DRAM moves ~4x the requested bytes at 32 B (profiles/r1_probe_random_sectors_ncu.txt), "
+                                                "that DRAM rate is the random-access ceiling `frac_of_random_access_ceiling` refers to")
+        hbm = None
+        if world == 1 and not args.no_hbm_arm:
+            try:
+                hbm = hbm_regime_arm(fb, args, local_rank, barrier, peak, peak_src, random_peaks)
+            except Exception as e:  # the headline line must not depend on the side measurement
+                hbm = {"unavailable": repr(e)[:300]}
+        roofline["hbm_regime"] = hbm
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             cpu = cpu_baseline(prefix, ds, args, all_threads=False, sample_reads=args.cpu_sample_reads)
+            allc = cpu_baseline(prefix, ds, args, all_threads=True, sample_reads=0)
+            cpu["all_cores"] = {k_: allc[k_] for k_ in ("value", "unit", "cores", "sample")}
+            cpu["ref_us_per_kmer_excl_io"] = cpu["detail"].get("ref_us_per_kmer_excl_io")
+            cpu["note"] = ("value = k-mer positions answered / wall time of the reference process (incl. index load and text output); "
+                           "ref_us_per_kmer_excl_io is the reference's own 'us/query (excluding I/O)' log line; all_cores = one reference process per host core")
             if build:
                 build["cpu_baseline"] = reference_build(ds, os.path.join(ds["dir"], "bench_build_ref"))
+        n_runs = res["n_runs"]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -555,21 +645,20 @@ def main():
                        "kmers_per_gpu_per_step": kmers_per_step, "found_fraction": counts.positive / counts.n_queries,
                        "index_nodes": info["n_nodes"], "index_device_bytes": info["device_bytes"], "parallelism": f"reads sharded x{world}, index replicated, no collective", "cpu_affinity": affinity,
                        "l2": "per-step inputs+outputs (1.5 GB reads, 9.6 GB hits at the default size) exceed the 126 MB L2; the index itself is L2-resident by design of this config",
+                       "value_is": "fin_search_device: the dense (unitig, offset) table written to HBM, inputs resident in HBM",
                        "index_build_s": build_s},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(n_bases + 8 * (n_reads + 1)),
-                    "d2h_bytes_per_step": int(kmers_per_step * 8), "ms_per_step": e2e_total / args.steps * 1e3,
-                    "api": "fin_search_batch32 (pinned host buffers, 3-stream sub-batch pipeline)",
-                    "d2h_link_gbs": d2h_link_gbs, "d2h_floor_ms_per_step": kmers_per_step * 8 / d2h_link_gbs / 1e6,
-                    "note": "the hits (8 B per k-mer) leave over PCIe: the step cannot be shorter than d2h_floor_ms_per_step on this host"},
-            "gpu_launches": int(gpu_launches), "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu, "build": build,
-            "runs": {"value": world * kmers_per_step * args.steps / (runs_total_ms / 1e3), "unit": UNIT, "ms_per_step": runs_total_ms / args.steps,
-                     "search_kernel_ms": float(np.mean(runs_search_ms)), "runs_per_read": n_runs / n_reads, "bytes_per_read": 16 * n_runs / n_reads + 8,
-                     "api": "fin_search_device_runs",
-                     "e2e": {"value": world * kmers_per_step * args.steps / e2e_runs_total, "unit": UNIT, "ms_per_step": e2e_runs_total / args.steps * 1e3,
-                             "h2d_bytes_per_step": int(n_bases + 8 * (n_reads + 1)), "d2h_bytes_per_step": int(16 * n_runs + 8 * (n_reads + 1)),
-                             "api": "fin_search_batch_runs (pinned host buffers)"},
-                     "expand_on_host_ms_per_step": expand_s_per_read * n_reads * 1e3, "expand_threads": cpu_threads()},
-            "search_parity": search_parity, "wall_s_device_arm": wall_dev,
+            "e2e": {"value": total_kmers / e2e_total, "unit": UNIT, "h2d_bytes_per_step": int(n_bases + 8 * (n_reads + 1)),
+                    "d2h_bytes_per_step": int(16 * n_runs + 8 * (n_reads + 1)), "ms_per_step": e2e_total / args.steps * 1e3,
+                    "api": "fin_search_batch_runs: pinned host buffers in, the complete answer out as run-length records (fin_run, 16 B per run; "
+                           "fin_expand_runs turns them into the dense table bit for bit)",
+                    "runs_per_read": n_runs / n_reads, "expand_on_host_ms_per_step": res["expand_ms_per_step"], "expand_threads": cpu_threads(),
+                    "dense": {"value": total_kmers / e2e_dense_total, "unit": UNIT, "ms_per_step": e2e_dense_total / args.steps * 1e3,
+                              "d2h_bytes_per_step": int(kmers_per_step * 8), "api": "fin_search_batch32 (dense table, 8 B per k-mer over PCIe)",
+                              "d2h_link_gbs": res["d2h_link_gbs"], "d2h_floor_ms_per_step": kmers_per_step * 8 / res["d2h_link_gbs"] / 1e6}},
+            "runs": {"value": total_kmers / (runs_total_ms / 1e3), "unit": UNIT, "ms_per_step": runs_total_ms / args.steps,
+                     "search_kernel_ms": float(np.mean(res["runs_kernel_ms"])), "api": "fin_search_device_runs (records sorted by read on the device)"},
+            "gpu_launches": int(res["launches_dense"]), "gpu_launches_runs_arm": int(res["launches_runs"]), "clocks": clocks, "roofline": roofline,
+            "cpu_baseline": cpu, "build": build, "search_parity": search_parity, "wall_s_device_arm": wall_dev,
         }
         print(json.dumps(line))
     if world > 1:

@@ -199,7 +199,8 @@ static void launch_search(const IndexView& v, const uint64_t* d_packed, const ui
     if (po.hit_bytes == 8) {
         SearchOut<int64_t> out{reinterpret_cast<HitPair<int64_t>*>(po.d_hits), d_out_offsets, po.d_fmask, po.sink, sf};
         if (sf) {
-            strand_filter_kernel<int64_t><<<fb, ft, 0, st>>>(v, d_packed, d_offsets, n_reads, n_strands, po.d_strand_flags, d_out_offsets, out.hits);
+            strand_filter_kernel<int64_t><<<fb, ft, 0, st>>>(v, d_packed, d_offsets, n_reads, n_strands, po.d_strand_flags, d_out_offsets, out.hits,
+                                                             count ? d_totals : nullptr);
             g_launches++;
         }
         if (count) launch_search_t<int64_t, true, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
@@ -209,7 +210,7 @@ static void launch_search(const IndexView& v, const uint64_t* d_packed, const ui
     SearchOut<int32_t> out{reinterpret_cast<HitPair<int32_t>*>(po.d_hits), d_out_offsets, po.d_fmask, po.sink, sf};
     if (sf) {
         strand_filter_kernel<int32_t><<<fb, ft, 0, st>>>(v, d_packed, d_offsets, n_reads, n_strands, po.d_strand_flags, d_out_offsets,
-                                                         po.hit_bytes == 4 ? out.hits : nullptr);
+                                                         po.hit_bytes == 4 ? out.hits : nullptr, count ? d_totals : nullptr);
         g_launches++;
     }
     if (po.hit_bytes == 4) {
@@ -272,6 +273,7 @@ static void accumulate(const SearchTotals& t, fin_search_counts& c, fin_access_c
     a.n_walk_words += (int64_t)t.n_walk_words;
     a.n_bases += (int64_t)t.n_bases;
     a.n_kmers += (int64_t)t.n_kmers;
+    a.n_filter_lookups += (int64_t)t.n_filter;
 }
 
 // -------------------------------------------------------------------------------------------------------
@@ -392,9 +394,9 @@ uint64_t DeviceIndex::search_device_runs(const void* d_seqs, const uint64_t* d_r
 struct SubBatchLimits {
     uint64_t reads, bases;
 };
-static SubBatchLimits sub_batch_limits(bool runs, uint64_t n_reads) {
-    // runs: at least four sub-batches per call so that the first copy-in stays short
-    SubBatchLimits l = runs ? SubBatchLimits{std::min<uint64_t>(1ull << 21, std::max<uint64_t>(1ull << 18, n_reads / 4)), 384ull << 20}
+static SubBatchLimits sub_batch_limits(bool runs, int turn) {
+    // runs: sub-batches double from 256 k reads to 2 M, so that the first copy-in (which nothing hides) stays short
+    SubBatchLimits l = runs ? SubBatchLimits{std::min<uint64_t>(1ull << 21, (1ull << 18) << std::min(turn, 8)), 384ull << 20}
                             : SubBatchLimits{1ull << 19, 48ull << 20};
     if (const char* e = getenv("FIN_SUB_READS")) if (atoll(e) > 0) l.reads = (uint64_t)atoll(e);
     if (const char* e = getenv("FIN_SUB_MBASES")) if (atoll(e) > 0) l.bases = (uint64_t)atoll(e) << 20;
@@ -511,8 +513,8 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
 
     uint64_t r0 = 0, out_pos = 0, max_len = 0;
     int turn = 0;
-    const SubBatchLimits lim = sub_batch_limits(false, n_reads);
     while (r0 < n_reads) {
+        const SubBatchLimits lim = sub_batch_limits(false, turn);
         uint64_t nkm = 0;
         const uint64_t r1 = cut_sub_batch(read_offsets, n_reads, r0, k, lim, nkm, max_len);
         if (out_pos + nkm > out_capacity) throw arg_error("out_capacity is smaller than the number of k-mer positions of the batch");
@@ -606,8 +608,8 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
     uint64_t r0 = 0, max_len = 0;
     int turn = 0;
     SearchSlot* prev = nullptr;
-    const SubBatchLimits lim = sub_batch_limits(true, n_reads);
     while (r0 < n_reads) {
+        const SubBatchLimits lim = sub_batch_limits(true, turn);
         uint64_t nkm = 0;
         const uint64_t r1 = cut_sub_batch(read_offsets, n_reads, r0, k, lim, nkm, max_len);
         SearchSlot& s = *slots_[turn % kSlots];

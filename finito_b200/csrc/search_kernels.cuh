@@ -21,6 +21,7 @@ struct SearchTotals {  // device-side accumulators of one launch
     unsigned int pad;
     unsigned long long next_read;  // work counter of the persistent search kernel
     unsigned long long n_runs;     // runs mode: records appended (RunSink::count)
+    unsigned long long n_filter;   // s-mer table lookups of the strand prefilter (counting mode only)
 };
 
 enum : unsigned { kErrBadBase = 1u, kErrWindowUnderflow = 2u, kErrLookupRange = 4u, kErrReadTooLong = 8u, kErrBadOffsets = 16u };
@@ -137,7 +138,8 @@ FIN_D uint32_t smer_revcomp(uint32_t x, const int s) {  // reverse the 2-bit gro
 // end of each candidate stretch backwards, so that one absent s-mer rules out `need` stretches at once (Boyer-Moore
 // style): a strand that does not match costs ~n_starts / need lookups instead of n_starts.
 template <bool RC>
-FIN_D bool strand_has_candidate(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t b0, const int n_starts, const int need) {
+FIN_D bool strand_has_candidate(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t b0, const int n_starts, const int need,
+                                unsigned& lookups) {
     const int s = ix.smer_s;
     const uint32_t mask = smer_mask(s);
     int a = 0;             // the stretch under test starts here
@@ -148,6 +150,7 @@ FIN_D bool strand_has_candidate(const IndexView& ix, const uint64_t* __restrict_
         while (j > stop) {
             uint32_t code = read_smer(packed, b0 + (uint64_t)j, mask);
             if (RC) code = smer_revcomp(code, s);
+            lookups++;
             if (!smer_present(ix.smer, code)) break;
             j--;
         }
@@ -159,13 +162,14 @@ FIN_D bool strand_has_candidate(const IndexView& ix, const uint64_t* __restrict_
 }
 
 // which strands of the read at bases [b0, b0 + len) of `packed` can hold a k-mer of the index
-FIN_D unsigned strand_candidates(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t b0, const uint64_t len) {
+FIN_D unsigned strand_candidates(const IndexView& ix, const uint64_t* __restrict__ packed, const uint64_t b0, const uint64_t len,
+                                 unsigned& lookups) {
     const int s = ix.smer_s, k = ix.k;
     if (ix.smer == nullptr) return kStrandFwd | kStrandRc;
     if (len < (uint64_t)k) return 0;
     const int n_starts = (int)len - s + 1, need = k - s + 1;
-    return (strand_has_candidate<false>(ix, packed, b0, n_starts, need) ? kStrandFwd : 0u) |
-           (strand_has_candidate<true>(ix, packed, b0, n_starts, need) ? kStrandRc : 0u);
+    return (strand_has_candidate<false>(ix, packed, b0, n_starts, need, lookups) ? kStrandFwd : 0u) |
+           (strand_has_candidate<true>(ix, packed, b0, n_starts, need, lookups) ? kStrandRc : 0u);
 }
 
 // ---- drop_first_char (common.hh:38-48), word-parallel ------------------------------------------------------
@@ -378,9 +382,6 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
     unsigned sflags = 0;         // strands of this read that are streamed (strand prefilter)
     // stream state (common.hh:80-103)
     int st = ST_IDLE, end = 0, c = 0;
-#ifdef FIN_PREFETCH_ROWS
-    int cn = 4;
-#endif
     int start = 0, kmer_start = 0;
     Ival I{0, 0}, Ik{0, 0};
     unsigned pendI = 0, pendK = 0;  // sides of the pending drops
@@ -419,12 +420,6 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
         const uint64_t b = b0 + (uint64_t)(strand ? len - 1 - end : end);
         const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(packed) + (b >> 4));
         c = (int)((w >> (2 * (b & 15))) & 3u) ^ (strand ? 3 : 0);
-#ifdef FIN_PREFETCH_ROWS
-        // the character after this one, when it sits in the same 16-base word (15 times out of 16): lets the step prefetch
-        // the rank rows the NEXT extension will read, together with the LCS words of the same line
-        const uint32_t nb = (uint32_t)(b & 15) + (strand ? 0xFFFFFFFFu : 1u);
-        cn = nb < 16u ? (int)((w >> (2 * nb)) & 3u) ^ (strand ? 3 : 0) : 4;
-#endif
     }
 
     // takes a new read; returns false (and stays idle) when the read has no k-mer
@@ -544,17 +539,6 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
         const idx_t il = I.l, ir = I.r + 1, kl = Ik.l, kr = Ik.r + 1;
         uint32_t uw = 0;
         uint64_t w_il = 0, w_ir = 0, w_kl = 0, w_kr = 0;
-#if defined(FIN_PREFETCH_ROWS) && !defined(FIN_EMU)
-        if (post && cn < 4) {  // rows A,C live in the first 32-byte sector of a line, G,T in the second
-            const char* lb = reinterpret_cast<const char*>(ix.lines);
-            const char* p0 = lb + ((size_t)(il >> 6) << 7) + ((cn >> 1) << 5);
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(p0));
-            if ((kl >> 6) != (il >> 6)) {
-                const char* p1 = lb + ((size_t)(kl >> 6) << 7) + ((cn >> 1) << 5);
-                asm volatile("prefetch.global.L1 [%0];" ::"l"(p1));
-            }
-        }
-#endif
         if (single) uw = __ldg(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
         if (pendI & kDropLeft) w_il = __ldg(lw + lcs_word_index(il));
         if (pendI & kDropRight) w_ir = __ldg(lw + lcs_word_index(ir));
@@ -708,11 +692,6 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
             const int j = end - (k - 1);
             const int i = strand ? nk - 1 - j : j;
             bool take = hit;
-#ifdef FIN_DENSE_READBACK  // experiment: the round-1 merge (read the forward strand's hit back) in dense mode
-            if (!RUNS) {
-                if (strand) take = hit && o[i].unitig == (HitT)-1;
-            } else
-#endif
             if (strand == 0) {
                 fm |= (uint32_t)hit << (j & 31);
                 if ((j & 31) == 31 && j != nk - 1) {  // the last word stays in the register for the reverse strand
@@ -853,11 +832,14 @@ __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) sea
 template <class HitT>
 static __global__ void strand_filter_kernel(const IndexView ix, const uint64_t* __restrict__ packed, const uint64_t* __restrict__ read_offsets,
                                             const uint64_t n_reads, const int n_strands, uint8_t* __restrict__ flags,
-                                            const uint64_t* __restrict__ out_offsets, HitPair<HitT>* __restrict__ hits) {
+                                            const uint64_t* __restrict__ out_offsets, HitPair<HitT>* __restrict__ hits,
+                                            SearchTotals* __restrict__ count_into) {
     const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_reads) return;
     const uint64_t b0 = read_offsets[r], len = read_offsets[r + 1] - b0;
-    unsigned f = strand_candidates(ix, packed, b0, len);
+    unsigned lookups = 0;
+    unsigned f = strand_candidates(ix, packed, b0, len, lookups);
+    if (count_into && lookups) atomicAdd(&count_into->n_filter, (unsigned long long)lookups);
     if (n_strands < 2) f &= kStrandFwd;
     flags[r] = (uint8_t)f;
     if (hits != nullptr && f == 0) {

@@ -143,7 +143,8 @@ int emu_search(const char* prefix, const char* seqs, const uint64_t* offs, uint6
             v.smer = smer.data();
             v.smer_s = s;
             for (uint64_t r = 0; r < n_reads; r++) {
-                unsigned f = strand_candidates(v, packed.data(), offs[r], offs[r + 1] - offs[r]);
+                unsigned lookups = 0;
+                unsigned f = strand_candidates(v, packed.data(), offs[r], offs[r + 1] - offs[r], lookups);
                 if (n_strands < 2) f &= kStrandFwd;
                 sflags[r] = (uint8_t)f;
                 if (strands_streamed) *strands_streamed += (f & 1) + ((f >> 1) & 1);
