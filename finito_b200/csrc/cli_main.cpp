@@ -16,6 +16,10 @@
 #include <thread>
 #include <vector>
 
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include "../../include/finito_b200.h"
 #include "seqio.hpp"
 
@@ -118,12 +122,8 @@ int build_fmin_command(int argc, char** argv) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// "(u,p) (u,p) ...\n" per read (search_fmin.hh:54-65)
-inline char* put_int(char* p, int64_t v) {
-    if (v < 0) {
-        *p++ = '-';
-        v = -v;
-    }
+// "(u,p) (u,p) ...\n" per read (search_fmin.hh:54-65), straight from the run-length answers of fin_search_batch_runs
+inline char* put_uint(char* p, uint64_t v) {
     char tmp[24];
     int n = 0;
     do {
@@ -134,22 +134,21 @@ inline char* put_int(char* p, int64_t v) {
     return p;
 }
 
-// Text of reads [r0, r1) of a batch into `out` (grown as needed, never zero-filled).  Worst case per hit: "(" + 20 + "," +
-// 20 + ")" + " " = 44 bytes; the bound actually used comes from the largest values the index can report.
 struct TextBuf {
     std::unique_ptr<char[]> p;
     size_t cap = 0, len = 0;
     void reserve(size_t n) {
         if (n > cap) {
-            p.reset(new char[n]);
+            p.reset(new char[n]);  // never zero-filled
             cap = n;
         }
     }
 };
 
-template <class HitT>
-void format_reads(const HitT* hits, const uint64_t* offsets, uint64_t r0, uint64_t r1, uint64_t hit0, int64_t k, size_t bytes_per_hit,
-                  TextBuf& out) {
+// Text of reads [r0, r1) of a batch.  Worst case per k-mer position: "(" + digits + "," + digits + ")" + " ", bounded by the
+// widest pair the index can report (or "(-1,-1) ").
+void format_reads(const fin_run* runs, const uint64_t* run_offsets, const uint64_t* offsets, uint64_t r0, uint64_t r1, int64_t k,
+                  size_t bytes_per_hit, TextBuf& out) {
     uint64_t n_hits = 0;
     for (uint64_t r = r0; r < r1; r++) {
         const uint64_t len = offsets[r + 1] - offsets[r];
@@ -157,18 +156,40 @@ void format_reads(const HitT* hits, const uint64_t* offsets, uint64_t r0, uint64
     }
     out.reserve(n_hits * bytes_per_hit + (r1 - r0) + 16);
     char* p = out.p.get();
-    const HitT* h = hits + 2 * hit0;
+    static const char kMiss[] = " (-1,-1)";
     for (uint64_t r = r0; r < r1; r++) {
         const uint64_t len = offsets[r + 1] - offsets[r];
         const uint64_t n = len >= (uint64_t)k ? len - k + 1 : 0;
-        for (uint64_t i = 0; i < n; i++, h += 2) {
-            if (i) *p++ = ' ';
-            *p++ = '(';
-            p = put_int(p, (int64_t)h[0]);
-            *p++ = ',';
-            p = put_int(p, (int64_t)h[1]);
-            *p++ = ')';
+        uint64_t i = 0;
+        auto misses_until = [&](uint64_t stop) {
+            for (; i < stop; i++) {
+                memcpy(p, kMiss + (i ? 0 : 1), 8);  // without the leading blank at the start of the line
+                p += i ? 8 : 7;
+            }
+        };
+        for (uint64_t t = run_offsets[r]; t < run_offsets[r + 1]; t++) {
+            const fin_run& q = runs[t];
+            misses_until(q.first_kmer);
+            const uint64_t cnt = q.len_rc & ~FIN_RUN_RC;
+            // "(unitig," is the same for the whole run
+            char head[24];
+            char* h = head;
+            *h++ = ' ';
+            *h++ = '(';
+            h = put_uint(h, q.unitig);
+            *h++ = ',';
+            const size_t hl = (size_t)(h - head);
+            uint64_t off = q.first_offset;
+            const bool rc = q.len_rc & FIN_RUN_RC;
+            for (uint64_t d = 0; d < cnt; d++, i++) {
+                memcpy(p, head + (i ? 0 : 1), hl);
+                p += i ? hl : hl - 1;
+                p = put_uint(p, off);
+                *p++ = ')';
+                off = rc ? off - 1 : off + 1;
+            }
         }
+        misses_until(n);
         *p++ = '\n';
     }
     out.len = (size_t)(p - out.p.get());
@@ -187,115 +208,206 @@ struct QueryTotals {
     int64_t found_fwd = 0, found_rc = 0, positive = 0, n_queries = 0;
 };
 
-// run_fmin_queries_streaming (search_fmin.hh:33-84) as a two-stage pipeline: the main thread searches batch i+1 on the
-// GPU(s) while a writer thread formats batch i on all host cores and writes it, in read order.  Hits travel as 2 x int32
-// whenever the index allows it, through pinned buffers.
-template <class HitT>
-void run_query_batches(const std::vector<fin_index*>& indexes, int64_t k, const fin::SeqBatch& all, FILE* out, QueryTotals& tot,
-                       size_t bytes_per_hit) {
-    const uint64_t n = all.size();
+// run_fmin_queries_streaming (search_fmin.hh:33-84) as a three-stage pipeline over a ring of batches: a parser thread
+// reads the next records of the file (bounded memory, whatever the file size), the main thread searches a batch on
+// the GPU(s) - the answers come back as run-length records, ~50 bytes per read instead of 8 bytes per k-mer -, a writer
+// thread formats the text on all host cores and writes it in read order (regular files: one pwrite per core).
+struct BatchSlot {
+    enum State { Empty, Parsed, Searched } state = Empty;
+    fin::SeqBatch reads;
+    bool last = false;  // set by the parser: no batch follows (this one may be empty)
+    struct Block {      // one contiguous block of the batch's reads per GPU
+        uint64_t r0 = 0, r1 = 0;
+        std::vector<uint64_t> offs, run_offsets;
+        fin_run* runs = nullptr;  // pinned
+        uint64_t cap = 0;
+        fin_search_counts counts{};
+    };
+    std::vector<Block> blocks;
+};
+
+void search_block(fin_index* index, const fin::SeqBatch& reads, BatchSlot::Block& b) {
+    const uint64_t n = b.r1 - b.r0, base = reads.offsets[b.r0];
+    b.offs.resize(n + 1);
+    for (uint64_t i = 0; i <= n; i++) b.offs[i] = reads.offsets[b.r0 + i] - base;
+    b.run_offsets.resize(n + 1);
+    b.counts = fin_search_counts{};
+    for (int attempt = 0;; attempt++) {
+        const uint64_t want = std::max<uint64_t>(4096, 8 * n);
+        if (b.cap < want) {
+            fin_host_free(b.runs);
+            b.runs = nullptr;
+            void* p = nullptr;
+            check(fin_host_alloc(want * sizeof(fin_run), &p));
+            b.runs = static_cast<fin_run*>(p);
+            b.cap = want;
+        }
+        uint64_t n_runs = 0;
+        const fin_status st = fin_search_batch_runs(index, reads.seqs.data() + base, b.offs.data(), n, b.run_offsets.data(), b.runs, b.cap,
+                                                    &n_runs, &b.counts);
+        if (st == FIN_ERR_ARG && n_runs > b.cap && attempt == 0) {  // more runs than expected: the call says how many
+            fin_host_free(b.runs);
+            b.runs = nullptr;
+            b.cap = 0;
+            void* p = nullptr;
+            check(fin_host_alloc(n_runs * sizeof(fin_run), &p));
+            b.runs = static_cast<fin_run*>(p);
+            b.cap = n_runs;
+            continue;
+        }
+        check(st);
+        return;
+    }
+}
+
+void run_query_file(const std::vector<fin_index*>& indexes, const fin_index_info& info, const std::string& infile, FILE* out,
+                    QueryTotals& tot) {
+    log_line("Running streaming queries from input file " + infile);
+    const int64_t k = info.k;
+    // "(u,p) ": the widest pair this index can report, or "(-1,-1) "
+    const size_t bytes_per_hit = (size_t)std::max(8, decimal_digits(info.n_unitigs) + decimal_digits(info.text_len) + 4);
     const uint64_t max_reads = 1u << 19, max_bases = 128ull << 20;
     const unsigned n_threads = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
-    // batch boundaries and the largest batch (sizes the two pinned hit buffers)
-    std::vector<uint64_t> cuts{0};
-    uint64_t max_hits = 1;
-    for (uint64_t r0 = 0; r0 < n;) {
-        uint64_t r1 = r0 + 1;
-        while (r1 < n && r1 - r0 < max_reads && all.offsets[r1 + 1] - all.offsets[r0] <= max_bases) r1++;
-        max_hits = std::max(max_hits, fin_count_kmers(all.offsets.data() + r0, r1 - r0, k));
-        cuts.push_back(r1);
-        r0 = r1;
-    }
-    struct Slot {
-        HitT* hits = nullptr;
-        std::vector<uint64_t> offs;
-        uint64_t n_hits = 0;
-        bool full = false;
-    } slots[2];
-    for (Slot& s : slots) {
-        void* p = nullptr;
-        check(fin_host_alloc(max_hits * 2 * sizeof(HitT), &p));
-        s.hits = static_cast<HitT*>(p);
-    }
+    constexpr int kRing = 3;
+    BatchSlot ring[kRing];
     std::mutex mu;
     std::condition_variable cv;
-    bool done = false;
-    std::string writer_error;
-    int64_t us_format = 0, us_write = 0, us_search = 0, us_wait_slot = 0;
+    std::string parse_error, write_error, search_error;
+    bool abort = false;
+    int64_t us_parse = 0, us_format = 0, us_write = 0, us_search = 0, us_wait_parser = 0, us_wait_writer = 0;
+    uint64_t n_batches = 0;
+
+    std::thread parser([&] {
+        try {
+            fin::SeqReader reader(infile);
+            for (size_t b = 0;; b++) {
+                BatchSlot& s = ring[b % kRing];
+                {
+                    std::unique_lock<std::mutex> lk(mu);
+                    cv.wait(lk, [&] { return s.state == BatchSlot::Empty || abort; });
+                    if (abort) return;
+                }
+                const int64_t t0 = now_micros();
+                s.reads.seqs.clear();
+                s.reads.offsets.clear();
+                const bool more = reader.next(s.reads, max_reads, max_bases);
+                us_parse += now_micros() - t0;
+                {
+                    std::lock_guard<std::mutex> lk(mu);
+                    s.last = !more;
+                    s.state = BatchSlot::Parsed;
+                }
+                cv.notify_all();
+                if (!more) return;
+            }
+        } catch (const std::exception& e) {
+            std::lock_guard<std::mutex> lk(mu);
+            parse_error = e.what();
+            abort = true;
+            cv.notify_all();
+        }
+    });
 
     std::thread writer([&] {
         std::vector<TextBuf> parts(n_threads);
+        const int fd = fileno(out);
+        struct stat sb;
+        // positional writes need a plain file that is not in append mode (O_APPEND ignores the offset of pwrite)
+        const bool regular = fd >= 0 && fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && !(fcntl(fd, F_GETFL) & O_APPEND);
+        off_t file_pos = 0;
+        if (regular) {
+            std::fflush(out);
+            file_pos = lseek(fd, 0, SEEK_CUR);
+        }
         for (size_t b = 0;; b++) {
-            Slot& s = slots[b & 1];
+            BatchSlot& s = ring[b % kRing];
             {
                 std::unique_lock<std::mutex> lk(mu);
-                cv.wait(lk, [&] { return s.full || done; });
-                if (!s.full) return;
+                cv.wait(lk, [&] { return s.state == BatchSlot::Searched || abort; });
+                if (abort) return;
             }
-            if (writer_error.empty()) {
-                const uint64_t nr = s.offs.size() - 1, per = (nr + n_threads - 1) / n_threads;
-                std::vector<uint64_t> hit_start(n_threads + 1, 0);
-                for (unsigned t = 0; t < n_threads; t++) {
-                    const uint64_t a = std::min<uint64_t>(nr, t * per), e = std::min<uint64_t>(nr, (t + 1) * per);
-                    hit_start[t + 1] = hit_start[t] + fin_count_kmers(s.offs.data() + a, e - a, k);
-                }
+            const bool last = s.last;
+            for (BatchSlot::Block& blk : s.blocks) {
+                if (!write_error.empty()) break;
+                const uint64_t nr = blk.r1 - blk.r0, per = (nr + n_threads - 1) / n_threads;
                 const int64_t t0 = now_micros();
                 std::vector<std::thread> workers;
                 for (unsigned t = 0; t < n_threads; t++) {
                     const uint64_t a = std::min<uint64_t>(nr, t * per), e = std::min<uint64_t>(nr, (t + 1) * per);
-                    workers.emplace_back([&, t, a, e] { format_reads<HitT>(s.hits, s.offs.data(), a, e, hit_start[t], k, bytes_per_hit, parts[t]); });
+                    workers.emplace_back([&, t, a, e] { format_reads(blk.runs, blk.run_offsets.data(), blk.offs.data(), a, e, k, bytes_per_hit, parts[t]); });
                 }
                 for (auto& w : workers) w.join();
                 const int64_t t1 = now_micros();
-                for (unsigned t = 0; t < n_threads; t++)
-                    if (parts[t].len && std::fwrite(parts[t].p.get(), 1, parts[t].len, out) != parts[t].len)
-                        writer_error = "Error writing the output file";
+                if (regular) {  // the parts land at known offsets: one pwrite per core
+                    std::vector<off_t> at(n_threads + 1, file_pos);
+                    for (unsigned t = 0; t < n_threads; t++) at[t + 1] = at[t] + (off_t)parts[t].len;
+                    std::vector<char> failed(n_threads, 0);
+                    workers.clear();
+                    for (unsigned t = 0; t < n_threads; t++)
+                        workers.emplace_back([&, t] {
+                            size_t done = 0;
+                            while (done < parts[t].len) {
+                                const ssize_t w = pwrite(fd, parts[t].p.get() + done, parts[t].len - done, at[t] + (off_t)done);
+                                if (w <= 0) {
+                                    failed[t] = 1;
+                                    return;
+                                }
+                                done += (size_t)w;
+                            }
+                        });
+                    for (auto& w : workers) w.join();
+                    for (char f : failed)
+                        if (f) write_error = "Error writing the output file";
+                    file_pos = at[n_threads];
+                } else {
+                    for (unsigned t = 0; t < n_threads; t++)
+                        if (parts[t].len && std::fwrite(parts[t].p.get(), 1, parts[t].len, out) != parts[t].len)
+                            write_error = "Error writing the output file";
+                }
                 us_format += t1 - t0;
                 us_write += now_micros() - t1;
             }
             {
                 std::lock_guard<std::mutex> lk(mu);
-                s.full = false;
+                s.state = BatchSlot::Empty;
+                if (!write_error.empty()) abort = true;
             }
             cv.notify_all();
+            if (last || !write_error.empty()) {
+                if (regular) lseek(fd, file_pos, SEEK_SET);  // later fwrite()s of this stream (none today) continue behind the text
+                return;
+            }
         }
     });
 
-    std::string search_error;
-    for (size_t b = 0; b + 1 < cuts.size() && search_error.empty(); b++) {
-        const uint64_t r0 = cuts[b], r1 = cuts[b + 1];
-        Slot& s = slots[b & 1];
+    for (size_t b = 0;; b++) {
+        BatchSlot& s = ring[b % kRing];
         const int64_t tw = now_micros();
         {
             std::unique_lock<std::mutex> lk(mu);
-            cv.wait(lk, [&] { return !s.full; });
+            cv.wait(lk, [&] { return s.state == BatchSlot::Parsed || abort; });
+            if (abort) break;
         }
         const int64_t ts = now_micros();
-        us_wait_slot += ts - tw;
-        s.offs.assign(r1 - r0 + 1, 0);
-        for (uint64_t i = r0; i <= r1; i++) s.offs[i - r0] = all.offsets[i] - all.offsets[r0];
-        s.n_hits = fin_count_kmers(s.offs.data(), r1 - r0, k);
+        us_wait_parser += ts - tw;
+        const uint64_t n = s.reads.size();
         // reads are independent (search_fmin.hh:43): the batch is cut into one contiguous block per GPU, every GPU holds
-        // the whole index, one host thread drives each handle; the hits land in disjoint ranges of the same buffer
-        const size_t n_dev = std::max<size_t>(1, std::min<size_t>(indexes.size(), (size_t)(r1 - r0)));
-        std::vector<fin_search_counts> cs(n_dev);
+        // the whole index, one host thread drives each handle
+        const size_t n_dev = std::max<size_t>(1, std::min<size_t>(indexes.size(), (size_t)std::max<uint64_t>(1, n)));
+        if (s.blocks.size() < n_dev) s.blocks.resize(n_dev);
         std::vector<std::string> errors(n_dev);
         std::vector<std::thread> gpu_threads;
-        const uint64_t nb_reads = r1 - r0;
-        for (size_t d = 0; d < n_dev; d++) {
-            const uint64_t a = nb_reads * d / n_dev, e = nb_reads * (d + 1) / n_dev;
-            const uint64_t hit_a = fin_count_kmers(s.offs.data(), a, k), hit_n = fin_count_kmers(s.offs.data() + a, e - a, k);
-            auto work = [&, d, a, e, hit_a, hit_n] {
-                std::vector<uint64_t> sub(s.offs.begin() + (long)a, s.offs.begin() + (long)e + 1);
-                for (uint64_t& o : sub) o -= s.offs[a];
-                cs[d] = fin_search_counts{};
-                const char* seqs = all.seqs.data() + all.offsets[r0] + s.offs[a];
-                fin_status st;
-                if (sizeof(HitT) == 4)
-                    st = fin_search_batch32(indexes[d], seqs, sub.data(), e - a, reinterpret_cast<int32_t*>(s.hits) + 2 * hit_a, hit_n, &cs[d]);
-                else
-                    st = fin_search_batch(indexes[d], seqs, sub.data(), e - a, reinterpret_cast<int64_t*>(s.hits) + 2 * hit_a, hit_n, &cs[d]);
-                if (st != FIN_OK) errors[d] = fin_last_error();  // thread-local message: read it on this thread
+        for (size_t d = 0; d < s.blocks.size(); d++) {
+            BatchSlot::Block& blk = s.blocks[d];
+            blk.r0 = d < n_dev ? n * d / n_dev : n;
+            blk.r1 = d < n_dev ? n * (d + 1) / n_dev : n;
+            if (d >= n_dev) continue;
+            auto work = [&, d] {
+                try {
+                    search_block(indexes[d], s.reads, s.blocks[d]);
+                } catch (const std::exception& e) {
+                    errors[d] = e.what();
+                }
             };
             if (n_dev == 1) work();
             else gpu_threads.emplace_back(work);
@@ -303,44 +415,41 @@ void run_query_batches(const std::vector<fin_index*>& indexes, int64_t k, const 
         for (auto& t : gpu_threads) t.join();
         for (size_t d = 0; d < n_dev; d++) {
             if (!errors[d].empty()) search_error = errors[d];
-            tot.found_fwd += cs[d].found_fwd;
-            tot.found_rc += cs[d].found_rc;
-            tot.positive += cs[d].positive;
-            tot.n_queries += cs[d].n_queries;
+            const fin_search_counts& c = s.blocks[d].counts;
+            tot.found_fwd += c.found_fwd;
+            tot.found_rc += c.found_rc;
+            tot.positive += c.positive;
+            tot.n_queries += c.n_queries;
         }
         us_search += now_micros() - ts;
-        if (!search_error.empty()) break;
+        n_batches++;
+        const bool last = s.last;
         {
             std::lock_guard<std::mutex> lk(mu);
-            s.full = true;
+            if (!search_error.empty()) abort = true;
+            else s.state = BatchSlot::Searched;
         }
         cv.notify_all();
+        if (last || !search_error.empty()) break;
+        const int64_t tq = now_micros();
+        {   // the slot the next batch will use must have been written out: that wait is the writer's backlog
+            BatchSlot& nx = ring[(b + 1) % kRing];
+            std::unique_lock<std::mutex> lk(mu);
+            cv.wait(lk, [&] { return nx.state != BatchSlot::Searched || abort; });
+        }
+        us_wait_writer += now_micros() - tq;
     }
-    {
-        std::unique_lock<std::mutex> lk(mu);
-        cv.wait(lk, [&] { return (!slots[0].full && !slots[1].full) || !search_error.empty(); });
-        done = true;
-    }
-    cv.notify_all();
+    parser.join();
     writer.join();
-    for (Slot& s : slots) fin_host_free(s.hits);
-    log_line("pipeline: GPU search " + std::to_string(us_search / 1000) + " ms, waiting for the writer " + std::to_string(us_wait_slot / 1000) +
-             " ms | writer: formatting " + std::to_string(us_format / 1000) + " ms, fwrite " + std::to_string(us_write / 1000) + " ms (" +
-             std::to_string(cuts.size() - 1) + " batches)");
+    for (BatchSlot& s : ring)
+        for (BatchSlot::Block& blk : s.blocks) fin_host_free(blk.runs);
+    log_line("pipeline: parser " + std::to_string(us_parse / 1000) + " ms | GPU search " + std::to_string(us_search / 1000) +
+             " ms (waited " + std::to_string(us_wait_parser / 1000) + " ms for the parser, " + std::to_string(us_wait_writer / 1000) +
+             " ms for the writer) | writer: formatting " + std::to_string(us_format / 1000) + " ms, write " + std::to_string(us_write / 1000) +
+             " ms (" + std::to_string(n_batches) + " batches)");
+    if (!parse_error.empty()) throw std::runtime_error(parse_error);
     if (!search_error.empty()) throw std::runtime_error(search_error);
-    if (!writer_error.empty()) throw std::runtime_error(writer_error);
-}
-
-void run_query_file(const std::vector<fin_index*>& indexes, const fin_index_info& info, const std::string& infile, FILE* out,
-                    QueryTotals& tot) {
-    log_line("Running streaming queries from input file " + infile);
-    fin::SeqBatch all;
-    fin::append_sequences(infile, all);
-    // "(u,p) ": the widest pair this index can report, or "(-1,-1) "
-    const size_t bytes_per_hit = (size_t)std::max(8, decimal_digits(info.n_unitigs) + decimal_digits(info.text_len) + 4);
-    const bool fits32 = info.n_unitigs < 0x7FFFFFFF && info.text_len < 0x7FFFFFFF;
-    if (fits32) run_query_batches<int32_t>(indexes, info.k, all, out, tot, bytes_per_hit);
-    else run_query_batches<int64_t>(indexes, info.k, all, out, tot, bytes_per_hit);
+    if (!write_error.empty()) throw std::runtime_error(write_error);
 }
 
 int search_fmin_command(int argc, char** argv) {

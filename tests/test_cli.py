@@ -147,3 +147,83 @@ def test_cli_input_formats_fastq_gzip_and_file_lists(tmp_path):
     assert run("build-fmin", "-o", prefix, "-i", os.path.join(d, "input.sbwt"), "-u", ugz).returncode == 0
     for suf in H.INDEX_SUFFIXES:
         assert H.files_equal(prefix + suf, os.path.join(d, "ref" + suf)), suf
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(not H.have_ref(), reason="needs the prebuilt reference binary oracle/_ref/finito_ref")
+def test_cli_one_million_reads_of_config_2_against_the_reference(tmp_path):
+    """BASELINE.json configs[1] at 1 M reads (120 M k-mer positions, 1.3 GB of text): the CLI's output against the
+    unmodified reference binary run as one process per host core over consecutive shards of the same reads
+    (the reference is single-threaded, search_fmin.hh:43), sha256 of the concatenated text."""
+    import hashlib
+    from concurrent.futures import ThreadPoolExecutor
+
+    n = 1_000_000
+    ds = make_dataset("bench", genome_len=5_000_000, k=31, n_reads=n, read_len=150, seed=20260102, families=50)
+    seqs, offs = ds["reads"]
+    prefix = str(tmp_path / "ix")
+    assert run("build-fmin", "-o", prefix, "-i", ds["sbwt"], "-u", ds["unitigs"]).returncode == 0
+    rec = np.empty((n, 150 + 3), dtype=np.uint8)
+    rec[:, 0], rec[:, 1], rec[:, -1] = ord(">"), ord("\n"), ord("\n")
+    rec[:, 2:152] = seqs.reshape(n, 150)
+    q = str(tmp_path / "reads.fna")
+    rec.tofile(q)
+    out = str(tmp_path / "ours.txt")
+    r = run("search-fmin", "-i", prefix, "-q", q, "-o", out)
+    assert r.returncode == 0, r.stderr[-500:]
+    shards = max(1, len(os.sched_getaffinity(0)))
+    per = (n + shards - 1) // shards
+    paths = []
+    for s in range(shards):
+        a, b = s * per, min(n, (s + 1) * per)
+        if a < b:
+            p = str(tmp_path / f"shard{s}.fna")
+            rec[a:b].tofile(p)
+            paths.append(p)
+    with ThreadPoolExecutor(len(paths)) as ex:
+        rcs = list(ex.map(lambda p: H.ref_run("search-fmin", "-i", prefix, "-q", p, "-o", p + ".out").returncode, paths))
+    assert rcs == [0] * len(paths)
+    want = hashlib.sha256()
+    for p in paths:
+        with open(p + ".out", "rb") as f:
+            for blk in iter(lambda: f.read(1 << 24), b""):
+                want.update(blk)
+    got = hashlib.sha256()
+    with open(out, "rb") as f:
+        for blk in iter(lambda: f.read(1 << 24), b""):
+            got.update(blk)
+    assert got.hexdigest() == want.hexdigest()
+
+
+@pytest.mark.gpu
+def test_cli_streams_many_batches_and_appends(tmp_path):
+    """More reads than one batch of the pipeline (2^19) with ragged lengths, multi-line FASTA records and an output that is
+    opened in append mode by the shell (no positional writes there): same text as the library call."""
+    ds = make_dataset("cli", genome_len=2_000_000, k=31, n_reads=20_000, read_len=150, seed=108)
+    seqs, offs = ds["reads"]
+    prefix = str(tmp_path / "ix")
+    assert run("build-fmin", "-o", prefix, "-i", ds["sbwt"], "-u", ds["unitigs"]).returncode == 0
+    raw = seqs.tobytes()
+    rng = np.random.default_rng(3)
+    reads = []
+    for i in range(600_000):
+        j = int(rng.integers(0, 20_000))
+        r = raw[int(offs[j]):int(offs[j + 1])]
+        reads.append(r[: int(rng.integers(1, 151))] if i % 5 == 0 else r)
+    q = str(tmp_path / "many.fna")
+    with open(q, "wb") as f:
+        for i, r in enumerate(reads):
+            f.write(b">x\n" + (r[:70] + b"\n" + r[70:] if i % 3 == 0 and len(r) > 70 else r) + b"\n")
+    s2, o2 = H.batch_of(reads)
+    with fb.FinimizerIndex.load(prefix) as ix:
+        hits, _ = ix.search_batch((s2, o2))
+        k = ix.info["k"]
+    want = fb.format_hits(hits, [max(0, len(r) - k + 1) for r in reads]).encode()
+    out = str(tmp_path / "out.txt")
+    r = run("search-fmin", "-i", prefix, "-q", q, "-o", out)
+    assert r.returncode == 0, r.stderr[-400:]
+    assert open(out, "rb").read() == want
+    app = str(tmp_path / "app.txt")
+    open(app, "wb").write(b"header line\n")
+    rc = subprocess.run(f"{CLI} search-fmin -i {prefix} -q {q} >> {app}", shell=True, capture_output=True).returncode
+    assert rc == 0 and open(app, "rb").read() == b"header line\n" + want
