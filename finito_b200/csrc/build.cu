@@ -9,6 +9,8 @@
 #include <ctime>
 
 #include "build_host.hpp"
+#include <thread>
+
 #include "engine.hpp"
 #include "build_kernels.cuh"
 
@@ -83,7 +85,9 @@ static DevBuf<uint8_t> lcs_on_device(const DeviceSbwt& d) {
     uint8_t* cur = last.p;
     uint8_t* nxt = next.p;
     for (int round = 0; round < (int)d.args.k; round++) {
-        lcs_round_kernel<<<(unsigned)((d.nw + 127) / 128), 128>>>(d.args, cur, nxt, lcs.p, (uint8_t)round);
+        const uint64_t words_per_block = 32ull * kLcsWarpsPerBlock;
+        lcs_round_warp_kernel<<<(unsigned)((d.nw + words_per_block - 1) / words_per_block), 32 * kLcsWarpsPerBlock>>>(d.args, cur, nxt, lcs.p,
+                                                                                                             (uint8_t)round);
         g_launches++;
         std::swap(cur, nxt);
     }
@@ -118,17 +122,21 @@ template <class T> static PackedVec pack_on_device(const T* d_in, uint64_t n, in
 }
 
 // LCS file -> padded bytes on the device
-static DevBuf<uint8_t> lcs_bytes_from_packed(const PackedVec& lcs, uint64_t nw) {
+static DevBuf<uint8_t> lcs_bytes_from_packed(const PackedVec& lcs, uint64_t nw, int64_t k) {
     if (lcs.width > 8) throw format_error("LCS wider than 8 bits (k <= 255)");
     const uint64_t n = lcs.size(), padded = nw * 64 + 64;
     DevBuf<uint8_t> bytes(padded);
     FIN_CUDA(cudaMemset(bytes.p, 0, padded));
     DevBuf<uint64_t> words = to_device(lcs.words);
     if (n) {
-        unpack_bits_to_bytes_kernel<<<(unsigned)((n + 255) / 256), 256>>>(words.p, n, lcs.width, bytes.p);
+        DevBuf<unsigned int> d_bad(1);
+        FIN_CUDA(cudaMemset(d_bad.p, 0, 4));
+        unpack_bits_to_bytes_kernel<<<(unsigned)((n + 255) / 256), 256>>>(words.p, n, lcs.width, bytes.p, (uint32_t)k, d_bad.p);
         g_launches++;
         FIN_CUDA(cudaGetLastError());
-        FIN_CUDA(cudaDeviceSynchronize());
+        unsigned bad = 0;
+        FIN_CUDA(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
+        if (bad) throw format_error("the LCS file does not belong to this SBWT: LCS[0] must be 0 and every value below k");
     }
     return bytes;
 }
@@ -151,7 +159,7 @@ DevBuf<uint64_t> index_lines_device(const IndexHost& h) {
     if (N >= kIndexLimit32) throw limit_error("index too large for the 32-bit column/text positions of this build");
     if (N < 2) throw domain_error("SBWT with fewer than 2 columns");
     const DeviceSbwt ds = upload_sbwt(h.sbwt);
-    DevBuf<uint8_t> lcs = lcs_bytes_from_packed(h.lcs, ds.nw);
+    DevBuf<uint8_t> lcs = lcs_bytes_from_packed(h.lcs, ds.nw, h.sbwt.k);
     if (h.ustart.words.size() < ds.nw || h.fmin.words.size() < ds.nw) throw format_error("Ustart / fmin bit vectors shorter than the SBWT");
     DevBuf<uint64_t> us(ds.nw), fm(ds.nw);
     FIN_CUDA(cudaMemcpy(us.p, h.ustart.words.data(), ds.nw * 8, cudaMemcpyHostToDevice));
@@ -583,7 +591,7 @@ static PackedVec lcs_for_build(const SbwtHost& sbwt, const DeviceSbwt& ds, const
     if (!lcs_path.empty()) {
         PackedVec lcs = load_packed_file(lcs_path, 0);
         if (lcs.size() != (uint64_t)sbwt.n_nodes) throw format_error("LCS length differs from the number of SBWT columns");
-        d_bytes = lcs_bytes_from_packed(lcs, ds.nw);
+        d_bytes = lcs_bytes_from_packed(lcs, ds.nw, sbwt.k);
         return lcs;
     }
     d_bytes = lcs_on_device(ds);
@@ -602,7 +610,7 @@ RarestBuilder* builder_open(const std::string& sbwt_path, const std::string& uni
     check_sbwt_limits(sbwt);
     const DeviceSbwt ds = upload_sbwt(sbwt);
     DevBuf<uint8_t> d_lcs;
-    PackedVec lcs = lcs_for_build(sbwt, ds, lcs_path, out_prefix, rank == 0, d_lcs);
+    PackedVec lcs = lcs_for_build(sbwt, ds, lcs_path, out_prefix, false, d_lcs);  // rank 0 writes it with the other files (finish)
     SeqBatch unitigs;
     append_sequences(files[0], unitigs);
     return new RarestBuilder(std::move(sbwt), std::move(lcs), ds, std::move(d_lcs), unitigs, rank, world);
@@ -649,6 +657,21 @@ std::string build_fmin_device(const std::string& sbwt_path, const std::string& u
     g_build_timing = fin_build_timing{};
     const double t_begin = wall_ms();
     const std::vector<std::string> files = unitig_file_list(unitig_path);
+    // the unitig file is read and parsed by a second host thread while this one loads the SBWT and computes the LCS
+    SeqBatch unitigs;
+    std::string unitig_error;
+    std::thread unitig_reader([&] {
+        try {
+            append_sequences(files[0], unitigs);
+        } catch (const std::exception& e) {
+            unitig_error = e.what();
+            if (unitig_error.empty()) unitig_error = "cannot read the unitig file";
+        }
+    });
+    struct Joiner {
+        std::thread& t;
+        ~Joiner() { if (t.joinable()) t.join(); }
+    } joiner{unitig_reader};
     SbwtHost sbwt = load_sbwt_file(sbwt_path, true);
     if (type != "rarest" && type != "shortest" && type != "verify") throw arg_error("Error: unknown type: " + type);
     select_device(device);
@@ -657,12 +680,13 @@ std::string build_fmin_device(const std::string& sbwt_path, const std::string& u
     const double t_loaded = wall_ms();
     const DeviceSbwt ds = upload_sbwt(sbwt);
     DevBuf<uint8_t> d_lcs;
-    PackedVec lcs = lcs_for_build(sbwt, ds, lcs_path, out_prefix, true, d_lcs);
+    // rarest writes <prefix>.LCS.sdsl with the other six files at the end; the stats types only write this one
+    PackedVec lcs = lcs_for_build(sbwt, ds, lcs_path, out_prefix, type != "rarest", d_lcs);
     const double t_lcs = wall_ms();
 
     std::string result;
-    SeqBatch unitigs;
-    append_sequences(files[0], unitigs);
+    unitig_reader.join();
+    if (!unitig_error.empty()) throw io_error(unitig_error);
     const double t_unitigs = wall_ms();
     g_build_timing.load_sbwt_ms = (float)(t_loaded - t_begin);
     g_build_timing.lcs_ms = (float)(t_lcs - t_loaded);

@@ -1,7 +1,9 @@
 // Kernels of the build-fmin path.  The per-thread bodies are FIN_D functions so that tests/emu can run the
 // same source on the host; build.cu holds the host driver.
-//   lcs_round_kernel     : one round of the label-propagation LCS algorithm — update + propagate fused
-//                          (include/lcs_basic_parallel_algorithm.hpp:10-27, rounds :80-109)
+//   lcs_round_warp_kernel: one round of the label-propagation LCS algorithm — update + propagate fused, one warp per
+//                          2048 columns, edges compacted in shared memory and written out as 16-byte stores
+//                          (include/lcs_basic_parallel_algorithm.hpp:10-27, rounds :80-109); lcs_round_word is the
+//                          same round for one 64-column word, the form tests/emu runs on the host
 //   first_kmer_kernel    : SBWT column of every unitig's first k-mer = colex sort key and Ustart mark
 //                          (include/PackedStrings.hh:104-137, SBWT.hh:320-347)
 //   build_stream_kernel  : FinimizerIndexBuilder::add_sequence (include/FinimizerIndex.hh:321-389) over chunks
@@ -343,11 +345,99 @@ static __global__ void lcs_init_kernel(const LcsArgs a, uint8_t* __restrict__ la
     lcs[i] = a.k;  // "not set yet" (:76-78)
 }
 
-static __global__ void __launch_bounds__(128) lcs_round_kernel(const LcsArgs a, const uint8_t* __restrict__ last,
-                                                               uint8_t* __restrict__ next, uint8_t* __restrict__ lcs,
-                                                               uint8_t round) {
-    const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (w < a.n_words) lcs_round_word(a, last, next, lcs, w, round);
+// The same round, one WARP per 32 consecutive words (2048 columns).  lcs_round_word's scatter issues up to 256 byte
+// stores per thread, every one of them a separate L2 transaction of a few useful bytes (5 % of the HBM rate).  The
+// edges of 32 consecutive words with label c land on ONE contiguous stretch of `next` (C[c] + rank_c is monotone), so
+// the lanes compact their bytes into shared memory at the offset their word's rank gives them and the warp then copies
+// the stretch out with aligned 16-byte stores (byte stores only at its two ragged ends).
+constexpr int kLcsWarpsPerBlock = 4;
+constexpr int kLcsStageBytes = 2048 + 32;  // 32 words x 64 edges, + the 16-byte misalignment of the destination
+
+static __global__ void __launch_bounds__(32 * kLcsWarpsPerBlock) lcs_round_warp_kernel(const LcsArgs a, const uint8_t* __restrict__ last,
+                                                                                     uint8_t* __restrict__ next, uint8_t* __restrict__ lcs,
+                                                                                     const uint8_t round) {
+    __shared__ __align__(16) uint8_t stage[kLcsWarpsPerBlock][4][kLcsStageBytes];
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint64_t w0 = ((uint64_t)blockIdx.x * kLcsWarpsPerBlock + warp) * 32u;
+    if (w0 >= a.n_words) return;  // the whole warp
+    const uint64_t w = w0 + lane;
+    const bool live = w < a.n_words;
+    const uint64_t i0 = w * 64;
+    if (w == 0) next[0] = 0;  // the root has no incoming edge (:86)
+    uint32_t lv[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) lv[j] = 0;
+    if (live) {  // update (:21-27), as in lcs_round_word
+        uint32_t cv[16];
+        const uint4* lp = reinterpret_cast<const uint4*>(last + i0);
+        const uint4* cp = reinterpret_cast<const uint4*>(lcs + i0);
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+            const uint4 x = lp[q], y = cp[q];
+            lv[4 * q] = x.x; lv[4 * q + 1] = x.y; lv[4 * q + 2] = x.z; lv[4 * q + 3] = x.w;
+            cv[4 * q] = y.x; cv[4 * q + 1] = y.y; cv[4 * q + 2] = y.z; cv[4 * q + 3] = y.w;
+        }
+        uint32_t prev = i0 ? last[i0 - 1] : 0xFFu;
+        bool changed = false;
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const uint32_t ch = (lv[j] >> (8 * b)) & 0xFFu;
+                const uint32_t cur = (cv[j] >> (8 * b)) & 0xFFu;
+                if (cur == a.k && ch != prev && i0 + 4 * j + b < a.n) {
+                    cv[j] = (cv[j] & ~(0xFFu << (8 * b))) | ((uint32_t)round << (8 * b));
+                    changed = true;
+                }
+                prev = ch;
+            }
+        }
+        if (changed) {
+            uint4* cq = reinterpret_cast<uint4*>(lcs + i0);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                uint4 y;
+                y.x = cv[4 * q]; y.y = cv[4 * q + 1]; y.z = cv[4 * q + 2]; y.w = cv[4 * q + 3];
+                cq[q] = y;
+            }
+        }
+    }
+    // propagate (:10-19)
+    uint64_t base[4];
+    unsigned total[4];
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const uint64_t bits = live ? a.rows[(uint64_t)c * a.n_words + w] : 0;
+        const uint64_t my_dst = (uint64_t)a.C[c] + (live ? a.word_dst[(uint64_t)c * a.n_words + w] : 0u);
+        const uint64_t b0 = __shfl_sync(0xFFFFFFFFu, my_dst, 0);
+        base[c] = b0;
+        const unsigned head = (unsigned)(b0 & 15u);
+        const unsigned off = live ? (unsigned)(my_dst - b0) : 0u;
+        total[c] = __reduce_max_sync(0xFFFFFFFFu, live ? off + (unsigned)__popcll(bits) : 0u);
+        uint8_t* sp = stage[warp][c] + head + off;
+#pragma unroll
+        for (int j = 0; j < 16; j++) {
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                if ((bits >> (4 * j + b)) & 1ULL) *sp++ = (uint8_t)((lv[j] >> (8 * b)) & 0xFFu);
+            }
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const unsigned head = (unsigned)(base[c] & 15u), end = head + total[c];  // bytes [head, end) of the stage are valid
+        uint8_t* g = next + (base[c] - head);                                     // 16-byte aligned
+        const uint8_t* sp = stage[warp][c];
+        for (unsigned q = lane; q * 16u < end; q += 32u) {
+            const unsigned lo = q * 16u, hi = lo + 16u;
+            if (lo >= head && hi <= end) {
+                *reinterpret_cast<uint4*>(g + lo) = *reinterpret_cast<const uint4*>(sp + lo);
+            } else {
+                for (unsigned x = lo < head ? head : lo; x < (hi < end ? hi : end); x++) g[x] = sp[x];
+            }
+        }
+    }
 }
 
 static __global__ void first_kmer_kernel(const IndexView ix, const uint64_t* __restrict__ text,
@@ -393,13 +483,18 @@ __global__ void pack_bits_kernel(const T* __restrict__ in, uint64_t n, uint32_t 
 }
 
 // the inverse, for widths <= 8 (an LCS file given with --lcs): one thread per element
-static __global__ void unpack_bits_to_bytes_kernel(const uint64_t* __restrict__ words, uint64_t n, uint32_t width, uint8_t* __restrict__ out) {
+// also checks what the word-parallel drop_first_char relies on (search_kernels.cuh): LCS[0] = 0 and every value < k
+// (the reference guards the scan with `first > 0`, common.hh:43; a foreign or corrupt file must not send it out of bounds)
+static __global__ void unpack_bits_to_bytes_kernel(const uint64_t* __restrict__ words, uint64_t n, uint32_t width, uint8_t* __restrict__ out,
+                                                   uint32_t k, unsigned int* __restrict__ bad) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint64_t bit = i * width, wi = bit >> 6, off = bit & 63;
     uint64_t v = words[wi] >> off;
     if (off + width > 64) v |= words[wi + 1] << (64 - off);
-    out[i] = (uint8_t)(v & ((1ULL << width) - 1ULL));
+    v &= (1ULL << width) - 1ULL;
+    out[i] = (uint8_t)v;
+    if (v >= k || (i == 0 && v != 0)) atomicOr(bad, 1u);
 }
 
 // clears the bits past n in the last word of each of the 4 rows (they never count, SBWT.hh:395-424 stores whole words)

@@ -17,6 +17,7 @@
 #include <vector>
 
 #include <fcntl.h>
+#include <sys/mman.h>
 #include <sys/stat.h>
 #include <unistd.h>
 
@@ -338,13 +339,27 @@ void run_query_file(const std::vector<fin_index*>& indexes, const fin_index_info
                 }
                 for (auto& w : workers) w.join();
                 const int64_t t1 = now_micros();
-                if (regular) {  // the parts land at known offsets: one pwrite per core
+                if (regular) {  // the parts land at known offsets: every core copies its own
                     std::vector<off_t> at(n_threads + 1, file_pos);
                     for (unsigned t = 0; t < n_threads; t++) at[t + 1] = at[t] + (off_t)parts[t].len;
+                    const size_t total = (size_t)(at[n_threads] - file_pos);
                     std::vector<char> failed(n_threads, 0);
                     workers.clear();
+                    // through a shared mapping when the descriptor allows it (read-write open): the page cache is filled by all
+                    // cores at once; buffered write()s to ONE file serialise on the inode lock
+                    char* map = nullptr;
+                    const off_t map_off = file_pos & ~(off_t)4095;
+                    const size_t map_len = (size_t)(file_pos - map_off) + total;
+                    if (total && ftruncate(fd, at[n_threads]) == 0) {
+                        void* m = mmap(nullptr, map_len, PROT_WRITE, MAP_SHARED, fd, map_off);
+                        if (m != MAP_FAILED) map = static_cast<char*>(m);
+                    }
                     for (unsigned t = 0; t < n_threads; t++)
                         workers.emplace_back([&, t] {
+                            if (map) {
+                                memcpy(map + (at[t] - map_off), parts[t].p.get(), parts[t].len);
+                                return;
+                            }
                             size_t done = 0;
                             while (done < parts[t].len) {
                                 const ssize_t w = pwrite(fd, parts[t].p.get() + done, parts[t].len - done, at[t] + (off_t)done);
@@ -356,6 +371,7 @@ void run_query_file(const std::vector<fin_index*>& indexes, const fin_index_info
                             }
                         });
                     for (auto& w : workers) w.join();
+                    if (map) munmap(map, map_len);
                     for (char f : failed)
                         if (f) write_error = "Error writing the output file";
                     file_pos = at[n_threads];
@@ -502,7 +518,7 @@ int search_fmin_command(int argc, char** argv) {
 
     int64_t total_queries = 0;
     for (size_t i = 0; i < query_files.size(); i++) {
-        FILE* out = to_stdout ? stdout : std::fopen(out_files[i].c_str(), "wb");
+        FILE* out = to_stdout ? stdout : std::fopen(out_files[i].c_str(), "w+b");  // read-write: the writer maps the file
         if (!out) throw std::runtime_error("Error writing to file: " + out_files[i]);
         QueryTotals tot;
         const int64_t t0 = now_micros();

@@ -65,6 +65,32 @@ def test_build_with_given_lcs_and_error_paths(gpu_lib, tmp_path):
     assert e.value.status == fb.FIN_ERR_FORMAT
 
 
+def test_foreign_lcs_file_is_refused(gpu_lib, tmp_path):
+    """An LCS that cannot belong to the SBWT (a value >= k, or LCS[0] != 0) would send the word-parallel drop_first_char
+    out of bounds (the reference guards it with `first > 0`, common.hh:43): FIN_ERR_FORMAT at build and at load instead."""
+    import shutil
+
+    fb = gpu_lib
+    d = os.path.join(H.GOLDEN, "syn_k12")  # k = 12: 4-bit LCS entries, value 15 is representable and >= k
+    raw = bytearray(open(os.path.join(d, "ref.LCS.sdsl"), "rb").read())
+    assert raw[8] == 4
+    for name, patch in (("big", (9 + 20, 0xFF)), ("first", (9, raw[9] | 0x01))):
+        bad = bytearray(raw)
+        bad[patch[0]] = patch[1]
+        p = str(tmp_path / f"{name}.LCS.sdsl")
+        open(p, "wb").write(bad)
+        with pytest.raises(fb.FinitoError) as e:
+            fb.build_fmin(os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), str(tmp_path / "x"), lcs_path=p)
+        assert e.value.status == fb.FIN_ERR_FORMAT
+        ix_prefix = str(tmp_path / name)
+        for suf in H.INDEX_SUFFIXES:
+            shutil.copy(os.path.join(d, "ref" + suf), ix_prefix + suf)
+        open(ix_prefix + ".LCS.sdsl", "wb").write(bad)
+        with pytest.raises(fb.FinitoError) as e:
+            fb.FinimizerIndex.load(ix_prefix)
+        assert e.value.status == fb.FIN_ERR_FORMAT
+
+
 @pytest.mark.parametrize("case", golden_cases())
 def test_golden_stats_modes(case, gpu_lib, tmp_path):
     """BASELINE.json configs[2]: --type shortest|verify -t T print statistics only (build_fmin.hh:95-214)."""
