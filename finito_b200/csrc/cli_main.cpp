@@ -16,10 +16,6 @@
 #include <thread>
 #include <vector>
 
-#include <fcntl.h>
-#include <sys/mman.h>
-#include <sys/stat.h>
-#include <unistd.h>
 
 #include "../../include/finito_b200.h"
 #include "seqio.hpp"
@@ -214,7 +210,7 @@ struct QueryTotals {
 // the GPU(s) - the answers come back as run-length records, ~50 bytes per read instead of 8 bytes per k-mer -, a writer
 // thread formats the text on all host cores and writes it in read order (regular files: one pwrite per core).
 struct BatchSlot {
-    enum State { Empty, Parsed, Searched } state = Empty;
+    enum State { Empty, Parsed, Searched, Formatted } state = Empty;
     fin::SeqBatch reads;
     bool last = false;  // set by the parser: no batch follows (this one may be empty)
     struct Block {      // one contiguous block of the batch's reads per GPU
@@ -225,6 +221,7 @@ struct BatchSlot {
         fin_search_counts counts{};
     };
     std::vector<Block> blocks;
+    std::vector<TextBuf> parts;  // the text of the batch: blocks x formatting threads, in read order
 };
 
 void search_block(fin_index* index, const fin::SeqBatch& reads, BatchSlot::Block& b) {
@@ -309,17 +306,10 @@ void run_query_file(const std::vector<fin_index*>& indexes, const fin_index_info
         }
     });
 
-    std::thread writer([&] {
-        std::vector<TextBuf> parts(n_threads);
-        const int fd = fileno(out);
-        struct stat sb;
-        // positional writes need a plain file that is not in append mode (O_APPEND ignores the offset of pwrite)
-        const bool regular = fd >= 0 && fstat(fd, &sb) == 0 && S_ISREG(sb.st_mode) && !(fcntl(fd, F_GETFL) & O_APPEND);
-        off_t file_pos = 0;
-        if (regular) {
-            std::fflush(out);
-            file_pos = lseek(fd, 0, SEEK_CUR);
-        }
+    // formatting on all cores, then one sequential write per part (buffered writes to ONE file serialise on the inode
+    // lock, and filling a shared mapping from many threads stalls the search thread's pinning of pageable memory on the
+    // process's mmap lock: measured, profiles/r2_cli_timing.log); the two stages run on consecutive batches
+    std::thread formatter([&] {
         for (size_t b = 0;; b++) {
             BatchSlot& s = ring[b % kRing];
             {
@@ -327,72 +317,53 @@ void run_query_file(const std::vector<fin_index*>& indexes, const fin_index_info
                 cv.wait(lk, [&] { return s.state == BatchSlot::Searched || abort; });
                 if (abort) return;
             }
-            const bool last = s.last;
-            for (BatchSlot::Block& blk : s.blocks) {
-                if (!write_error.empty()) break;
+            const int64_t t0 = now_micros();
+            s.parts.resize(s.blocks.size() * n_threads);
+            std::vector<std::thread> workers;
+            for (size_t d = 0; d < s.blocks.size(); d++) {
+                BatchSlot::Block& blk = s.blocks[d];
                 const uint64_t nr = blk.r1 - blk.r0, per = (nr + n_threads - 1) / n_threads;
-                const int64_t t0 = now_micros();
-                std::vector<std::thread> workers;
                 for (unsigned t = 0; t < n_threads; t++) {
                     const uint64_t a = std::min<uint64_t>(nr, t * per), e = std::min<uint64_t>(nr, (t + 1) * per);
-                    workers.emplace_back([&, t, a, e] { format_reads(blk.runs, blk.run_offsets.data(), blk.offs.data(), a, e, k, bytes_per_hit, parts[t]); });
+                    TextBuf& part = s.parts[d * n_threads + t];
+                    workers.emplace_back([&blk, &part, a, e, k, bytes_per_hit] {
+                        format_reads(blk.runs, blk.run_offsets.data(), blk.offs.data(), a, e, k, bytes_per_hit, part);
+                    });
                 }
-                for (auto& w : workers) w.join();
-                const int64_t t1 = now_micros();
-                if (regular) {  // the parts land at known offsets: every core copies its own
-                    std::vector<off_t> at(n_threads + 1, file_pos);
-                    for (unsigned t = 0; t < n_threads; t++) at[t + 1] = at[t] + (off_t)parts[t].len;
-                    const size_t total = (size_t)(at[n_threads] - file_pos);
-                    std::vector<char> failed(n_threads, 0);
-                    workers.clear();
-                    // through a shared mapping when the descriptor allows it (read-write open): the page cache is filled by all
-                    // cores at once; buffered write()s to ONE file serialise on the inode lock
-                    char* map = nullptr;
-                    const off_t map_off = file_pos & ~(off_t)4095;
-                    const size_t map_len = (size_t)(file_pos - map_off) + total;
-                    if (total && ftruncate(fd, at[n_threads]) == 0) {
-                        void* m = mmap(nullptr, map_len, PROT_WRITE, MAP_SHARED, fd, map_off);
-                        if (m != MAP_FAILED) map = static_cast<char*>(m);
-                    }
-                    for (unsigned t = 0; t < n_threads; t++)
-                        workers.emplace_back([&, t] {
-                            if (map) {
-                                memcpy(map + (at[t] - map_off), parts[t].p.get(), parts[t].len);
-                                return;
-                            }
-                            size_t done = 0;
-                            while (done < parts[t].len) {
-                                const ssize_t w = pwrite(fd, parts[t].p.get() + done, parts[t].len - done, at[t] + (off_t)done);
-                                if (w <= 0) {
-                                    failed[t] = 1;
-                                    return;
-                                }
-                                done += (size_t)w;
-                            }
-                        });
-                    for (auto& w : workers) w.join();
-                    if (map) munmap(map, map_len);
-                    for (char f : failed)
-                        if (f) write_error = "Error writing the output file";
-                    file_pos = at[n_threads];
-                } else {
-                    for (unsigned t = 0; t < n_threads; t++)
-                        if (parts[t].len && std::fwrite(parts[t].p.get(), 1, parts[t].len, out) != parts[t].len)
-                            write_error = "Error writing the output file";
-                }
-                us_format += t1 - t0;
-                us_write += now_micros() - t1;
             }
+            for (auto& w : workers) w.join();
+            us_format += now_micros() - t0;
+            const bool last = s.last;
+            {
+                std::lock_guard<std::mutex> lk(mu);
+                s.state = BatchSlot::Formatted;
+            }
+            cv.notify_all();
+            if (last) return;
+        }
+    });
+
+    std::thread writer([&] {
+        for (size_t b = 0;; b++) {
+            BatchSlot& s = ring[b % kRing];
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return s.state == BatchSlot::Formatted || abort; });
+                if (abort) return;
+            }
+            const int64_t t0 = now_micros();
+            for (const TextBuf& part : s.parts)
+                if (write_error.empty() && part.len && std::fwrite(part.p.get(), 1, part.len, out) != part.len)
+                    write_error = "Error writing the output file";
+            us_write += now_micros() - t0;
+            const bool last = s.last;
             {
                 std::lock_guard<std::mutex> lk(mu);
                 s.state = BatchSlot::Empty;
                 if (!write_error.empty()) abort = true;
             }
             cv.notify_all();
-            if (last || !write_error.empty()) {
-                if (regular) lseek(fd, file_pos, SEEK_SET);  // later fwrite()s of this stream (none today) continue behind the text
-                return;
-            }
+            if (last || !write_error.empty()) return;
         }
     });
 
@@ -451,11 +422,12 @@ void run_query_file(const std::vector<fin_index*>& indexes, const fin_index_info
         {   // the slot the next batch will use must have been written out: that wait is the writer's backlog
             BatchSlot& nx = ring[(b + 1) % kRing];
             std::unique_lock<std::mutex> lk(mu);
-            cv.wait(lk, [&] { return nx.state != BatchSlot::Searched || abort; });
+            cv.wait(lk, [&] { return (nx.state != BatchSlot::Searched && nx.state != BatchSlot::Formatted) || abort; });
         }
         us_wait_writer += now_micros() - tq;
     }
     parser.join();
+    formatter.join();
     writer.join();
     for (BatchSlot& s : ring)
         for (BatchSlot::Block& blk : s.blocks) fin_host_free(blk.runs);
@@ -518,7 +490,7 @@ int search_fmin_command(int argc, char** argv) {
 
     int64_t total_queries = 0;
     for (size_t i = 0; i < query_files.size(); i++) {
-        FILE* out = to_stdout ? stdout : std::fopen(out_files[i].c_str(), "w+b");  // read-write: the writer maps the file
+        FILE* out = to_stdout ? stdout : std::fopen(out_files[i].c_str(), "wb");
         if (!out) throw std::runtime_error("Error writing to file: " + out_files[i]);
         QueryTotals tot;
         const int64_t t0 = now_micros();
