@@ -55,14 +55,50 @@ def parse_args():
 def dataset(args, rank=0):
     from fin_datasets import make_dataset
 
+    if args.genome >= 50_000_000:
+        return device_built_dataset(args, rank)
     # planted repeats as in SURVEY.md §8(d) config 2: 50 families x 5 copies x 2 kb at 1 % divergence per 5 Mbp
     return make_dataset("bench", genome_len=args.genome, k=args.k, n_reads=args.reads, read_len=args.read_len,
                         seed=20260102 + rank, families=max(1, args.genome // 100_000))
 
 
+def device_built_dataset(args, rank):
+    """Large inputs (configs[3] / [4]): the genome comes from tools/fin_datagen bigenome, the disjoint SPSS ("flipped unitigs") and
+    its plain-matrix SBWT from the device pipeline fin_spss_build -> fin_sbwt_build (seconds instead of the minutes the CPU
+    generator needs); the reads are simulated by tools/fin_datagen from the same genome.  Rank 0's genome is shared by all
+    ranks (one index), every rank draws its own reads."""
+    import finito_b200 as fb
+
+    work = os.environ.get("FIN_WORK") or ("/dev/shm/finwork" if os.path.isdir("/dev/shm") else os.path.join(ROOT, "_work"))
+    d = os.path.join(work, f"benchbig_g{args.genome}_k{args.k}")
+    os.makedirs(d, exist_ok=True)
+    genome, spss, sbwt = (os.path.join(d, f) for f in ("genome.fna", "unitigs.fna", "index.sbwt"))
+    reads_bin = os.path.join(d, f"reads_r{rank}_{args.reads}x{args.read_len}.bin")
+    datagen = os.path.join(ROOT, "tools", "fin_datagen")
+    done = os.path.join(d, ".done")
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if rank == 0 and not os.path.exists(done):
+        subprocess.run([datagen, "bigenome", genome, str(args.genome), "20260104", "1", "0.30", str(max(2000, args.genome // 50_000))],
+                       check=True, capture_output=True)
+        fb.spss_build(genome, args.k, spss, flip=True, seed=7, device=local_rank)
+        fb.sbwt_build(spss, args.k, sbwt, 8, device=local_rank)
+        open(done, "w").close()
+    while not os.path.exists(done):  # the other ranks of the node wait for rank 0's files
+        time.sleep(0.2)
+    if not os.path.exists(reads_bin):  # several ranks may want rank 0's reads at once: write aside, rename
+        tmp = f"{reads_bin}.{os.getpid()}.bin"
+        subprocess.run([datagen, "reads", genome, str(args.reads), str(args.read_len), "0.01", str(9 + rank), tmp], check=True, capture_output=True)
+        os.replace(tmp, reads_bin)
+    seqs = np.fromfile(reads_bin, dtype=np.uint8)
+    offs = np.arange(args.reads + 1, dtype=np.uint64) * np.uint64(args.read_len)
+    return {"dir": d, "genome": genome, "unitigs": spss, "sbwt": sbwt, "reads_bin": reads_bin, "reads": (seqs, offs), "k": args.k,
+            "n_reads": args.reads, "read_len": args.read_len}
+
+
 def workload_name(args):
+    which = "configs[1]" if (args.genome, args.k) == (5_000_000, 31) else "configs[3]" if args.k == 63 else "configs[4]" if args.genome >= 1_000_000_000 else "other size"
     return (f"synthetic {args.genome / 1e6:g} Mbp genome with planted repeats, flipped unitigs, k={args.k}, t=1 rarest, "
-            f"{args.reads} simulated {args.read_len} bp reads at 1% error per GPU (BASELINE.json configs[1])")
+            f"{args.reads} simulated {args.read_len} bp reads at 1% error per GPU (BASELINE.json {which})")
 
 
 class ClockSampler(threading.Thread):
@@ -552,12 +588,16 @@ def main():
 
     ds = dataset(args, rank)
     prefix = os.path.join(ds["dir"], "fmin")  # not "index": <prefix>.sbwt would overwrite the input index.sbwt
-    if not os.path.exists(prefix + ".FBV.sdsl"):
+    shared_index = args.genome >= 50_000_000  # device-built datasets: one index for all ranks, built by rank 0
+    built = prefix + ".built"
+    build_s = None
+    if not os.path.exists(built) and (rank == 0 or not shared_index):
         t0 = time.perf_counter()
         fb.build_fmin(ds["sbwt"], ds["unitigs"], prefix, device=local_rank)
         build_s = time.perf_counter() - t0
-    else:
-        build_s = None
+        open(built, "w").close()
+    while not os.path.exists(built):
+        time.sleep(0.2)
     ix = fb.FinimizerIndex.load(prefix, device=local_rank)
     info = ix.info
     seqs, offs = ds["reads"]

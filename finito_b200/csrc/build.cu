@@ -74,6 +74,7 @@ static DeviceSbwt upload_sbwt(const SbwtHost& s) {
 
 // ---- B1: LCS bytes on the device (k launches of lcs_round_kernel), padded with zeros to 64 * nw + 64 bytes ----------
 static DevBuf<uint8_t> lcs_on_device(const DeviceSbwt& d) {
+    NvtxRange range("fin:build:lcs_rounds");
     const uint64_t padded = d.nw * 64 + 64;
     DevBuf<uint8_t> last(padded), next(padded), lcs(padded);
     const unsigned T = 256;
@@ -301,6 +302,7 @@ class RarestBuilder {
 
     // add_sequence over this rank's chunks; overwrite rule as a max over table[colex] (B3)
     uint64_t stream() {
+        NvtxRange range("fin:build:stream");
         const size_t nc = chunk_end_ - chunk_begin_;
         d_table_.alloc(N_);
         FIN_CUDA(cudaMemset(d_table_.p, 0, d_table_.bytes()));
@@ -426,6 +428,7 @@ class RarestBuilder {
 
     // all slices in rank order (HOST): world * slice_words() u64 of fmin bits, the offsets back to back
     void finish(const uint64_t* bits_all, uint64_t n_bit_words, const uint32_t* offsets_all, uint64_t n_offsets, const std::string& out_prefix) {
+        NvtxRange range("fin:build:write_files");
         save_index_from_slices(std::move(sbwt_), std::move(lcs_file_), std::move(text_), std::move(ends_), std::move(ustart_), bits_all,
                                n_bit_words, offsets_all, n_offsets, out_prefix);
     }

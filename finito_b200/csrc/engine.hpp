@@ -5,6 +5,7 @@
 #include <string>
 #include <vector>
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include "device_index.cuh"
 #include "formats.hpp"
@@ -24,6 +25,14 @@ struct cuda_error : std::runtime_error { using std::runtime_error::runtime_error
     } while (0)
 
 extern thread_local uint64_t g_launches;  // kernels launched by this library on this thread
+
+// NVTX range per pipeline stage (header-only nvtx3: a no-op unless a profiler is attached)
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 // RAII device allocation
 template <class T> struct DevBuf {

@@ -357,6 +357,7 @@ static SbwtRows build_rows_device(const SeqBatch& seqs, int k) {
     g_sbwt_timing.keys_ms = ms_since(t0);
 
     // ---- 2. the k-mer nodes: sort, unique
+    NvtxRange range_sort("fin:sbwt_build:sort_and_join");
     t0 = clock::now();
     sort_keys<Key>(tmp, a.p, b.p, n_pos, 2 * k);
     uint64_t n = 0;

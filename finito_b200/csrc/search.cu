@@ -52,6 +52,7 @@ template <class T> static DevBuf<T> upload(const T* src, size_t n) {
 }
 
 DeviceIndex::DeviceIndex(const IndexHost& h, int device) : device_(device) {
+    NvtxRange range("fin:index_load:device_layout");
     int n_dev = 0;
     if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev <= 0) throw cuda_error("no CUDA device is visible");
     if (device < 0 || device >= n_dev) throw arg_error("CUDA device ordinal out of range");
@@ -465,6 +466,7 @@ static uint64_t cut_sub_batch(const uint64_t* read_offsets, uint64_t n_reads, ui
 // H2D of a sub-batch and its preparation kernels on the slot's stream
 static void stage_sub_batch(const IndexView& v, SearchSlot& s, const char* seqs, const uint64_t* read_offsets, uint64_t r0, uint64_t r1,
                             uint64_t nkm) {
+    NvtxRange range("fin:search:stage_sub_batch");
     const uint64_t base0 = read_offsets[r0];
     const uint64_t nr = r1 - r0, nb = read_offsets[r1] - base0;
     s.r0 = r0; s.nr = nr; s.nb = nb; s.nkm = nkm; s.base0 = base0;
@@ -580,6 +582,7 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
         s.recs_b.ensure(n);
     };
     auto phase_b = [&](SearchSlot& s) {
+        NvtxRange range("fin:search:runs_sort_and_copy_out");
         FIN_CUDA(cudaEventSynchronize(s.counted));
         uint64_t n = s.h_totals->n_runs;
         if (n > std::min<uint64_t>(s.keys_a.n, s.recs_a.n)) {  // more runs than the slot had room for: search again with enough

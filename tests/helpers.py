@@ -118,12 +118,15 @@ def oracle_lcs(sbwt, n_nodes, with_variant=True) -> np.ndarray:
 
 
 def emu_lib() -> C.CDLL:
-    so = os.path.join(EMU_DIR, "libfin_emu.so")
+    # FIN_EMU_ASAN=1 (tests/test_emu_sanitized.py): the kernel bodies under AddressSanitizer + UBSan on the host
+    asan = os.environ.get("FIN_EMU_ASAN") == "1"
+    so = os.path.join(EMU_DIR, "libfin_emu_asan.so" if asan else "libfin_emu.so")
     csrc = os.path.join(ROOT, "finito_b200", "csrc")
     srcs = [os.path.join(EMU_DIR, "emu.cpp")] + [os.path.join(csrc, f) for f in os.listdir(csrc)
                                                  if f.endswith((".cuh", ".hpp"))]
     if not _newer(so, *srcs):
-        subprocess.run(["/usr/bin/g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", so,
+        flags = ["-O1", "-g", "-fsanitize=address,undefined", "-fno-sanitize-recover=undefined", "-fno-omit-frame-pointer"] if asan else ["-O2"]
+        subprocess.run(["/usr/bin/g++", "-std=c++17", *flags, "-fPIC", "-shared", "-Wno-unknown-pragmas", "-o", so,
                         os.path.join(EMU_DIR, "emu.cpp"), "-lz", "-pthread"], check=True, capture_output=True)
     lib = C.CDLL(so)
     lib.emu_last_error.restype = C.c_char_p

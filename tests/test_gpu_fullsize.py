@@ -20,17 +20,39 @@ def colex_ranked(unitigs, k):
     return [unitigs[i] for i in order]
 
 
-PARAMS, IDS = [(31, 5_000_000, 1_000_000), (63, 2_000_000, 300_000)], ["config2_k31", "k63"]
+# configs[1] (5 Mbp, k=31), a small k=63 case, and configs[3]'s shape: 100 Mbp, k=63 (MAX_KMER_LENGTH-sized keys: 128-bit k-mers in
+# fin_sbwt_build, the 64-slot candidate window in the search) - that one is built by the device pipeline
+PARAMS, IDS = [(31, 5_000_000, 1_000_000), (63, 2_000_000, 300_000), (63, 100_000_000, 300_000)], ["config2_k31", "k63", "config4_k63_100Mbp"]
 if os.environ.get("FIN_FULLSIZE_GENOME"):  # one-off runs at other sizes, e.g. 200000000 for an index far beyond the L2
     PARAMS.append((int(os.environ.get("FIN_FULLSIZE_K", "31")), int(os.environ["FIN_FULLSIZE_GENOME"]), 1_000_000))
     IDS.append("env_size")
 
 
+def device_built_dataset(fb, d, genome_len, k, n_reads):
+    """genome (tools/fin_datagen bigenome, 30 % repeats) -> fin_spss_build -> fin_sbwt_build; reads from the same genome"""
+    import subprocess
+
+    d = str(d)
+    genome, spss, sbwt, reads_bin = (os.path.join(d, f) for f in ("genome.fna", "unitigs.fna", "index.sbwt", "reads.bin"))
+    datagen = os.path.join(H.TOOLS, "fin_datagen")
+    subprocess.run([datagen, "bigenome", genome, str(genome_len), "20260104", "1", "0.30", str(max(2000, genome_len // 50_000))], check=True,
+                   capture_output=True)
+    fb.spss_build(genome, k, spss, flip=True, seed=7)
+    fb.sbwt_build(spss, k, sbwt, 8)
+    subprocess.run([datagen, "reads", genome, str(n_reads), "150", "0.01", "9", reads_bin], check=True, capture_output=True)
+    seqs = np.fromfile(reads_bin, dtype=np.uint8)
+    offs = np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(150)
+    return {"dir": d, "genome": genome, "unitigs": spss, "sbwt": sbwt, "reads": (seqs, offs), "k": k, "n_reads": n_reads, "read_len": 150}
+
+
 @pytest.fixture(scope="module", params=PARAMS, ids=IDS)
 def big(request, gpu_lib, tmp_path_factory):
     k, genome_len, n_reads = request.param
-    ds = make_dataset("full", genome_len=genome_len, k=k, n_reads=n_reads, read_len=150, seed=20260102 + k,
-                      families=max(1, genome_len // 100_000))
+    if genome_len >= 50_000_000:
+        ds = device_built_dataset(gpu_lib, tmp_path_factory.mktemp("big"), genome_len, k, n_reads)
+    else:
+        ds = make_dataset("full", genome_len=genome_len, k=k, n_reads=n_reads, read_len=150, seed=20260102 + k,
+                          families=max(1, genome_len // 100_000))
     prefix = str(tmp_path_factory.mktemp("full") / "gpu")
     gpu_lib.build_fmin(ds["sbwt"], ds["unitigs"], prefix)
     return ds, prefix
