@@ -107,6 +107,14 @@ ABI = {
                             C.c_size_t]),
     "fin_build_last_timing": (C.c_int, [C.POINTER(_BuildTiming)]),
     "fin_lcs": (C.c_int, [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, _u64p]),
+    "fin_stats_open": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_int, C.c_int, C.c_int,
+                                 C.POINTER(C.c_void_p)]),
+    "fin_stats_free": (None, [C.c_void_p]),
+    "fin_stats_first_pass": (C.c_int, [C.c_void_p, _u64p]),
+    "fin_stats_table": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int]),
+    "fin_stats_second_pass": (C.c_int, [C.c_void_p, _u64p]),
+    "fin_stats_keys": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "fin_stats_finish": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_char_p, C.c_size_t]),
     "fin_builder_open": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int, C.c_int,
                                    C.POINTER(C.c_void_p)]),
     "fin_builder_free": (None, [C.c_void_p]),
@@ -390,6 +398,55 @@ def expand_runs(read_offsets: np.ndarray, k: int, run_offsets: np.ndarray, runs:
     _check(lib().fin_expand_runs(offs.ctypes.data, n, k, ro.ctypes.data, runs.ctypes.data, out.ctypes.data, out.size // 2,
                                  hit_bits // 8, threads))
     return out
+
+
+class ShardedStats:
+    """One rank of build-fmin --type shortest|verify sharded over GPUs (fin_stats_* in include/finito_b200.h;
+    include/build_fmin.hh:95-214).  Buffers are raw DEVICE pointers; finito_b200/distributed.py drives it."""
+
+    memory = "cuda"
+
+    def __init__(self, sbwt_path: str, unitig_path: str, type: str, t: int, rank: int, world: int, device: int = 0,
+                 out_prefix: str | None = None, lcs_path: str | None = None):
+        out = C.c_void_p()
+        _check(lib().fin_stats_open(os.fsencode(sbwt_path), os.fsencode(unitig_path), os.fsencode(lcs_path) if lcs_path else None,
+                                    os.fsencode(out_prefix) if out_prefix else None, type.encode(), t, device, rank, world, C.byref(out)))
+        self._h = C.c_void_p(out.value)
+
+    def close(self) -> None:
+        if self._h:
+            lib().fin_stats_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def first_pass(self) -> int:
+        n = C.c_uint64()
+        _check(lib().fin_stats_first_pass(self._h, C.byref(n)))
+        return int(n.value)
+
+    def table_out(self, ptr: int) -> None:
+        _check(lib().fin_stats_table(self._h, ptr, 0))
+
+    def table_in(self, ptr: int) -> None:
+        _check(lib().fin_stats_table(self._h, ptr, 1))
+
+    def second_pass(self) -> int:
+        n = C.c_uint64()
+        _check(lib().fin_stats_second_pass(self._h, C.byref(n)))
+        return int(n.value)
+
+    def keys(self, ptr: int) -> None:
+        _check(lib().fin_stats_keys(self._h, ptr))
+
+    def finish(self, keys_ptr: int, n_keys: int, write_line: bool = False) -> str:
+        buf = C.create_string_buffer(512)
+        _check(lib().fin_stats_finish(self._h, keys_ptr, n_keys, int(write_line), buf, len(buf)))
+        return buf.value.decode()
 
 
 def probe_random_sectors(device: int = 0, table_bytes: int = 8 << 30, repeats: int = 3, bytes_per_access: int = 32) -> float:

@@ -485,105 +485,173 @@ static void build_rarest(SbwtHost&& sbwt, PackedVec&& lcs_file, const DeviceSbwt
 
 // ---- B5 / B6: --type shortest | verify, statistics only (build_fmin.hh:95-214,252-267) ---------------------------
 // Unitigs stay in FILE order here (no permutation): the shared fmin_found bit vector of B5 makes the result depend on it.
+// build-fmin --type shortest|verify in stages, shardable over GPUs.  Rank r of `world`:
+//   shortest: streams a contiguous share of the chunks.  Pass 0 folds "first window per column whose finimizer ends at
+//             or after position k-1 of its unitig" into table[colex] with atomicMin - a min over ALL ranks' tables gives
+//             the table of the single pass (the closed form of build_fmin.hh:182-187 does not care who streamed what) -,
+//             pass 1 emits this rank's keys against the reduced table.
+//   verify  : a contiguous range of text positions; the per-position records are recomputed for the k positions past
+//             the range (a window reads the records of its k starts), the keys of the range's windows are this rank's.
+// The union of all ranks' keys, sorted and made unique, is the reference's std::set (common.hh:188-206).
+class StatsBuilder {
+   public:
+    StatsBuilder(const SbwtHost& sbwt, const DeviceSbwt& ds, const uint8_t* d_lcs_bytes, const SeqBatch& unitigs, const std::string& type,
+                 int64_t t, int rank, int world)
+        : shortest_(type == "shortest"), t_((uint32_t)t), k_((int)sbwt.k), N_((uint64_t)sbwt.n_nodes), n_kmers_(sbwt.n_kmers) {
+        if (type != "shortest" && type != "verify") throw arg_error("stats: type must be shortest or verify");
+        if (world < 1 || rank < 0 || rank >= world) throw arg_error("stats: rank / world out of range");
+        const uint64_t U = unitigs.size();
+        check_unitigs(unitigs, k_);
+        check_stats_t(t, sbwt.n_nodes);
+        d_lines_ = make_lines_device(ds, d_lcs_bytes);
+        ix_.lines = reinterpret_cast<const uint4*>(d_lines_.p);
+        ix_.n_nodes = (idx_t)N_;
+        ix_.k = k_;
+        std::vector<uint64_t> order(U), starts;  // FILE order (build_fmin.hh:202-214), not the colex permutation
+        std::iota(order.begin(), order.end(), 0);
+        PackedVec text;
+        pack_unitigs(unitigs, order, text, starts);
+        const PackedVec ends = unitig_ends(unitigs, order, starts);
+        T_ = text.size();
+        d_text_ = to_device(text.words, 2);
+        d_err_.alloc(1);
+        FIN_CUDA(cudaMemset(d_err_.p, 0, 4));
+        if (shortest_) {
+            const std::vector<BuildChunk> chunks = plan_build_chunks(starts, ends, k_, 0);
+            const std::pair<size_t, size_t> mine = shard_chunks(chunks, rank, world);
+            nc_ = (uint32_t)(mine.second - mine.first);
+            d_chunks_.alloc((size_t)nc_ + 1);
+            if (nc_) FIN_CUDA(cudaMemcpy(d_chunks_.p, chunks.data() + mine.first, (size_t)nc_ * sizeof(BuildChunk), cudaMemcpyHostToDevice));
+            d_first_.alloc(N_);
+            d_runs_.alloc((size_t)nc_ + 1);
+            FIN_CUDA(cudaMemset(d_first_.p, 0xFF, d_first_.bytes()));
+            FIN_CUDA(cudaMemset(d_runs_.p, 0, d_runs_.bytes()));
+        } else {
+            std::vector<uint32_t> ends32(U);
+            for (uint64_t u = 0; u < U; u++) ends32[u] = (uint32_t)ends.words[u];
+            d_ends_ = to_device(ends32);
+            n_unitigs_ = (uint32_t)U;
+            p0_ = T_ * (uint64_t)rank / (uint64_t)world;
+            p1_ = T_ * (uint64_t)(rank + 1) / (uint64_t)world;
+        }
+    }
+
+    uint64_t table_entries() const { return shortest_ ? N_ : 0; }
+    uint32_t* table() { return d_first_.p; }
+
+    void first_pass() {
+        if (shortest_) launch_shortest(std::integral_constant<int, 0>());
+        passed0_ = true;
+    }
+
+    uint64_t second_pass() {
+        if (!passed0_) throw arg_error("stats: second pass before the first");
+        if (shortest_) {
+            {  // run counts -> offsets; the element past the last chunk becomes the total
+                size_t tb = 0;
+                cub::DeviceScan::ExclusiveSum(nullptr, tb, d_runs_.p, d_runs_.p, (int64_t)nc_ + 1);
+                DevBuf<uint8_t> tmp(tb + 256);
+                FIN_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tb, d_runs_.p, d_runs_.p, (int64_t)nc_ + 1));
+                g_launches += 2;
+            }
+            uint32_t total = 0;
+            FIN_CUDA(cudaMemcpy(&total, d_runs_.p + nc_, 4, cudaMemcpyDeviceToHost));
+            n_keys_ = total;
+            d_keys_.alloc(n_keys_ + 1);
+            launch_shortest(std::integral_constant<int, 1>());
+        } else {
+            const uint64_t r1 = std::min<uint64_t>(T_, p1_ + (uint64_t)k_);  // records of [p0, r1), keys of the windows that start in [p0, p1)
+            n_keys_ = p1_ - p0_;
+            DevBuf<uint64_t> d_rec(r1 - p0_ + 1);
+            d_keys_.alloc(n_keys_ + 1);
+            if (r1 > p0_) {
+                rare_prefix_kernel<<<(unsigned)((r1 - p0_ + 255) / 256), 256>>>(ix_, d_text_.p, d_ends_.p, n_unitigs_, (uint32_t)p0_, (uint32_t)r1, t_,
+                                                                              d_rec.p, d_err_.p);
+                g_launches++;
+            }
+            if (n_keys_) {
+                verify_window_kernel<<<(unsigned)((n_keys_ + 255) / 256), 256>>>(d_rec.p, d_ends_.p, n_unitigs_, (uint32_t)p0_, (uint32_t)p1_, k_,
+                                                                               d_keys_.p, d_err_.p);
+                g_launches++;
+            }
+            FIN_CUDA(cudaGetLastError());
+            FIN_CUDA(cudaDeviceSynchronize());
+        }
+        unsigned err = 0;
+        FIN_CUDA(cudaMemcpy(&err, d_err_.p, 4, cudaMemcpyDeviceToHost));
+        if (err)
+            throw domain_error("the unitigs are not a disjoint spectrum-preserving string set of this SBWT "
+                               "(a unitig k-mer is missing from the SBWT or a window has no substring with at most t occurrences)");
+        return n_keys_;
+    }
+
+    uint64_t n_keys() const { return n_keys_; }
+    const uint64_t* keys() const { return d_keys_.p; }
+
+    // the std::set of the reference over the keys of ALL ranks (device): sort, unique, sum -> the stats string
+    std::string finish(const uint64_t* d_keys_all, uint64_t n_keys) const {
+        unsigned long long sums[3] = {0, 0, 0};
+        if (n_keys) {
+            DevBuf<uint64_t> d_sorted(n_keys), d_unique(n_keys);
+            DevBuf<uint64_t> d_nuniq(1);
+            size_t tb1 = 0, tb2 = 0;
+            cub::DeviceRadixSort::SortKeys(nullptr, tb1, d_keys_all, d_sorted.p, (int64_t)n_keys);
+            cub::DeviceSelect::Unique(nullptr, tb2, d_sorted.p, d_unique.p, d_nuniq.p, (int64_t)n_keys);
+            DevBuf<uint8_t> tmp(std::max(tb1, tb2) + 256);
+            FIN_CUDA(cub::DeviceRadixSort::SortKeys(tmp.p, tb1, d_keys_all, d_sorted.p, (int64_t)n_keys));
+            FIN_CUDA(cub::DeviceSelect::Unique(tmp.p, tb2, d_sorted.p, d_unique.p, d_nuniq.p, (int64_t)n_keys));
+            g_launches += 10;
+            uint64_t n_unique = 0;
+            FIN_CUDA(cudaMemcpy(&n_unique, d_nuniq.p, 8, cudaMemcpyDeviceToHost));
+            DevBuf<unsigned long long> d_sums(3);
+            FIN_CUDA(cudaMemset(d_sums.p, 0, 24));
+            if (n_unique) {
+                stat_sum_kernel<<<(unsigned)((n_unique + 255) / 256), 256>>>(d_unique.p, n_unique, d_sums.p);
+                g_launches++;
+                FIN_CUDA(cudaGetLastError());
+            }
+            FIN_CUDA(cudaMemcpy(sums, d_sums.p, 24, cudaMemcpyDeviceToHost));
+        }
+        return stats_string(sums[0], sums[1], sums[2], n_kmers_);
+    }
+
+    int t() const { return (int)t_; }
+
+   private:
+    template <class Pass> void launch_shortest(Pass) {
+        constexpr int P = Pass::value;
+        if (nc_ == 0) return;
+        const unsigned blocks = (nc_ + 127) / 128;
+        switch (window_capacity(k_)) {
+            case 32: shortest_stream_kernel<32, P><<<blocks, 128>>>(ix_, d_text_.p, d_chunks_.p, nc_, t_, d_first_.p, d_runs_.p, d_keys_.p, d_err_.p); break;
+            case 64: shortest_stream_kernel<64, P><<<blocks, 128>>>(ix_, d_text_.p, d_chunks_.p, nc_, t_, d_first_.p, d_runs_.p, d_keys_.p, d_err_.p); break;
+            case 128: shortest_stream_kernel<128, P><<<blocks, 128>>>(ix_, d_text_.p, d_chunks_.p, nc_, t_, d_first_.p, d_runs_.p, d_keys_.p, d_err_.p); break;
+            default: shortest_stream_kernel<256, P><<<blocks, 128>>>(ix_, d_text_.p, d_chunks_.p, nc_, t_, d_first_.p, d_runs_.p, d_keys_.p, d_err_.p); break;
+        }
+        g_launches++;
+        FIN_CUDA(cudaGetLastError());
+        FIN_CUDA(cudaDeviceSynchronize());
+    }
+
+    bool shortest_, passed0_ = false;
+    uint32_t t_;
+    int k_;
+    uint64_t N_, T_ = 0, n_keys_ = 0, p0_ = 0, p1_ = 0;
+    int64_t n_kmers_;
+    uint32_t nc_ = 0, n_unitigs_ = 0;
+    IndexView ix_{};
+    DevBuf<uint64_t> d_lines_, d_text_, d_keys_;
+    DevBuf<BuildChunk> d_chunks_;
+    DevBuf<uint32_t> d_first_, d_runs_, d_ends_;
+    DevBuf<unsigned int> d_err_;
+};
+
 static std::string build_stats(const SbwtHost& sbwt, const DeviceSbwt& ds, const uint8_t* d_lcs_bytes, const SeqBatch& unitigs,
                                const std::string& type, int64_t t) {
-    const int k = (int)sbwt.k;
-    const uint64_t N = (uint64_t)sbwt.n_nodes, U = unitigs.size();
-    check_unitigs(unitigs, k);
-    check_stats_t(t, sbwt.n_nodes);
-
-    DevBuf<uint64_t> d_lines = make_lines_device(ds, d_lcs_bytes);
-    IndexView ix{};
-    ix.lines = reinterpret_cast<const uint4*>(d_lines.p);
-    ix.n_nodes = (idx_t)N;
-    ix.k = k;
-    std::vector<uint64_t> order(U), starts;
-    std::iota(order.begin(), order.end(), 0);
-    PackedVec text;
-    pack_unitigs(unitigs, order, text, starts);
-    const PackedVec ends = unitig_ends(unitigs, order, starts);
-    const uint64_t T = text.size();
-    DevBuf<uint64_t> d_text = to_device(text.words, 2);
-    DevBuf<unsigned int> d_err(1);
-    FIN_CUDA(cudaMemset(d_err.p, 0, 4));
-
-    DevBuf<uint64_t> d_keys;
-    uint64_t n_keys = 0;
-    if (type == "shortest") {
-        const std::vector<BuildChunk> chunks = plan_build_chunks(starts, ends, k, 0);
-        const uint32_t nc = (uint32_t)chunks.size();
-        DevBuf<BuildChunk> d_chunks = to_device(chunks);
-        DevBuf<uint32_t> d_first(N), d_runs((size_t)nc + 1);
-        FIN_CUDA(cudaMemset(d_first.p, 0xFF, d_first.bytes()));
-        FIN_CUDA(cudaMemset(d_runs.p, 0, d_runs.bytes()));
-        const unsigned blocks = (nc + 127) / 128;
-        auto launch = [&](auto pass) {
-            constexpr int P = decltype(pass)::value;
-            switch (window_capacity(k)) {
-                case 32: shortest_stream_kernel<32, P><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, (uint32_t)t, d_first.p, d_runs.p, d_keys.p, d_err.p); break;
-                case 64: shortest_stream_kernel<64, P><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, (uint32_t)t, d_first.p, d_runs.p, d_keys.p, d_err.p); break;
-                case 128: shortest_stream_kernel<128, P><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, (uint32_t)t, d_first.p, d_runs.p, d_keys.p, d_err.p); break;
-                default: shortest_stream_kernel<256, P><<<blocks, 128>>>(ix, d_text.p, d_chunks.p, nc, (uint32_t)t, d_first.p, d_runs.p, d_keys.p, d_err.p); break;
-            }
-            g_launches++;
-            FIN_CUDA(cudaGetLastError());
-        };
-        launch(std::integral_constant<int, 0>());
-        {  // run counts -> offsets; the element past the last chunk becomes the total
-            size_t tb = 0;
-            cub::DeviceScan::ExclusiveSum(nullptr, tb, d_runs.p, d_runs.p, (int64_t)nc + 1);
-            DevBuf<uint8_t> tmp(tb + 256);
-            FIN_CUDA(cub::DeviceScan::ExclusiveSum(tmp.p, tb, d_runs.p, d_runs.p, (int64_t)nc + 1));
-            g_launches += 2;
-        }
-        uint32_t total = 0;
-        FIN_CUDA(cudaMemcpy(&total, d_runs.p + nc, 4, cudaMemcpyDeviceToHost));
-        n_keys = total;
-        d_keys.alloc(n_keys + 1);
-        launch(std::integral_constant<int, 1>());
-    } else {  // verify
-        std::vector<uint32_t> ends32(U);
-        for (uint64_t u = 0; u < U; u++) ends32[u] = (uint32_t)ends.words[u];
-        DevBuf<uint32_t> d_ends = to_device(ends32);
-        DevBuf<uint64_t> d_rec(T + 1);
-        n_keys = T;
-        d_keys.alloc(T + 1);
-        const unsigned blocks = (unsigned)((T + 255) / 256);
-        rare_prefix_kernel<<<blocks, 256>>>(ix, d_text.p, d_ends.p, (uint32_t)U, (uint32_t)T, (uint32_t)t, d_rec.p, d_err.p);
-        verify_window_kernel<<<blocks, 256>>>(d_rec.p, d_ends.p, (uint32_t)U, (uint32_t)T, k, d_keys.p, d_err.p);
-        g_launches += 2;
-        FIN_CUDA(cudaGetLastError());
-    }
-    unsigned err = 0;
-    FIN_CUDA(cudaMemcpy(&err, d_err.p, 4, cudaMemcpyDeviceToHost));
-    if (err)
-        throw domain_error("the unitigs are not a disjoint spectrum-preserving string set of this SBWT "
-                           "(a unitig k-mer is missing from the SBWT or a window has no substring with at most t occurrences)");
-
-    // the std::set of the reference: sort, unique, sum
-    unsigned long long sums[3] = {0, 0, 0};
-    if (n_keys) {
-        DevBuf<uint64_t> d_sorted(n_keys), d_unique(n_keys);
-        DevBuf<uint64_t> d_nuniq(1);
-        size_t tb1 = 0, tb2 = 0;
-        cub::DeviceRadixSort::SortKeys(nullptr, tb1, d_keys.p, d_sorted.p, (int64_t)n_keys);
-        cub::DeviceSelect::Unique(nullptr, tb2, d_sorted.p, d_unique.p, d_nuniq.p, (int64_t)n_keys);
-        DevBuf<uint8_t> tmp(std::max(tb1, tb2) + 256);
-        FIN_CUDA(cub::DeviceRadixSort::SortKeys(tmp.p, tb1, d_keys.p, d_sorted.p, (int64_t)n_keys));
-        FIN_CUDA(cub::DeviceSelect::Unique(tmp.p, tb2, d_sorted.p, d_unique.p, d_nuniq.p, (int64_t)n_keys));
-        g_launches += 10;
-        uint64_t n_unique = 0;
-        FIN_CUDA(cudaMemcpy(&n_unique, d_nuniq.p, 8, cudaMemcpyDeviceToHost));
-        DevBuf<unsigned long long> d_sums(3);
-        FIN_CUDA(cudaMemset(d_sums.p, 0, 24));
-        if (n_unique) {
-            stat_sum_kernel<<<(unsigned)((n_unique + 255) / 256), 256>>>(d_unique.p, n_unique, d_sums.p);
-            g_launches++;
-            FIN_CUDA(cudaGetLastError());
-        }
-        FIN_CUDA(cudaMemcpy(sums, d_sums.p, 24, cudaMemcpyDeviceToHost));
-    }
-    return stats_string(sums[0], sums[1], sums[2], sbwt.n_kmers);
+    StatsBuilder b(sbwt, ds, d_lcs_bytes, unitigs, type, t, 0, 1);
+    b.first_pass();
+    const uint64_t n = b.second_pass();
+    return b.finish(b.keys(), n);
 }
 
 // ---- staged builder behind the fin_builder_* entry points ---------------------------------------------------------
@@ -608,14 +676,28 @@ static PackedVec lcs_for_build(const SbwtHost& sbwt, const DeviceSbwt& ds, const
 RarestBuilder* builder_open(const std::string& sbwt_path, const std::string& unitig_path, const std::string& lcs_path,
                             const std::string& out_prefix, int device, int rank, int world) {
     const std::vector<std::string> files = unitig_file_list(unitig_path);
+    SeqBatch unitigs;  // read by a second host thread while this one loads the SBWT and computes the LCS
+    std::string unitig_error;
+    std::thread unitig_reader([&] {
+        try {
+            append_sequences(files[0], unitigs);
+        } catch (const std::exception& e) {
+            unitig_error = e.what();
+            if (unitig_error.empty()) unitig_error = "cannot read the unitig file";
+        }
+    });
+    struct Joiner {
+        std::thread& t;
+        ~Joiner() { if (t.joinable()) t.join(); }
+    } joiner{unitig_reader};
     SbwtHost sbwt = load_sbwt_file(sbwt_path, true);
     select_device(device);
     check_sbwt_limits(sbwt);
     const DeviceSbwt ds = upload_sbwt(sbwt);
     DevBuf<uint8_t> d_lcs;
     PackedVec lcs = lcs_for_build(sbwt, ds, lcs_path, out_prefix, false, d_lcs);  // rank 0 writes it with the other files (finish)
-    SeqBatch unitigs;
-    append_sequences(files[0], unitigs);
+    unitig_reader.join();
+    if (!unitig_error.empty()) throw io_error(unitig_error);
     return new RarestBuilder(std::move(sbwt), std::move(lcs), ds, std::move(d_lcs), unitigs, rank, world);
 }
 void builder_free(RarestBuilder* b) { delete b; }
@@ -647,6 +729,54 @@ void builder_finish(RarestBuilder& b, const uint64_t* bits_all, uint64_t n_bit_w
 
 thread_local fin_build_timing g_build_timing{};
 fin_build_timing last_build_timing() { return g_build_timing; }
+
+// ---- staged stats modes behind the fin_stats_* entry points --------------------------------------------------------
+struct StatsHandle {
+    SbwtHost sbwt;
+    DevBuf<uint8_t> d_lcs;
+    std::unique_ptr<StatsBuilder> b;
+    std::string out_prefix;
+    int rank = 0;
+};
+
+StatsHandle* stats_open(const std::string& sbwt_path, const std::string& unitig_path, const std::string& lcs_path, const std::string& out_prefix,
+                        const std::string& type, int64_t t, int device, int rank, int world) {
+    const std::vector<std::string> files = unitig_file_list(unitig_path);
+    std::unique_ptr<StatsHandle> h(new StatsHandle());
+    h->sbwt = load_sbwt_file(sbwt_path, true);
+    if (type != "shortest" && type != "verify") throw arg_error("Error: unknown type: " + type);
+    select_device(device);
+    check_sbwt_limits(h->sbwt);
+    const DeviceSbwt ds = upload_sbwt(h->sbwt);
+    // the reference computes and saves the LCS for every type (build_fmin.hh:373-380): rank 0 writes it
+    lcs_for_build(h->sbwt, ds, lcs_path, out_prefix, rank == 0 && !out_prefix.empty(), h->d_lcs);
+    SeqBatch unitigs;
+    append_sequences(files[0], unitigs);
+    h->b.reset(new StatsBuilder(h->sbwt, ds, h->d_lcs.p, unitigs, type, (int64_t)(signed char)t, rank, world));
+    h->out_prefix = out_prefix;
+    h->rank = rank;
+    return h.release();
+}
+void stats_free(StatsHandle* h) { delete h; }
+uint64_t stats_first_pass(StatsHandle& h) {
+    h.b->first_pass();
+    return h.b->table_entries();
+}
+void stats_table(StatsHandle& h, uint32_t* d_table, bool set) {
+    const uint64_t n = h.b->table_entries();
+    if (!n) return;
+    if (set) FIN_CUDA(cudaMemcpy(h.b->table(), d_table, n * 4, cudaMemcpyDeviceToDevice));
+    else FIN_CUDA(cudaMemcpy(d_table, h.b->table(), n * 4, cudaMemcpyDeviceToDevice));
+}
+uint64_t stats_second_pass(StatsHandle& h) { return h.b->second_pass(); }
+void stats_keys(const StatsHandle& h, uint64_t* d_keys) {
+    if (h.b->n_keys()) FIN_CUDA(cudaMemcpy(d_keys, h.b->keys(), h.b->n_keys() * 8, cudaMemcpyDeviceToDevice));
+}
+std::string stats_finish(StatsHandle& h, const uint64_t* d_keys_all, uint64_t n_keys_all, bool write_line) {
+    const std::string r = h.b->finish(d_keys_all, n_keys_all);
+    if (write_line && !h.out_prefix.empty()) append_stats_line(h.out_prefix, h.b->t(), r);
+    return r;
+}
 
 static double wall_ms() {
     timespec ts;

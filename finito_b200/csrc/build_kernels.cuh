@@ -606,29 +606,31 @@ FIN_D uint32_t unitig_of(const uint32_t* __restrict__ ends, uint32_t n_unitigs, 
     return lo;
 }
 
+// text positions [p_begin, p_end): rec[p - p_begin]
 static __global__ void rare_prefix_kernel(const IndexView ix, const uint64_t* __restrict__ text, const uint32_t* __restrict__ ends,
-                                          uint32_t n_unitigs, uint32_t text_len, uint32_t t, uint64_t* __restrict__ rec,
+                                          uint32_t n_unitigs, uint32_t p_begin, uint32_t p_end, uint32_t t, uint64_t* __restrict__ rec,
                                           unsigned int* __restrict__ error_flags) {
-    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= text_len) return;
+    const uint64_t p = (uint64_t)p_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= p_end) return;
     const uint32_t e = __ldg(ends + unitig_of(ends, n_unitigs, (uint32_t)p));
     unsigned err = 0;
-    rec[p] = shortest_rare_prefix(ix, text, p, (int)min((uint32_t)ix.k, e - (uint32_t)p), t, err);
+    rec[p - p_begin] = shortest_rare_prefix(ix, text, p, (int)min((uint32_t)ix.k, e - (uint32_t)p), t, err);
     if (err) atomicOr(error_flags, err);
 }
 
+// windows that start in [p_begin, p_end): keys[p - p_begin]; rec is indexed from p_begin and reaches k positions past p_end
 static __global__ void verify_window_kernel(const uint64_t* __restrict__ rec, const uint32_t* __restrict__ ends, uint32_t n_unitigs,
-                                            uint32_t text_len, int k, uint64_t* __restrict__ keys,
+                                            uint32_t p_begin, uint32_t p_end, int k, uint64_t* __restrict__ keys,
                                             unsigned int* __restrict__ error_flags) {
-    const uint64_t p = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= text_len) return;
+    const uint64_t p = (uint64_t)p_begin + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= p_end) return;
     const uint32_t e = __ldg(ends + unitig_of(ends, n_unitigs, (uint32_t)p));
     uint64_t key = kNoStatKey;
     if (p + (uint64_t)k <= e) {
-        key = verify_window_min(rec, p, k);
+        key = verify_window_min(rec, p - p_begin, k);
         if (key == kNoStatKey) atomicOr(error_flags, kErrWindowUnderflow);  // the reference inserts its sentinel (k+1, N, N)
     }
-    keys[p] = key;
+    keys[p - p_begin] = key;
 }
 
 // sums[0] += valid keys, sums[1] += their freq, sums[2] += their len   (print_finimizer_stats, common.hh:188-197)

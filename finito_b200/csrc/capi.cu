@@ -9,6 +9,11 @@ struct fin_index {
     std::unique_ptr<fin::DeviceIndex> dev;
 };
 
+struct fin_stats {
+    fin::StatsHandle* h = nullptr;
+    ~fin_stats() { fin::stats_free(h); }
+};
+
 struct fin_builder {
     fin::RarestBuilder* b = nullptr;
     ~fin_builder() { fin::builder_free(b); }
@@ -302,4 +307,50 @@ fin_status fin_builder_finish(fin_builder* b, const uint64_t* bits_all, uint64_t
     });
 }
 
+
+fin_status fin_stats_open(const char* sbwt_path, const char* unitig_path, const char* lcs_path, const char* out_prefix, const char* type,
+                          int64_t t, int device, int rank, int world, fin_stats** out) {
+    return guarded([&] {
+        require(sbwt_path && unitig_path && type && out, "fin_stats_open: null argument");
+        *out = nullptr;
+        std::unique_ptr<fin_stats> s(new fin_stats());
+        s->h = fin::stats_open(sbwt_path, unitig_path, lcs_path ? lcs_path : "", out_prefix ? out_prefix : "", type, t, device, rank, world);
+        *out = s.release();
+    });
+}
+void fin_stats_free(fin_stats* s) { delete s; }
+fin_status fin_stats_first_pass(fin_stats* s, uint64_t* n_table) {
+    return guarded([&] {
+        require(s && n_table, "fin_stats_first_pass: null argument");
+        *n_table = fin::stats_first_pass(*s->h);
+    });
+}
+fin_status fin_stats_table(fin_stats* s, void* d_table, int set) {
+    return guarded([&] {
+        require(s && d_table, "fin_stats_table: null argument");
+        fin::stats_table(*s->h, static_cast<uint32_t*>(d_table), set != 0);
+    });
+}
+fin_status fin_stats_second_pass(fin_stats* s, uint64_t* n_keys) {
+    return guarded([&] {
+        require(s && n_keys, "fin_stats_second_pass: null argument");
+        *n_keys = fin::stats_second_pass(*s->h);
+    });
+}
+fin_status fin_stats_keys(const fin_stats* s, void* d_keys) {
+    return guarded([&] {
+        require(s && d_keys, "fin_stats_keys: null argument");
+        fin::stats_keys(*s->h, static_cast<uint64_t*>(d_keys));
+    });
+}
+fin_status fin_stats_finish(fin_stats* s, const void* d_keys_all, uint64_t n_keys_all, int write_line, char* stats_out, size_t stats_cap) {
+    return guarded([&] {
+        require(s && (d_keys_all || n_keys_all == 0), "fin_stats_finish: null argument");
+        const std::string r = fin::stats_finish(*s->h, static_cast<const uint64_t*>(d_keys_all), n_keys_all, write_line != 0);
+        if (stats_out) {
+            require(r.size() + 1 <= stats_cap, "fin_stats_finish: stats buffer too small");
+            memcpy(stats_out, r.c_str(), r.size() + 1);
+        }
+    });
+}
 }  // extern "C"

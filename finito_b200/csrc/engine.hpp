@@ -132,4 +132,15 @@ void builder_slice(const RarestBuilder& b, uint64_t* d_bits, uint32_t* d_offsets
 void builder_finish(RarestBuilder& b, const uint64_t* bits_all, uint64_t n_bit_words, const uint32_t* offsets_all, uint64_t n_offsets,
                     const std::string& out_prefix);
 
+// staged build-fmin --type shortest|verify, shardable over GPUs (build.cu)
+struct StatsHandle;
+StatsHandle* stats_open(const std::string& sbwt_path, const std::string& unitig_path, const std::string& lcs_path, const std::string& out_prefix,
+                        const std::string& type, int64_t t, int device, int rank, int world);
+void stats_free(StatsHandle* h);
+uint64_t stats_first_pass(StatsHandle& h);
+void stats_table(StatsHandle& h, uint32_t* d_table, bool set);
+uint64_t stats_second_pass(StatsHandle& h);
+void stats_keys(const StatsHandle& h, uint64_t* d_keys);
+std::string stats_finish(StatsHandle& h, const uint64_t* d_keys_all, uint64_t n_keys_all, bool write_line);
+
 }  // namespace fin

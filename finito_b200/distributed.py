@@ -9,6 +9,10 @@ build-fmin   — the stream over the permuted unitigs (include/FinimizerIndex.hh
                writes the files.  `builder` is a finito_b200.ShardedBuilder (device buffers, NCCL) — or, in the CPU
                tests, an object with the same methods over host memory (gloo).
 
+build-fmin --type shortest|verify — every rank streams a share of the unitigs (shortest) or of the text positions
+               (verify); the per-column "first window" tables meet in ONE all-reduce(MIN), the key sets in ONE all-gather,
+               and every rank can then sort + unique + sum them (the reference's std::set, include/build_fmin.hh:134-214).
+
 Nothing here computes: the kernels are behind the C ABI.
 """
 from __future__ import annotations
@@ -109,3 +113,33 @@ def build_fmin_sharded(builder, group=None) -> dict:
     dist.barrier(group=group)
     return {"rank": rank, "world": world, "tuples_sent": n_tuples, "tuples_received": n_recv, "slice_finimizers": n_slice,
             "finimizers": sum(ns), "bases_streamed": int(info["bases_streamed"]), "stream_ms": float(builder.info["stream_ms"])}
+
+
+def stats_sharded(stats, group=None, write_line: bool = False) -> str:
+    """Drives one rank's ShardedStats (or the CPU stand-in of the tests) through first pass -> all-reduce(MIN) of the tables ->
+    second pass -> all-gather of the keys -> finish.  Returns the stats string (the same on every rank)."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    dev = torch.device("cuda", torch.cuda.current_device()) if stats.memory == "cuda" else torch.device("cpu")
+    n_table = stats.first_pass()
+    if n_table:
+        table = torch.empty(n_table, dtype=torch.int32, device=dev)  # u32 entries, 0xFFFFFFFF = no such window: unsigned MIN
+        stats.table_out(table.data_ptr())
+        as_i64 = table.to(torch.int64) & 0xFFFFFFFF
+        dist.all_reduce(as_i64, op=dist.ReduceOp.MIN, group=group)
+        table = as_i64.to(torch.int32)  # wraps the values >= 2^31 back to their bit pattern
+        stats.table_in(table.data_ptr())
+    n_keys = stats.second_pass()
+    mine = torch.empty(max(1, n_keys), dtype=torch.int64, device=dev)
+    stats.keys(mine.data_ptr())
+    sizes = torch.zeros(world, dtype=torch.int64, device=dev)
+    sizes[rank] = n_keys
+    dist.all_reduce(sizes, group=group)
+    sizes = [int(x) for x in sizes.cpu()]
+    pad = torch.zeros(max(1, max(sizes)), dtype=torch.int64, device=dev)
+    pad[:n_keys] = mine[:n_keys]
+    parts = [torch.empty_like(pad) for _ in range(world)]
+    dist.all_gather(parts, pad, group=group)
+    all_keys = torch.cat([p[:n] for p, n in zip(parts, sizes)]).contiguous()
+    if dev.type == "cuda":
+        torch.cuda.synchronize()
+    return stats.finish(all_keys.data_ptr(), int(all_keys.numel()), write_line=write_line and rank == 0)

@@ -274,6 +274,34 @@ fin_status fin_builder_slice(const fin_builder* b, void* d_bits, void* d_offsets
 fin_status fin_builder_finish(fin_builder* b, const uint64_t* bits_all, uint64_t n_bit_words, const uint32_t* offsets_all,
                               uint64_t n_offsets, const char* out_prefix);
 
+/* ------------------------------------------------------------------------------------------------
+ * build-fmin --type shortest | verify sharded over GPUs (include/build_fmin.hh:95-214): one process (or thread) per GPU,
+ * every rank opens the same inputs.  The reference streams the unitigs in file order with one shared `fmin_found` bit
+ * vector; its insertion rule has an order-free closed form (a window inserts iff no window with the same finimizer column
+ * that ends at or after position k-1 of its unitig comes earlier in the file), so rank r streams a share of the unitigs and
+ * the ranks meet twice.  Call order on every rank:
+ *   fin_stats_open        -> loads, LCS (rank 0 writes <out_prefix>.LCS.sdsl when out_prefix is not NULL/""), this rank's share
+ *   fin_stats_first_pass  -> shortest: table[column] = first such window of this rank's share; *n_table = its entries
+ *                            (n_nodes; 0 for verify, which needs no table)
+ *   fin_stats_table(out)  -> DEVICE u32[n_table]  ... the caller reduces the tables with MIN over the ranks (one all-reduce) ...
+ *   fin_stats_table(in)   -> the reduced table
+ *   fin_stats_second_pass -> this rank's keys (len, freq, column), *n_keys of them
+ *   fin_stats_keys        -> DEVICE u64[n_keys]  ... the caller concatenates the keys of all ranks (one all-gather) ...
+ *   fin_stats_finish      -> any rank: sort + unique + sums over ALL keys (DEVICE) = the reference's std::set; stats_out
+ *                            receives "<n>,<sum freq>,<avg freq>,<avg len>,<n k-mers>" (common.hh:188-206); write_line != 0
+ *                            appends "<t>,<stats>\n" to <out_prefix>_stats.txt (build_fmin.hh:386-395)
+ * world == 1: open, first_pass, second_pass, keys, finish  (what fin_build does for these types).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct fin_stats fin_stats;
+fin_status fin_stats_open(const char* sbwt_path, const char* unitig_path, const char* lcs_path, const char* out_prefix, const char* type,
+                          int64_t t, int device, int rank, int world, fin_stats** out);
+void fin_stats_free(fin_stats* s);
+fin_status fin_stats_first_pass(fin_stats* s, uint64_t* n_table);
+fin_status fin_stats_table(fin_stats* s, void* d_table, int set);
+fin_status fin_stats_second_pass(fin_stats* s, uint64_t* n_keys);
+fin_status fin_stats_keys(const fin_stats* s, void* d_keys);
+fin_status fin_stats_finish(fin_stats* s, const void* d_keys_all, uint64_t n_keys_all, int write_line, char* stats_out, size_t stats_cap);
+
 #ifdef __cplusplus
 }
 #endif

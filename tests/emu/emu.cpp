@@ -94,6 +94,115 @@ static std::vector<uint8_t> emu_lcs_bytes(const SbwtHost& s) {
     return lcs;
 }
 
+// build-fmin --type shortest|verify with the kernel bodies (one "thread" after the other), staged like StatsBuilder in
+// build.cu so that the gloo tests can shard it: rank r of `world` streams a share of the chunks (shortest) or of the text
+// positions (verify)
+struct EmuStats {
+    SbwtHost sbwt;
+    PackedVec lcs_file, text, ends;
+    std::vector<uint64_t> lines;
+    IndexView ix{};
+    std::string type;
+    uint32_t t = 1;
+    int k = 0;
+    uint64_t N = 0, T = 0, p0 = 0, p1 = 0;
+    std::vector<BuildChunk> chunks;  // this rank's
+    std::vector<uint32_t> first, runs;
+    std::vector<uint64_t> keys;
+    unsigned err = 0;
+
+    EmuStats(const char* sbwt_path, const char* unitig_path, const std::string& type_, int64_t t_, uint64_t per_chunk, int rank, int world)
+        : type(type_), t((uint32_t)t_) {
+        if (type != "shortest" && type != "verify") throw arg_error("emu_stats: type");
+        const std::vector<std::string> files = unitig_file_list(unitig_path);
+        sbwt = load_sbwt_file(sbwt_path, true);
+        check_sbwt_limits(sbwt);
+        N = (uint64_t)sbwt.n_nodes;
+        k = (int)sbwt.k;
+        check_stats_t(t_, sbwt.n_nodes);
+        lcs_file = lcs_bytes_to_packed(emu_lcs_bytes(sbwt), N, k);
+        SeqBatch unitigs;
+        append_sequences(files[0], unitigs);
+        check_unitigs(unitigs, k);
+        const uint64_t U = unitigs.size();
+        lines = make_lines(sbwt, &lcs_file, nullptr, nullptr);
+        ix.lines = reinterpret_cast<const uint4*>(lines.data());
+        ix.n_nodes = (idx_t)N;
+        ix.k = k;
+        std::vector<uint64_t> order(U), starts;
+        for (uint64_t u = 0; u < U; u++) order[u] = u;
+        pack_unitigs(unitigs, order, text, starts);
+        text.words.resize(text.words.size() + 2, 0);
+        ends = unitig_ends(unitigs, order, starts);
+        T = text.size();
+        if (type == "shortest") {
+            const std::vector<BuildChunk> all = plan_build_chunks(starts, ends, k, per_chunk);
+            const std::pair<size_t, size_t> mine = shard_chunks(all, rank, world);
+            chunks.assign(all.begin() + (long)mine.first, all.begin() + (long)mine.second);
+            first.assign(N, 0xFFFFFFFFu);
+            runs.assign(chunks.size() + 1, 0);
+        } else {
+            p0 = T * (uint64_t)rank / (uint64_t)world;
+            p1 = T * (uint64_t)(rank + 1) / (uint64_t)world;
+        }
+    }
+
+    template <class Pass> uint32_t run(Pass, size_t c, uint64_t* out) {
+        constexpr int P = Pass::value;
+        if (k <= 32) return shortest_stream_chunk<32, P>(ix, text.words.data(), chunks[c], t, first.data(), out, &err);
+        if (k <= 64) return shortest_stream_chunk<64, P>(ix, text.words.data(), chunks[c], t, first.data(), out, &err);
+        if (k <= 128) return shortest_stream_chunk<128, P>(ix, text.words.data(), chunks[c], t, first.data(), out, &err);
+        return shortest_stream_chunk<256, P>(ix, text.words.data(), chunks[c], t, first.data(), out, &err);
+    }
+
+    uint64_t first_pass() {
+        if (type != "shortest") return 0;
+        // the chunks in REVERSE order: the result must not depend on the order the "threads" run in
+        for (size_t c = chunks.size(); c-- > 0;) runs[c] = run(std::integral_constant<int, 0>(), c, nullptr);
+        return N;
+    }
+
+    uint64_t second_pass() {
+        keys.clear();
+        if (type == "shortest") {
+            uint64_t total = 0;
+            for (size_t c = 0; c < chunks.size(); c++) { const uint32_t n = runs[c]; runs[c] = (uint32_t)total; total += n; }
+            keys.assign(total + 1, kNoStatKey);
+            for (size_t c = chunks.size(); c-- > 0;) run(std::integral_constant<int, 1>(), c, keys.data() + runs[c]);
+            keys.resize(total);
+        } else {
+            const uint64_t r1 = std::min<uint64_t>(T, p1 + (uint64_t)k);
+            std::vector<uint64_t> rec(r1 - p0 + 1, kNoStatKey);
+            uint64_t u = 0;
+            for (uint64_t p = p0; p < r1; p++) {
+                while (ends.words[u] <= p) u++;
+                rec[p - p0] = shortest_rare_prefix(ix, text.words.data(), p, (int)std::min<uint64_t>((uint64_t)k, ends.words[u] - p), t, err);
+            }
+            u = 0;
+            for (uint64_t p = p0; p < p1; p++) {
+                while (ends.words[u] <= p) u++;
+                if (p + (uint64_t)k <= ends.words[u]) {
+                    const uint64_t key = verify_window_min(rec.data(), p - p0, k);
+                    if (key == kNoStatKey) err |= kErrWindowUnderflow;
+                    keys.push_back(key);
+                }
+            }
+        }
+        if (err) throw domain_error("emu: stats stream error flags " + std::to_string(err));
+        return keys.size();
+    }
+
+    std::string finish(const uint64_t* all, uint64_t n_all) const {
+        std::vector<uint64_t> v(all, all + n_all);
+        std::sort(v.begin(), v.end());
+        v.erase(std::unique(v.begin(), v.end()), v.end());
+        uint64_t n = 0, sf = 0, sl = 0;
+        for (uint64_t key : v)
+            if (key != kNoStatKey) { n++; sf += (key >> 32) & 0xFF; sl += key >> 40; }
+        return stats_string(n, sf, sl, sbwt.n_kmers);
+    }
+};
+
 extern "C" {
 
 const char* emu_last_error() { return g_err.c_str(); }
@@ -253,78 +362,46 @@ int emu_build(const char* sbwt_path, const char* unitig_path, const char* out_pr
 }
 
 
-// build-fmin --type shortest|verify with the kernel bodies (one "thread" after the other); result = the stats string
+void* emu_stats_open(const char* sbwt_path, const char* unitig_path, const char* type, int64_t t, int rank, int world) {
+    EmuStats* h = nullptr;
+    if (guarded([&] { h = new EmuStats(sbwt_path, unitig_path, type, t, 0, rank, world); })) return nullptr;
+    return h;
+}
+void emu_stats_free(void* h) { delete static_cast<EmuStats*>(h); }
+int emu_stats_first_pass(void* h, uint64_t* n_table) {
+    return guarded([&] { *n_table = static_cast<EmuStats*>(h)->first_pass(); });
+}
+int emu_stats_table(void* h, uint32_t* table, int set) {
+    return guarded([&] {
+        EmuStats& e = *static_cast<EmuStats*>(h);
+        if (set) memcpy(e.first.data(), table, e.first.size() * 4);
+        else memcpy(table, e.first.data(), e.first.size() * 4);
+    });
+}
+int emu_stats_second_pass(void* h, uint64_t* n_keys) {
+    return guarded([&] { *n_keys = static_cast<EmuStats*>(h)->second_pass(); });
+}
+int emu_stats_keys(void* h, uint64_t* out) {
+    return guarded([&] {
+        const EmuStats& e = *static_cast<EmuStats*>(h);
+        if (!e.keys.empty()) memcpy(out, e.keys.data(), e.keys.size() * 8);
+    });
+}
+int emu_stats_finish(void* h, const uint64_t* keys, uint64_t n, char* result, uint64_t cap) {
+    return guarded([&] {
+        const std::string r = static_cast<EmuStats*>(h)->finish(keys, n);
+        if (r.size() + 1 > cap) throw arg_error("buffer too small");
+        memcpy(result, r.c_str(), r.size() + 1);
+    });
+}
+
 int emu_stats(const char* sbwt_path, const char* unitig_path, const char* type_c, int64_t t, uint64_t per_chunk, char* result,
               uint64_t cap) {
     return guarded([&] {
-        const std::string type = type_c;
-        const std::vector<std::string> files = unitig_file_list(unitig_path);
-        SbwtHost sbwt = load_sbwt_file(sbwt_path, true);
-        check_sbwt_limits(sbwt);
-        const uint64_t N = (uint64_t)sbwt.n_nodes;
-        const int k = (int)sbwt.k;
-        check_stats_t(t, sbwt.n_nodes);
-        PackedVec lcs_file = lcs_bytes_to_packed(emu_lcs_bytes(sbwt), N, k);
-        SeqBatch unitigs;
-        append_sequences(files[0], unitigs);
-        check_unitigs(unitigs, k);
-        const uint64_t U = unitigs.size();
-        std::vector<uint64_t> lines = make_lines(sbwt, &lcs_file, nullptr, nullptr);
-        IndexView ix{};
-        ix.lines = reinterpret_cast<const uint4*>(lines.data());
-        ix.n_nodes = (idx_t)N;
-        ix.k = k;
-        std::vector<uint64_t> order(U), starts;
-        for (uint64_t u = 0; u < U; u++) order[u] = u;
-        PackedVec text;
-        pack_unitigs(unitigs, order, text, starts);
-        text.words.resize(text.words.size() + 2, 0);
-        PackedVec ends = unitig_ends(unitigs, order, starts);
-        const uint64_t T = text.size();
-        unsigned err = 0;
-        std::vector<uint64_t> keys;
-        if (type == "shortest") {
-            std::vector<BuildChunk> chunks = plan_build_chunks(starts, ends, k, per_chunk);
-            std::vector<uint32_t> first(N, 0xFFFFFFFFu), runs(chunks.size() + 1, 0);
-            auto run = [&](auto pass, size_t c, uint64_t* out) -> uint32_t {
-                constexpr int P = decltype(pass)::value;
-                if (k <= 32) return shortest_stream_chunk<32, P>(ix, text.words.data(), chunks[c], (uint32_t)t, first.data(), out, &err);
-                if (k <= 64) return shortest_stream_chunk<64, P>(ix, text.words.data(), chunks[c], (uint32_t)t, first.data(), out, &err);
-                if (k <= 128) return shortest_stream_chunk<128, P>(ix, text.words.data(), chunks[c], (uint32_t)t, first.data(), out, &err);
-                return shortest_stream_chunk<256, P>(ix, text.words.data(), chunks[c], (uint32_t)t, first.data(), out, &err);
-            };
-            // the chunks in REVERSE order: the result must not depend on the order the "threads" run in
-            uint64_t total = 0;
-            for (size_t c = chunks.size(); c-- > 0;) runs[c] = run(std::integral_constant<int, 0>(), c, nullptr);
-            for (size_t c = 0; c < chunks.size(); c++) { const uint32_t n = runs[c]; runs[c] = (uint32_t)total; total += n; }
-            keys.assign(total + 1, kNoStatKey);
-            for (size_t c = chunks.size(); c-- > 0;) run(std::integral_constant<int, 1>(), c, keys.data() + runs[c]);
-        } else if (type == "verify") {
-            std::vector<uint64_t> rec(T + 1, kNoStatKey);
-            uint64_t u = 0;
-            for (uint64_t p = 0; p < T; p++) {
-                while (ends.words[u] <= p) u++;
-                rec[p] = shortest_rare_prefix(ix, text.words.data(), p, (int)std::min<uint64_t>((uint64_t)k, ends.words[u] - p), (uint32_t)t, err);
-            }
-            u = 0;
-            for (uint64_t p = 0; p < T; p++) {
-                while (ends.words[u] <= p) u++;
-                if (p + (uint64_t)k <= ends.words[u]) {
-                    const uint64_t key = verify_window_min(rec.data(), p, k);
-                    if (key == kNoStatKey) err |= kErrWindowUnderflow;
-                    keys.push_back(key);
-                }
-            }
-        } else {
-            throw arg_error("emu_stats: type");
-        }
-        if (err) throw domain_error("emu: stats stream error flags " + std::to_string(err));
-        std::sort(keys.begin(), keys.end());
-        keys.erase(std::unique(keys.begin(), keys.end()), keys.end());
-        uint64_t n = 0, sf = 0, sl = 0;
-        for (uint64_t key : keys)
-            if (key != kNoStatKey) { n++; sf += (key >> 32) & 0xFF; sl += key >> 40; }
-        const std::string r = stats_string(n, sf, sl, sbwt.n_kmers);
+        EmuStats e(sbwt_path, unitig_path, type_c, t, per_chunk, 0, 1);
+        e.first_pass();
+        e.second_pass();
+        const std::string r = e.finish(e.keys.data(), e.keys.size());
         if (r.size() + 1 > cap) throw arg_error("buffer too small");
         memcpy(result, r.c_str(), r.size() + 1);
     });

@@ -144,6 +144,14 @@ def emu_lib() -> C.CDLL:
     lib.emu_builder_slice.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
     lib.emu_builder_finish.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]
     lib.emu_stats.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_uint64, C.c_char_p, C.c_uint64]
+    lib.emu_stats_open.restype = C.c_void_p
+    lib.emu_stats_open.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int64, C.c_int, C.c_int]
+    lib.emu_stats_free.argtypes = [C.c_void_p]
+    lib.emu_stats_first_pass.argtypes = [C.c_void_p, C.c_void_p]
+    lib.emu_stats_table.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    lib.emu_stats_second_pass.argtypes = [C.c_void_p, C.c_void_p]
+    lib.emu_stats_keys.argtypes = [C.c_void_p, C.c_void_p]
+    lib.emu_stats_finish.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_char_p, C.c_uint64]
     return lib
 
 
@@ -227,6 +235,52 @@ class EmuShardedBuilder:
     def close(self):
         if self.h:
             self.lib.emu_builder_free(self.h)
+            self.h = None
+
+
+class EmuShardedStats:
+    """Same methods as finito_b200.ShardedStats over HOST memory, the streams run by the kernel bodies on the CPU
+    (tests/emu).  Test infrastructure: lets gloo tests drive finito_b200.distributed.stats_sharded without a GPU."""
+
+    memory = "cpu"
+
+    def __init__(self, sbwt, unitigs, type, t, rank, world):
+        self.lib = emu_lib()
+        self.h = self.lib.emu_stats_open(os.fsencode(sbwt), os.fsencode(unitigs), type.encode(), t, rank, world)
+        if not self.h:
+            raise RuntimeError("emu: " + self.lib.emu_last_error().decode())
+
+    def _ok(self, rc):
+        if rc:
+            raise RuntimeError("emu: " + self.lib.emu_last_error().decode())
+
+    def first_pass(self):
+        n = np.zeros(1, dtype=np.uint64)
+        self._ok(self.lib.emu_stats_first_pass(self.h, n.ctypes.data))
+        return int(n[0])
+
+    def table_out(self, ptr):
+        self._ok(self.lib.emu_stats_table(self.h, ptr, 0))
+
+    def table_in(self, ptr):
+        self._ok(self.lib.emu_stats_table(self.h, ptr, 1))
+
+    def second_pass(self):
+        n = np.zeros(1, dtype=np.uint64)
+        self._ok(self.lib.emu_stats_second_pass(self.h, n.ctypes.data))
+        return int(n[0])
+
+    def keys(self, ptr):
+        self._ok(self.lib.emu_stats_keys(self.h, ptr))
+
+    def finish(self, keys_ptr, n_keys, write_line=False):
+        buf = C.create_string_buffer(512)
+        self._ok(self.lib.emu_stats_finish(self.h, keys_ptr, n_keys, buf, 512))
+        return buf.value.decode()
+
+    def close(self):
+        if self.h:
+            self.lib.emu_stats_free(self.h)
             self.h = None
 
 

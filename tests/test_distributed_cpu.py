@@ -121,3 +121,31 @@ def test_sharded_search_equals_single_process(world, tmp_path):
     for r in res:
         assert r[2] == [int(x) for x in wc]           # every rank holds the summed counters
     assert sum(r[3] for r in res) == want.shape[0]
+
+
+def _stats_worker(rank, world, port, sbwt, unitigs, typ, t, q):
+    try:
+        _init(rank, world, port)
+        from finito_b200.distributed import stats_sharded
+
+        s = H.EmuShardedStats(sbwt, unitigs, typ, t, rank, world)
+        q.put((rank, stats_sharded(s)))
+        s.close()
+        dist.destroy_process_group()
+    except Exception as e:
+        q.put((rank, repr(e)))
+        raise
+
+
+@pytest.mark.parametrize("case,world", [("syn_k31", 2), ("syn_k12", 3), ("kat_paper_example", 2)])
+def test_sharded_stats_modes_print_the_reference_line(case, world):
+    """build-fmin --type shortest|verify -t T sharded over `world` ranks (one all-reduce(MIN) of the first-window tables, one
+    all-gather of the keys): the `<t>,<stats>` line the unmodified reference wrote (tests/golden/stats_modes.json)."""
+    import json
+
+    d = os.path.join(H.GOLDEN, case)
+    for mode, line in json.load(open(os.path.join(H.GOLDEN, "stats_modes.json")))[case].items():
+        typ, t = mode.split(":")
+        res = _spawn(_stats_worker, world, (os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), typ, int(t)))
+        for r in res:
+            assert f"{t},{r[1]}\n" == line, (case, mode, r)

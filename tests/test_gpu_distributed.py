@@ -129,3 +129,101 @@ def test_nccl_build_and_search_over_all_gpus(gpu_lib, tmp_path):
     want, wc = H.Oracle(op).search_reads(seqs, offs)
     assert np.array_equal(res[0][2], want)
     assert all(r[3] == [int(x) for x in wc] for r in res)
+
+
+def stats_on_one_gpu(fb, sbwt, unitigs, typ, t, world):
+    """`world` ShardedStats on device 0; the all-reduce(MIN) and the all-gather of distributed.stats_sharded done with torch ops."""
+    import torch
+
+    ss = [fb.ShardedStats(sbwt, unitigs, typ, t, r, world, device=0) for r in range(world)]
+    tables = []
+    for s in ss:
+        n = s.first_pass()
+        if n:
+            tb = torch.empty(n, dtype=torch.int32, device="cuda")
+            s.table_out(tb.data_ptr())
+            tables.append(tb.to(torch.int64) & 0xFFFFFFFF)
+    if tables:
+        red = torch.stack(tables).min(dim=0).values.to(torch.int32)
+        for s in ss:
+            s.table_in(red.data_ptr())
+    keys = []
+    for s in ss:
+        n = s.second_pass()
+        kb = torch.empty(max(1, n), dtype=torch.int64, device="cuda")
+        s.keys(kb.data_ptr())
+        keys.append(kb[:n])
+    allk = torch.cat(keys).contiguous()
+    torch.cuda.synchronize()
+    out = [s.finish(allk.data_ptr(), int(allk.numel())) for s in ss]
+    shares = [int(x.numel()) for x in keys]
+    for s in ss:
+        s.close()
+    assert len(set(out)) == 1
+    return out[0], shares
+
+
+@pytest.mark.parametrize("case", golden_cases())
+@pytest.mark.parametrize("world", [1, 3])
+def test_staged_stats_golden(case, world, gpu_lib):
+    import json
+
+    d = os.path.join(H.GOLDEN, case)
+    for mode, line in json.load(open(os.path.join(H.GOLDEN, "stats_modes.json")))[case].items():
+        typ, t = mode.split(":")
+        got, _ = stats_on_one_gpu(gpu_lib, os.path.join(d, "input.sbwt"), os.path.join(d, "unitigs.fna"), typ, int(t), world)
+        assert f"{t},{got}\n" == line, (case, mode, world)
+
+
+@pytest.mark.parametrize("typ,t,world", [("shortest", 4, 8), ("verify", 4, 5), ("shortest", 1, 2)])
+def test_staged_stats_synthetic_matches_oracle(typ, t, world, gpu_lib, tmp_path):
+    ds = make_dataset("gpub", genome_len=1_000_000, k=31, n_reads=2000, read_len=150, seed=131)
+    want = H.oracle_build(ds["sbwt"], ds["unitigs"], str(tmp_path / "orc"), type=typ, t=t)
+    got, shares = stats_on_one_gpu(gpu_lib, ds["sbwt"], ds["unitigs"], typ, t, world)
+    assert got == want
+    assert min(shares) > 0  # every rank produced keys
+    assert gpu_lib.build_fmin(ds["sbwt"], ds["unitigs"], str(tmp_path / "one"), type=typ, t=t) == want
+
+
+def _nccl_stats_worker(rank, world, port, sbwt, unitigs, typ, t, q):
+    try:
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+        sys.path.insert(0, ROOT)
+        import torch
+        import torch.distributed as dist
+
+        import finito_b200 as fb
+        from finito_b200.distributed import stats_sharded
+
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+        s = fb.ShardedStats(sbwt, unitigs, typ, t, rank, world, device=rank)
+        q.put((rank, stats_sharded(s)))
+        s.close()
+        dist.destroy_process_group()
+    except Exception as e:
+        q.put((rank, repr(e)))
+        raise
+
+
+def test_nccl_stats_over_all_gpus(gpu_lib, tmp_path):
+    import torch
+    import torch.multiprocessing as mp
+
+    world = min(torch.cuda.device_count(), 8)
+    if world < 2:
+        pytest.skip("needs >= 2 GPUs (the one-GPU box covers the stages with test_staged_stats_*)")
+    ds = make_dataset("gpub", genome_len=1_000_000, k=31, n_reads=2000, read_len=150, seed=131)
+    for typ, t in (("shortest", 4), ("verify", 2)):
+        want = H.oracle_build(ds["sbwt"], ds["unitigs"], str(tmp_path / f"orc{typ}"), type=typ, t=t)
+        ctx = mp.get_context("spawn")
+        q = ctx.Queue()
+        port = 29500 + (os.getpid() + t) % 2000
+        procs = [ctx.Process(target=_nccl_stats_worker, args=(r, world, port, ds["sbwt"], ds["unitigs"], typ, t, q)) for r in range(world)]
+        for p in procs:
+            p.start()
+        res = [q.get(timeout=600) for _ in range(world)]
+        for p in procs:
+            p.join(timeout=60)
+            assert p.exitcode == 0
+        assert all(r[1] == want for r in res), (typ, res)
