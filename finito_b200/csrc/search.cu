@@ -128,15 +128,15 @@ DeviceIndex::~DeviceIndex() {
 static int window_capacity(int k) { return k <= 32 ? 32 : k <= 64 ? 64 : k <= 128 ? 128 : 256; }
 
 // persistent grid: as many blocks as are resident at once (148 SMs x blocks per SM), never more than the reads need
-template <int KCAP, class HitT, bool COUNT, bool RUNS>
-static void launch_search_k(const IndexView& v, const uint64_t* packed, const uint64_t* offsets, uint64_t n_reads,
+template <int KCAP, class HitT, bool COUNT, bool RUNS, int G>
+static void launch_search_g(const IndexView& v, const uint64_t* packed, const uint64_t* offsets, uint64_t n_reads,
                             const SearchOut<HitT>& out, SearchTotals* totals, int n_strands, cudaStream_t st) {
     const int threads = FIN_SEARCH_THREADS;
     static thread_local int resident[64] = {0};  // per device
     int dev = 0;
     FIN_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) throw arg_error("CUDA device ordinal out of range");
-    auto kernel = search_reads_kernel<KCAP, HitT, COUNT, RUNS>;
+    auto kernel = search_reads_kernel<KCAP, HitT, COUNT, RUNS, G>;
     if (!resident[dev]) {
         int per_sm = 0, sms = 0;
         // no shared memory: all of the unified L1/shared array as L1 (the index lines live there)
@@ -145,11 +145,31 @@ static void launch_search_k(const IndexView& v, const uint64_t* packed, const ui
         FIN_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
         resident[dev] = std::max(1, per_sm) * std::max(1, sms);
     }
-    const uint64_t need = (n_reads + threads - 1) / threads;
+    const uint64_t need = (n_reads * (uint64_t)G + threads - 1) / threads;
     const unsigned blocks = (unsigned)std::min<uint64_t>(need, (uint64_t)resident[dev]);
     kernel<<<blocks, threads, 0, st>>>(v, packed, offsets, n_reads, out, totals, n_strands);
     g_launches++;
     FIN_CUDA(cudaGetLastError());
+}
+
+// FIN_COOP_GROUP=2|4: the warp-cooperative variant (G lanes per chain), dense int32 hits without counters, k <= 64 only
+static int coop_group() {
+    static const int g = [] {
+        const char* e = getenv("FIN_COOP_GROUP");
+        const int v = e ? atoi(e) : 1;
+        return v == 2 || v == 4 ? v : 1;
+    }();
+    return g;
+}
+
+template <int KCAP, class HitT, bool COUNT, bool RUNS>
+static void launch_search_k(const IndexView& v, const uint64_t* packed, const uint64_t* offsets, uint64_t n_reads,
+                            const SearchOut<HitT>& out, SearchTotals* totals, int n_strands, cudaStream_t st) {
+    if constexpr (KCAP <= 64 && sizeof(HitT) == 4 && !COUNT && !RUNS) {
+        if (coop_group() == 2) return launch_search_g<KCAP, HitT, COUNT, RUNS, 2>(v, packed, offsets, n_reads, out, totals, n_strands, st);
+        if (coop_group() == 4) return launch_search_g<KCAP, HitT, COUNT, RUNS, 4>(v, packed, offsets, n_reads, out, totals, n_strands, st);
+    }
+    launch_search_g<KCAP, HitT, COUNT, RUNS, 1>(v, packed, offsets, n_reads, out, totals, n_strands, st);
 }
 
 template <class HitT, bool COUNT, bool RUNS>

@@ -370,7 +370,14 @@ template <class HitT> struct SearchOut {
     const uint8_t* strand_flags;  // per read kStrandFwd | kStrandRc from strand_filter_kernel; nullptr = stream every strand
 };
 
-template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
+// G > 1 = the warp-cooperative variant (BASELINE.json north_star; SURVEY.md section 7 hard part 1): G adjacent lanes own ONE
+// chain.  The control flow and the scalar state are replicated on the G lanes (it costs no issue slots: they execute the
+// same instructions anyway), the memory accesses of a step are dealt out - lane q of the group fetches the q-th rank row /
+// LCS word and the group exchanges the results with __shfl_sync - and only the group's first lane writes answers and
+// tallies counters.  Measured against G = 1 in profiles/r2_sweep_warp_cooperative.log (it loses: chains in flight per SM,
+// not loads per chain, are what hides the latency of a dependent walk); kept selectable with FIN_COOP_GROUP=2|4 so that
+// the comparison can be repeated, dense int32 hits only.
+template <int KCAP, class HitT, bool COUNT, bool RUNS, int G = 1> struct Chain {
     static constexpr bool WIDE = KCAP > 128;
     // the read
     uint64_t b0 = 0;
@@ -456,11 +463,28 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS> struct Chain {
                     const SearchOut<HitT>& out);
 };
 
-template <int KCAP, class HitT, bool COUNT, bool RUNS>
-FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc,
+#if defined(__CUDACC__) && !defined(FIN_EMU)
+// cooperative loads of a group of G lanes (G a power of two <= 32): the owner loads, everybody receives
+template <int G> FIN_D unsigned coop_sub() { return threadIdx.x & (unsigned)(G - 1); }
+template <int G> FIN_D unsigned coop_mask() { return (G >= 32 ? 0xFFFFFFFFu : ((1u << G) - 1u)) << ((threadIdx.x & 31u) & ~(unsigned)(G - 1)); }
+template <int G> FIN_D uint32_t coop_u32(const bool cond, const uint32_t v_owner, const int owner) {
+    return cond ? __shfl_sync(coop_mask<G>(), v_owner, owner, G) : 0u;
+}
+template <int G> FIN_D uint64_t coop_u64(const bool cond, const uint64_t v_owner, const int owner) {
+    return cond ? __shfl_sync(coop_mask<G>(), v_owner, owner, G) : 0ull;
+}
+#endif
+
+template <int KCAP, class HitT, bool COUNT, bool RUNS, int G>
+FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const uint64_t* __restrict__ packed, ReadCounters& rc,
                                                 const int n_strands, uint64_t* dq, const SearchOut<HitT>& out) {
     const int k = ix.k;
     const idx_t N = ix.n_nodes;
+#if defined(__CUDACC__) && !defined(FIN_EMU)
+    const bool leader = G == 1 || coop_sub<G>() == 0;
+#else
+    const bool leader = true;
+#endif
 
     // ---- A: extend both intervals with the current character (common.hh:114-143).  ST_EXTK = the finimizer
     //         interval is already extended, only the k-mer interval is being contracted and retried.
@@ -471,8 +495,26 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
         }
         const bool both = st == ST_EXT;
         // all four ranks at once (the k-mer interval speculatively: unused when it follows I)
-        const Ival JI = extend(ix, I, c);
-        const Ival JK = extend(ix, Ik, c);
+        Ival JI, JK;
+#if defined(__CUDACC__) && !defined(FIN_EMU)
+        if (G > 1) {  // one rank row per lane of the group, results exchanged
+            const unsigned sub = coop_sub<G>();
+            const idx_t pos[4] = {I.l, I.r + 1, Ik.l, Ik.r + 1};
+            idx_t r[4];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int owner = q % G;
+                const idx_t v = (int)sub == owner ? step_c(ix, pos[q], c) : 0u;
+                r[q] = coop_u32<G>(true, v, owner);
+            }
+            JI.l = r[0]; JI.r = r[1] - 1;
+            JK.l = r[2]; JK.r = r[3] - 1;
+        } else
+#endif
+        {
+            JI = extend(ix, I, c);
+            JK = extend(ix, Ik, c);
+        }
         if (COUNT && both) rc.c_rank += 2;
         if (both && is_empty(JI)) {         // :116-126 contract the finimizer interval from the left and retry
             kmer_start = ++start;
@@ -539,11 +581,31 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
         const idx_t il = I.l, ir = I.r + 1, kl = Ik.l, kr = Ik.r + 1;
         uint32_t uw = 0;
         uint64_t w_il = 0, w_ir = 0, w_kl = 0, w_kr = 0;
-        if (single) uw = __ldg(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
-        if (pendI & kDropLeft) w_il = __ldg(lw + lcs_word_index(il));
-        if (pendI & kDropRight) w_ir = __ldg(lw + lcs_word_index(ir));
-        if (pendK & kDropLeft) w_kl = __ldg(lw + lcs_word_index(kl));
-        if (pendK & kDropRight) w_kr = __ldg(lw + lcs_word_index(kr));
+#if defined(__CUDACC__) && !defined(FIN_EMU)
+        if (G > 1) {  // the five loads of the phase dealt out over the lanes of the group
+            const int sub = (int)coop_sub<G>();
+            const bool c_il = pendI & kDropLeft, c_ir = pendI & kDropRight, c_kl = pendK & kDropLeft, c_kr = pendK & kDropRight;
+            uint32_t m_uw = 0;
+            uint64_t m_il = 0, m_ir = 0, m_kl = 0, m_kr = 0;
+            if (single && sub == 0) m_uw = __ldg(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
+            if (c_il && sub == 0 % G) m_il = __ldg(lw + lcs_word_index(il));
+            if (c_ir && sub == 1 % G) m_ir = __ldg(lw + lcs_word_index(ir));
+            if (c_kl && sub == 2 % G) m_kl = __ldg(lw + lcs_word_index(kl));
+            if (c_kr && sub == 3 % G) m_kr = __ldg(lw + lcs_word_index(kr));
+            uw = coop_u32<G>(single, m_uw, 0);
+            w_il = coop_u64<G>(c_il, m_il, 0 % G);
+            w_ir = coop_u64<G>(c_ir, m_ir, 1 % G);
+            w_kl = coop_u64<G>(c_kl, m_kl, 2 % G);
+            w_kr = coop_u64<G>(c_kr, m_kr, 3 % G);
+        } else
+#endif
+        {
+            if (single) uw = __ldg(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
+            if (pendI & kDropLeft) w_il = __ldg(lw + lcs_word_index(il));
+            if (pendI & kDropRight) w_ir = __ldg(lw + lcs_word_index(ir));
+            if (pendK & kDropLeft) w_kl = __ldg(lw + lcs_word_index(kl));
+            if (pendK & kDropRight) w_kr = __ldg(lw + lcs_word_index(kr));
+        }
         if (single) {
             if (COUNT) rc.c_ustart++;
             if ((uw >> (ucol & 31)) & 1u) {
@@ -695,12 +757,12 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
             if (strand == 0) {
                 fm |= (uint32_t)hit << (j & 31);
                 if ((j & 31) == 31 && j != nk - 1) {  // the last word stays in the register for the reverse strand
-                    out.fmask[fmw + (uint32_t)(j >> 5)] = fm;
+                    if (leader) out.fmask[fmw + (uint32_t)(j >> 5)] = fm;
                     fm = 0;
                 }
             } else {
                 take = hit && !((fm >> (i & 31)) & 1u);
-                if ((i & 31) == 0 && i > 0 && (sflags & kStrandFwd)) fm = out.fmask[fmw + (uint32_t)(i >> 5) - 1u];
+                if ((i & 31) == 0 && i > 0 && (sflags & kStrandFwd)) fm = out.fmask[fmw + (uint32_t)(i >> 5) - 1u];  // G > 1: written by the leader long ago (a strand earlier)
             }
             rc.found[0] += hit && strand == 0 ? 1u : 0u;
             rc.found[1] += hit && strand != 0 ? 1u : 0u;
@@ -711,7 +773,7 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
                 h.unitig = take ? (HitT)walk_uid : (HitT)-1;
                 h.pos = take ? (HitT)pos : (HitT)-1;
                 // the first streamed strand writes every position, the reverse strand after a forward one only its own hits
-                if (strand == 0 || take || !(sflags & kStrandFwd)) o[i] = h;
+                if ((strand == 0 || take || !(sflags & kStrandFwd)) && leader) o[i] = h;
             } else {
                 const bool cont = take && walked && run_len > 0;
                 if (run_len > 0 && !cont) {  // the open run ended at the previous position j - 1
@@ -761,27 +823,29 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS>::step(const IndexView& ix, const uint6
 #ifndef FIN_SEARCH_MIN_BLOCKS
 #define FIN_SEARCH_MIN_BLOCKS 8  // 64 registers; 10 and 12 blocks spill and lose 4-30 % (profiles/r1_sweep_occupancy.log)
 #endif
-template <int KCAP, class HitT, bool COUNT, bool RUNS>
+template <int KCAP, class HitT, bool COUNT, bool RUNS, int G = 1>
 __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) search_reads_kernel(const IndexView ix, const uint64_t* __restrict__ packed,
                                                            const uint64_t* __restrict__ read_offsets, const uint64_t n_reads,
                                                            const SearchOut<HitT> out, SearchTotals* __restrict__ totals,
                                                            const int n_strands) {
     const unsigned full = 0xFFFFFFFFu;
     const unsigned lane = threadIdx.x & 31u;
-    Chain<KCAP, HitT, COUNT, RUNS> ch;
+    const bool leader = (lane & (unsigned)(G - 1)) == 0;  // first lane of its group of G (G = 1: every lane)
+    Chain<KCAP, HitT, COUNT, RUNS, G> ch;
     uint64_t dq[KCAP];
     ReadCounters rc;
     bool dry = false;  // the counter ran past the last read
     while (true) {
         const bool want = ch.st == ST_IDLE && !dry;
-        const unsigned m = __ballot_sync(full, want);
+        const unsigned m = __ballot_sync(full, want && leader);  // one read per group
         if (m) {
-            const int leader = __ffs((int)m) - 1;
+            const int first = __ffs((int)m) - 1;
             unsigned long long base = 0;
-            if ((int)lane == leader) base = atomicAdd(&totals->next_read, (unsigned long long)__popc(m));
-            base = __shfl_sync(full, base, leader);
+            if ((int)lane == first) base = atomicAdd(&totals->next_read, (unsigned long long)__popc(m));
+            base = __shfl_sync(full, base, first);
+            const unsigned my_leader = lane & ~(unsigned)(G - 1);
+            const uint64_t rid = base + (uint64_t)__popc(m & ((1u << my_leader) - 1u));  // the same value on the G lanes of a group
             if (want) {
-                const uint64_t rid = base + (uint64_t)__popc(m & ((1u << lane) - 1u));
                 if (rid < n_reads) {
                     const uint64_t b0 = __ldg(read_offsets + rid);
                     const uint64_t len64 = __ldg(read_offsets + rid + 1) - b0;
@@ -796,6 +860,11 @@ __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) sea
             continue;
         }
         ch.step(ix, packed, rc, n_strands, dq, out);
+    }
+    if (!leader) {  // the replicas tallied the same things as their leader
+        const unsigned err = rc.err;
+        rc = ReadCounters();
+        rc.err = err;
     }
 
     // ---- per-warp reduction of the counters, one atomic per warp and counter
