@@ -411,13 +411,19 @@ uint64_t DeviceIndex::search_device_runs(const void* d_seqs, const uint64_t* d_r
 // -------------------------------------------------------------------------------------------------------
 // Dense hits: 8 bytes per k-mer leave over PCIe, so small sub-batches (the copies of one hide behind the kernels of
 // the next).  Runs: the copies are small and what counts is the tail of every persistent kernel (a lane owns a read
-// for ~2.5 ms at 150 bp), so few, large sub-batches.  FIN_SUB_READS / FIN_SUB_MBASES override both (experiments).
+// for ~2.5 ms at 150 bp; every extra sub-batch costs 3-4 ms, profiles/r2_sweep_runs_subbatch.log), so few sub-batches that
+// double from 512 k to 4 M reads.  FIN_SUB_FIRST / FIN_SUB_CAP (runs), FIN_SUB_READS / FIN_SUB_MBASES (both) override.
 struct SubBatchLimits {
     uint64_t reads, bases;
 };
 static SubBatchLimits sub_batch_limits(bool runs, int turn) {
-    // runs: sub-batches double from 256 k reads to 2 M, so that the first copy-in (which nothing hides) stays short
-    SubBatchLimits l = runs ? SubBatchLimits{std::min<uint64_t>(1ull << 21, (1ull << 18) << std::min(turn, 8)), 384ull << 20}
+    // runs: sub-batches double, so that the first copy-in (which nothing hides) stays short
+    uint64_t first = 1ull << 19, cap = 1ull << 22;
+    if (runs) {
+        if (const char* e = getenv("FIN_SUB_FIRST")) if (atoll(e) > 0) first = (uint64_t)atoll(e);
+        if (const char* e = getenv("FIN_SUB_CAP")) if (atoll(e) > 0) cap = (uint64_t)atoll(e);
+    }
+    SubBatchLimits l = runs ? SubBatchLimits{std::min<uint64_t>(cap, first << std::min(turn, 8)), cap * 192}
                             : SubBatchLimits{1ull << 19, 48ull << 20};
     if (const char* e = getenv("FIN_SUB_READS")) if (atoll(e) > 0) l.reads = (uint64_t)atoll(e);
     if (const char* e = getenv("FIN_SUB_MBASES")) if (atoll(e) > 0) l.bases = (uint64_t)atoll(e) << 20;
@@ -639,7 +645,7 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
         turn++;
         if (s.busy) FIN_CUDA(cudaEventSynchronize(s.done));  // its phase B was issued two turns ago
         s.busy = false;
-        ensure_runs(s, nkm / 16 + 4096);
+        ensure_runs(s, nkm / 32 + 4096);  // ~4 runs per 150 bp read; more than that is searched again with the exact room
         stage_sub_batch(view_, s, seqs, read_offsets, r0, r1, nkm);
         launch_a(s);
         s.busy = true;
