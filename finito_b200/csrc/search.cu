@@ -22,6 +22,8 @@ thread_local uint64_t g_launches = 0;
 // -------------------------------------------------------------------------------------------------------
 struct SearchSlot {
     cudaStream_t stream = nullptr;
+    cudaStream_t prep_stream = nullptr;             // copy-in + packing + prefilter of the runs pipeline (high priority)
+    cudaEvent_t prepped = nullptr;
     cudaEvent_t counted = nullptr, done = nullptr;  // kernels + totals copy finished / everything finished
     DevBuf<uint8_t> ascii, scan_tmp, sort_tmp, strand_flags;
     DevBuf<uint64_t> packed, offsets, out_offsets;
@@ -38,6 +40,8 @@ struct SearchSlot {
     uint64_t r0 = 0, nr = 0, nb = 0, nkm = 0, base0 = 0;
     ~SearchSlot() {
         if (stream) cudaStreamDestroy(stream);
+        if (prep_stream) cudaStreamDestroy(prep_stream);
+        if (prepped) cudaEventDestroy(prepped);
         if (counted) cudaEventDestroy(counted);
         if (done) cudaEventDestroy(done);
         if (h_totals) cudaFreeHost(h_totals);
@@ -192,6 +196,7 @@ struct PipelineOut {
     void* d_hits = nullptr;
     uint32_t* d_fmask = nullptr;
     uint8_t* d_strand_flags = nullptr;  // n_reads bytes when the index has a strand prefilter
+    bool filter_done = false;           // the strand prefilter of this batch was already launched (launch_filter)
     RunSink sink{nullptr, nullptr, nullptr, 0};
 };
 
@@ -211,29 +216,37 @@ static void launch_prepare(const IndexView& v, const uint8_t* d_ascii, uint64_t 
     g_launches += 2;
 }
 
+// the strand prefilter of a batch (runs mode: hit_bytes 0, nothing to fill; dense: the reads no strand of which is streamed
+// get their (-1,-1) here)
+static void launch_filter(const IndexView& v, const uint64_t* d_packed, const uint64_t* d_offsets, uint64_t n_reads,
+                          const uint64_t* d_out_offsets, const PipelineOut& po, SearchTotals* d_totals, bool count, int n_strands,
+                          cudaStream_t st) {
+    if (n_reads == 0 || !v.smer || !po.d_strand_flags) return;
+    const unsigned ft = 128, fb = (unsigned)((n_reads + ft - 1) / ft);
+    if (po.hit_bytes == 8)
+        strand_filter_kernel<int64_t><<<fb, ft, 0, st>>>(v, d_packed, d_offsets, n_reads, n_strands, po.d_strand_flags, d_out_offsets,
+                                                         reinterpret_cast<HitPair<int64_t>*>(po.d_hits), count ? d_totals : nullptr);
+    else
+        strand_filter_kernel<int32_t><<<fb, ft, 0, st>>>(v, d_packed, d_offsets, n_reads, n_strands, po.d_strand_flags, d_out_offsets,
+                                                         po.hit_bytes == 4 ? reinterpret_cast<HitPair<int32_t>*>(po.d_hits) : nullptr,
+                                                         count ? d_totals : nullptr);
+    g_launches++;
+    FIN_CUDA(cudaGetLastError());
+}
+
 static void launch_search(const IndexView& v, const uint64_t* d_packed, const uint64_t* d_offsets, uint64_t n_reads,
                           const uint64_t* d_out_offsets, const PipelineOut& po, SearchTotals* d_totals, bool count, int n_strands,
                           cudaStream_t st) {
     if (n_reads == 0) return;
     const uint8_t* sf = v.smer ? po.d_strand_flags : nullptr;
-    const unsigned ft = 128, fb = (unsigned)((n_reads + ft - 1) / ft);
+    if (!po.filter_done) launch_filter(v, d_packed, d_offsets, n_reads, d_out_offsets, po, d_totals, count, n_strands, st);
     if (po.hit_bytes == 8) {
         SearchOut<int64_t> out{reinterpret_cast<HitPair<int64_t>*>(po.d_hits), d_out_offsets, po.d_fmask, po.sink, sf};
-        if (sf) {
-            strand_filter_kernel<int64_t><<<fb, ft, 0, st>>>(v, d_packed, d_offsets, n_reads, n_strands, po.d_strand_flags, d_out_offsets, out.hits,
-                                                             count ? d_totals : nullptr);
-            g_launches++;
-        }
         if (count) launch_search_t<int64_t, true, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
         else launch_search_t<int64_t, false, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
         return;
     }
     SearchOut<int32_t> out{reinterpret_cast<HitPair<int32_t>*>(po.d_hits), d_out_offsets, po.d_fmask, po.sink, sf};
-    if (sf) {
-        strand_filter_kernel<int32_t><<<fb, ft, 0, st>>>(v, d_packed, d_offsets, n_reads, n_strands, po.d_strand_flags, d_out_offsets,
-                                                         po.hit_bytes == 4 ? out.hits : nullptr, count ? d_totals : nullptr);
-        g_launches++;
-    }
     if (po.hit_bytes == 4) {
         if (count) launch_search_t<int32_t, true, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
         else launch_search_t<int32_t, false, false>(v, d_packed, d_offsets, n_reads, out, d_totals, n_strands, st);
@@ -429,13 +442,17 @@ static SubBatchLimits sub_batch_limits(bool runs, int turn) {
     if (const char* e = getenv("FIN_SUB_MBASES")) if (atoll(e) > 0) l.bases = (uint64_t)atoll(e) << 20;
     return l;
 }
-static constexpr int kSlots = 3;
+static constexpr int kSlots = 4;
 
 void DeviceIndex::ensure_slots() {
     if (slots_.empty()) {
         for (int i = 0; i < kSlots; i++) {
             std::unique_ptr<SearchSlot> s(new SearchSlot());
             FIN_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+            int lo_prio = 0, hi_prio = 0;
+            FIN_CUDA(cudaDeviceGetStreamPriorityRange(&lo_prio, &hi_prio));
+            FIN_CUDA(cudaStreamCreateWithPriority(&s->prep_stream, cudaStreamNonBlocking, hi_prio));
+            FIN_CUDA(cudaEventCreateWithFlags(&s->prepped, cudaEventDisableTiming));
             FIN_CUDA(cudaEventCreateWithFlags(&s->counted, cudaEventDisableTiming));
             FIN_CUDA(cudaEventCreateWithFlags(&s->done, cudaEventDisableTiming));
             FIN_CUDA(cudaHostAlloc((void**)&s->h_totals, sizeof(SearchTotals), cudaHostAllocDefault));
@@ -446,7 +463,10 @@ void DeviceIndex::ensure_slots() {
     // a previous call that ended with an exception may have left sub-batches in flight: let them finish and forget them,
     // so that their copies no longer write into the caller's buffers and their totals never reach this call's counters
     for (auto& s : slots_) {
-        if (s->busy) cudaStreamSynchronize(s->stream);
+        if (s->busy) {
+            cudaStreamSynchronize(s->prep_stream);
+            cudaStreamSynchronize(s->stream);
+        }
         s->busy = false;
     }
 }
@@ -458,7 +478,10 @@ struct SlotDrain {
     ~SlotDrain() {
         if (!armed) return;
         for (auto& s : slots) {
-            if (s->busy) cudaStreamSynchronize(s->stream);
+            if (s->busy) {
+                cudaStreamSynchronize(s->prep_stream);
+                cudaStreamSynchronize(s->stream);
+            }
             s->busy = false;
         }
     }
@@ -491,7 +514,7 @@ static uint64_t cut_sub_batch(const uint64_t* read_offsets, uint64_t n_reads, ui
 
 // H2D of a sub-batch and its preparation kernels on the slot's stream
 static void stage_sub_batch(const IndexView& v, SearchSlot& s, const char* seqs, const uint64_t* read_offsets, uint64_t r0, uint64_t r1,
-                            uint64_t nkm) {
+                            uint64_t nkm, cudaStream_t st) {
     NvtxRange range("fin:search:stage_sub_batch");
     const uint64_t base0 = read_offsets[r0];
     const uint64_t nr = r1 - r0, nb = read_offsets[r1] - base0;
@@ -511,10 +534,10 @@ static void stage_sub_batch(const IndexView& v, SearchSlot& s, const char* seqs,
         FIN_CUDA(cudaHostAlloc((void**)&s.h_offsets_pinned, s.h_offsets_cap * 8, cudaHostAllocDefault));
     }
     for (uint64_t i = 0; i <= nr; i++) s.h_offsets_pinned[i] = read_offsets[r0 + i] - base0;
-    FIN_CUDA(cudaMemsetAsync(s.totals.p, 0, sizeof(SearchTotals), s.stream));
-    FIN_CUDA(cudaMemcpyAsync(s.ascii.p, seqs + base0, nb, cudaMemcpyHostToDevice, s.stream));
-    FIN_CUDA(cudaMemcpyAsync(s.offsets.p, s.h_offsets_pinned, (nr + 1) * 8, cudaMemcpyHostToDevice, s.stream));
-    launch_prepare(v, s.ascii.p, nb, s.offsets.p, nr, s.packed.p, s.out_offsets.p, s.scan_tmp.p, tmp, (SearchTotals*)s.totals.p, s.stream);
+    FIN_CUDA(cudaMemsetAsync(s.totals.p, 0, sizeof(SearchTotals), st));
+    FIN_CUDA(cudaMemcpyAsync(s.ascii.p, seqs + base0, nb, cudaMemcpyHostToDevice, st));
+    FIN_CUDA(cudaMemcpyAsync(s.offsets.p, s.h_offsets_pinned, (nr + 1) * 8, cudaMemcpyHostToDevice, st));
+    launch_prepare(v, s.ascii.p, nb, s.offsets.p, nr, s.packed.p, s.out_offsets.p, s.scan_tmp.p, tmp, (SearchTotals*)s.totals.p, st);
 }
 
 template <class HitT>
@@ -550,7 +573,7 @@ void DeviceIndex::search_host(const char* seqs, const uint64_t* read_offsets, ui
         turn++;
         retire(s);
         s.hits.ensure(std::max<uint64_t>(nkm, 1) * 2 * sizeof(HitT));
-        stage_sub_batch(view_, s, seqs, read_offsets, r0, r1, nkm);
+        stage_sub_batch(view_, s, seqs, read_offsets, r0, r1, nkm, s.stream);
         PipelineOut po;
         po.hit_bytes = (int)sizeof(HitT);
         po.d_hits = s.hits.p;
@@ -575,9 +598,15 @@ template void DeviceIndex::search_host<int32_t>(const char*, const uint64_t*, ui
 template void DeviceIndex::search_host<int64_t>(const char*, const uint64_t*, uint64_t, int64_t*, uint64_t, fin_search_counts*, int);
 
 // -------------------------------------------------------------------------------------------------------
-// host batch, answers as runs.  Per sub-batch: (A) copy in, pack, search -> appended records + their count;
-// (B) once the count is on the host: sort by (read, first k-mer), CSR offsets, copy out.  B of sub-batch i is
-// issued after A of sub-batch i+1, so the GPU always has the next search queued while the host waits for a count.
+// host batch, answers as runs.  Per sub-batch t:
+//   stage(t)  on the slot's high-priority prep stream: copy in, pack, offsets, strand prefilter        -> event prepped
+//   search(t) on the slot's stream, after prepped(t): the persistent search kernel, totals to the host -> event counted
+//   finish(t) once the record count is on the host: sort by (read, first k-mer), CSR offsets, copy out -> event done
+// A persistent search kernel owns every SM until its last blocks retire, so whatever else has to run before the next
+// search kernel runs in that tail.  stage(t+1) is therefore issued BEFORE search(t): its copy-in overlaps search(t-1) and
+// its small kernels take the first SM slots that search(t-1) frees (stream priority), while search(t) - whose own staging
+// finished a whole sub-batch earlier - fills the rest of the tail.  finish(t-1) is issued after search(t), so the GPU
+// always has the next search queued while the host waits for a count.
 // -------------------------------------------------------------------------------------------------------
 uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_offsets, uint64_t n_reads, uint64_t* run_offsets,
                                        fin_run* runs, uint64_t runs_capacity, fin_search_counts* counts) {
@@ -590,34 +619,52 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
     unsigned flags = 0;
     uint64_t run_pos = 0;
 
-    auto launch_a = [&](SearchSlot& s) {
-        PipelineOut po;
-        po.hit_bytes = 0;
-        po.d_fmask = s.fmask.p;
-        po.d_strand_flags = s.strand_flags.p;
-        SearchTotals* dt = (SearchTotals*)s.totals.p;
-        po.sink = RunSink{s.keys_a.p, s.recs_a.p, &dt->n_runs, std::min<uint64_t>(s.keys_a.n, s.recs_a.n)};
-        launch_search(view_, s.packed.p, s.offsets.p, s.nr, s.out_offsets.p, po, dt, count_accesses, 2, s.stream);
-        FIN_CUDA(cudaMemcpyAsync(s.h_totals, s.totals.p, sizeof(SearchTotals), cudaMemcpyDeviceToHost, s.stream));
-        FIN_CUDA(cudaEventRecord(s.counted, s.stream));
-    };
     auto ensure_runs = [&](SearchSlot& s, uint64_t n) {
         s.keys_a.ensure(n);
         s.keys_b.ensure(n);
         s.recs_a.ensure(n);
         s.recs_b.ensure(n);
     };
-    auto phase_b = [&](SearchSlot& s) {
+    auto pipeline_out = [&](SearchSlot& s) {
+        PipelineOut po;
+        po.hit_bytes = 0;
+        po.d_fmask = s.fmask.p;
+        po.d_strand_flags = s.strand_flags.p;
+        po.filter_done = true;
+        po.sink = RunSink{s.keys_a.p, s.recs_a.p, &((SearchTotals*)s.totals.p)->n_runs, std::min<uint64_t>(s.keys_a.n, s.recs_a.n)};
+        return po;
+    };
+    auto stage = [&](SearchSlot& s, uint64_t r0, uint64_t r1, uint64_t nkm) {
+        if (s.busy) FIN_CUDA(cudaEventSynchronize(s.done));  // its previous sub-batch was finished kSlots - 1 turns ago
+        s.busy = false;
+        ensure_runs(s, nkm / 32 + 4096);  // ~4 runs per 150 bp read; more than that is searched again with the exact room
+        stage_sub_batch(view_, s, seqs, read_offsets, r0, r1, nkm, s.prep_stream);
+        launch_filter(view_, s.packed.p, s.offsets.p, s.nr, s.out_offsets.p, pipeline_out(s), (SearchTotals*)s.totals.p, count_accesses, 2,
+                      s.prep_stream);
+        FIN_CUDA(cudaEventRecord(s.prepped, s.prep_stream));
+        s.busy = true;
+    };
+    auto search = [&](SearchSlot& s) {
+        FIN_CUDA(cudaStreamWaitEvent(s.stream, s.prepped, 0));
+        launch_search(view_, s.packed.p, s.offsets.p, s.nr, s.out_offsets.p, pipeline_out(s), (SearchTotals*)s.totals.p, count_accesses, 2,
+                      s.stream);
+        FIN_CUDA(cudaMemcpyAsync(s.h_totals, s.totals.p, sizeof(SearchTotals), cudaMemcpyDeviceToHost, s.stream));
+        FIN_CUDA(cudaEventRecord(s.counted, s.stream));
+    };
+    auto finish = [&](SearchSlot& s) {
         NvtxRange range("fin:search:runs_sort_and_copy_out");
         FIN_CUDA(cudaEventSynchronize(s.counted));
         uint64_t n = s.h_totals->n_runs;
         if (n > std::min<uint64_t>(s.keys_a.n, s.recs_a.n)) {  // more runs than the slot had room for: search again with enough
-            flags |= s.h_totals->error_flags;
+            const unsigned first_flags = s.h_totals->error_flags;  // what packing and the offset check found
             FIN_CUDA(cudaStreamSynchronize(s.stream));
             ensure_runs(s, n + n / 8 + 1024);
-            FIN_CUDA(cudaMemsetAsync(s.totals.p, 0, sizeof(SearchTotals), s.stream));
-            launch_a(s);
-            FIN_CUDA(cudaEventSynchronize(s.counted));
+            SearchTotals* dt = (SearchTotals*)s.totals.p;
+            FIN_CUDA(cudaMemsetAsync(&dt->found_fwd, 0, sizeof(SearchTotals), s.stream));
+            launch_search(view_, s.packed.p, s.offsets.p, s.nr, s.out_offsets.p, pipeline_out(s), dt, false, 2, s.stream);
+            FIN_CUDA(cudaMemcpyAsync(s.h_totals, s.totals.p, sizeof(SearchTotals), cudaMemcpyDeviceToHost, s.stream));
+            FIN_CUDA(cudaStreamSynchronize(s.stream));
+            flags |= first_flags;
             n = s.h_totals->n_runs;
         }
         flags |= s.h_totals->error_flags;
@@ -634,26 +681,34 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
     };
 
     if (n_reads == 0) run_offsets[0] = 0;
-    uint64_t r0 = 0, max_len = 0;
-    int turn = 0;
+    // the sub-batch plan of the call (offsets validated, k-mer positions counted) is made as it goes: cut(t+1) while the GPU works
+    uint64_t next_r0 = 0, max_len = 0;
+    int planned = 0;
+    auto cut_next = [&](uint64_t& r0, uint64_t& r1, uint64_t& nkm) {
+        if (next_r0 >= n_reads) return false;
+        r0 = next_r0;
+        r1 = cut_sub_batch(read_offsets, n_reads, r0, k, sub_batch_limits(true, planned), nkm, max_len);
+        next_r0 = r1;
+        planned++;
+        return true;
+    };
+    uint64_t r0 = 0, r1 = 0, nkm = 0;
+    int t = 0;
     SearchSlot* prev = nullptr;
-    while (r0 < n_reads) {
-        const SubBatchLimits lim = sub_batch_limits(true, turn);
-        uint64_t nkm = 0;
-        const uint64_t r1 = cut_sub_batch(read_offsets, n_reads, r0, k, lim, nkm, max_len);
-        SearchSlot& s = *slots_[turn % kSlots];
-        turn++;
-        if (s.busy) FIN_CUDA(cudaEventSynchronize(s.done));  // its phase B was issued two turns ago
-        s.busy = false;
-        ensure_runs(s, nkm / 32 + 4096);  // ~4 runs per 150 bp read; more than that is searched again with the exact room
-        stage_sub_batch(view_, s, seqs, read_offsets, r0, r1, nkm);
-        launch_a(s);
-        s.busy = true;
-        if (prev) phase_b(*prev);
-        prev = &s;
-        r0 = r1;
+    bool have = cut_next(r0, r1, nkm);
+    if (have) stage(*slots_[0], r0, r1, nkm);
+    while (have) {
+        SearchSlot& cur = *slots_[t % kSlots];
+        uint64_t a0 = 0, a1 = 0, akm = 0;
+        const bool more = cut_next(a0, a1, akm);
+        if (more) stage(*slots_[(t + 1) % kSlots], a0, a1, akm);  // before search(t): see the note above
+        search(cur);
+        if (prev) finish(*prev);
+        prev = &cur;
+        have = more;
+        t++;
     }
-    if (prev) phase_b(*prev);
+    if (prev) finish(*prev);
     for (auto& s : slots_) {
         if (s->busy) FIN_CUDA(cudaEventSynchronize(s->done));
         s->busy = false;
