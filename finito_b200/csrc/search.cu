@@ -2,6 +2,7 @@
 // host buffers -> H2D -> pack -> search -> D2H that stands in for run_fmin_queries_streaming
 // (include/search_fmin.hh:33-84) minus the text formatting, which stays on the host (cli_main.cpp).
 #include <algorithm>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 
@@ -635,8 +636,10 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
         return po;
     };
     auto stage = [&](SearchSlot& s, uint64_t r0, uint64_t r1, uint64_t nkm) {
-        if (s.busy) FIN_CUDA(cudaEventSynchronize(s.done));  // its previous sub-batch was finished kSlots - 1 turns ago
-        s.busy = false;
+        // The slot's previous sub-batch was searched and its finish() issued kSlots - 1 turns ago: the staging buffers are
+        // free (the host saw `counted`), and what finish() still reads (the appended records) is only written again by
+        // the next search on the slot's own stream, i.e. behind it.  No wait on `done` here: the sort of finish() sits
+        // behind the running persistent kernel and would stall the host for a whole sub-batch.
         ensure_runs(s, nkm / 32 + 4096);  // ~4 runs per 150 bp read; more than that is searched again with the exact room
         stage_sub_batch(view_, s, seqs, read_offsets, r0, r1, nkm, s.prep_stream);
         launch_filter(view_, s.packed.p, s.offsets.p, s.nr, s.out_offsets.p, pipeline_out(s), (SearchTotals*)s.totals.p, count_accesses, 2,
@@ -651,9 +654,15 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
         FIN_CUDA(cudaMemcpyAsync(s.h_totals, s.totals.p, sizeof(SearchTotals), cudaMemcpyDeviceToHost, s.stream));
         FIN_CUDA(cudaEventRecord(s.counted, s.stream));
     };
+    static const bool trace = getenv("FIN_TRACE") != nullptr;
+    const auto t_enter = std::chrono::steady_clock::now();
+    auto since = [&] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_enter).count(); };
     auto finish = [&](SearchSlot& s) {
         NvtxRange range("fin:search:runs_sort_and_copy_out");
+        const double w0 = since();
         FIN_CUDA(cudaEventSynchronize(s.counted));
+        if (trace) fprintf(stderr, "[fin trace] finish r0=%llu nr=%llu: waited %.2f ms for the count (at %.2f ms)\n", (unsigned long long)s.r0,
+                           (unsigned long long)s.nr, since() - w0, since());
         uint64_t n = s.h_totals->n_runs;
         if (n > std::min<uint64_t>(s.keys_a.n, s.recs_a.n)) {  // more runs than the slot had room for: search again with enough
             const unsigned first_flags = s.h_totals->error_flags;  // what packing and the offset check found
@@ -701,8 +710,11 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
         SearchSlot& cur = *slots_[t % kSlots];
         uint64_t a0 = 0, a1 = 0, akm = 0;
         const bool more = cut_next(a0, a1, akm);
+        const double s0 = since();
         if (more) stage(*slots_[(t + 1) % kSlots], a0, a1, akm);  // before search(t): see the note above
+        const double s1 = since();
         search(cur);
+        if (trace) fprintf(stderr, "[fin trace] t=%d: stage(t+1) %.2f ms on the host, search(t) enqueued at %.2f ms\n", t, s1 - s0, since());
         if (prev) finish(*prev);
         prev = &cur;
         have = more;
@@ -714,6 +726,7 @@ uint64_t DeviceIndex::search_host_runs(const char* seqs, const uint64_t* read_of
         s->busy = false;
     }
     drain.armed = false;
+    if (trace) fprintf(stderr, "[fin trace] done at %.2f ms\n", since());
     check_flags(flags);
     if (counts) *counts = c;
     return run_pos;
