@@ -41,7 +41,9 @@ inline SeqFormat sequence_file_format(std::string name) {  // SBWT/src/SeqIO.cpp
 // memory stays O(batch) however large the input is (the reference streams one read at a time, search_fmin.hh:43-72).
 class SeqReader {
    public:
-    explicit SeqReader(const std::string& path) : path_(path), fmt_(sequence_file_format(path)) {
+    // chunk_bytes: how much is read (or inflated) per refill; tests use tiny chunks to put every boundary case on a record
+    explicit SeqReader(const std::string& path, size_t chunk_bytes = 16u << 20)
+        : path_(path), fmt_(sequence_file_format(path)), kChunk(std::max<size_t>(chunk_bytes, 16)) {
         if (has_suffix(path, ".gz")) {  // the reference decides by the extension too (SeqIO.cpp:19-52)
             gz_ = gzopen(path.c_str(), "rb");
             if (!gz_) throw io_error("Error opening file " + path);
@@ -88,7 +90,6 @@ class SeqReader {
     }
 
    private:
-    static constexpr size_t kChunk = 16u << 20;
 
     void fill() {  // keeps [pos_, end_), reads more behind it
         if (pos_ > 0) {
@@ -119,18 +120,26 @@ class SeqReader {
         if (pos_ >= end_) return false;
         const char* b = buf_.data();
         if (fmt_ == SeqFormat::Fasta) {  // up to the next '>' at the start of a line
-            size_t q = std::max(scan_, pos_ + 1);
+            size_t q = std::max(scan_, pos_ + 1);  // scan_: no record start before it (kept across refills)
             while (q < end_) {
                 const char* nl = static_cast<const char*>(memchr(b + q, '\n', end_ - q));
-                if (!nl) break;
-                q = (size_t)(nl - b) + 1;
-                if (q < end_ && b[q] == '>') {
-                    rec_end = q;
-                    scan_ = q;
+                if (!nl) {
+                    scan_ = end_;
+                    return false;
+                }
+                const size_t after = (size_t)(nl - b) + 1;
+                if (after >= end_) {  // the first character of the next line is not in the buffer yet: look at this newline again
+                    scan_ = (size_t)(nl - b);
+                    return false;
+                }
+                if (b[after] == '>') {
+                    rec_end = after;
+                    scan_ = after;
                     return true;
                 }
+                q = after;
             }
-            scan_ = q;  // everything before q holds no record start
+            scan_ = std::max(scan_, std::min(q, end_));
             return false;
         }
         size_t q = pos_;  // FASTQ: four lines
@@ -179,6 +188,7 @@ class SeqReader {
 
     std::string path_;
     SeqFormat fmt_;
+    size_t kChunk;
     gzFile gz_ = nullptr;
     FILE* f_ = nullptr;
     std::vector<char> buf_;

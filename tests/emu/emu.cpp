@@ -292,6 +292,34 @@ int emu_search(const char* prefix, const char* seqs, const uint64_t* offs, uint6
     });
 }
 
+// the incremental FASTA/FASTQ(.gz) reader of the CLI and of build-fmin (seqio.hpp), batch by batch with the given limits and
+// refill size; returns the number of reads, the bases back to back in `seqs` (capacity cap) and n + 1 offsets
+int64_t emu_read_sequences(const char* path, uint64_t chunk_bytes, uint64_t max_reads, uint64_t max_bases, char* seqs, uint64_t cap,
+                           uint64_t* offsets, uint64_t offsets_cap, uint64_t* n_batches) {
+    int64_t n = -1;
+    guarded([&] {
+        SeqReader reader(path, (size_t)chunk_bytes);
+        uint64_t total = 0, reads = 0;
+        *n_batches = 0;
+        offsets[0] = 0;
+        for (;;) {
+            SeqBatch b;
+            if (!reader.next(b, max_reads, max_bases)) break;
+            (*n_batches)++;
+            if (b.size() > max_reads) throw arg_error("a batch holds more reads than asked for");
+            for (uint64_t i = 0; i < b.size(); i++) {
+                const uint64_t len = b.offsets[i + 1] - b.offsets[i];
+                if (total + len > cap || reads + 1 >= offsets_cap) throw arg_error("buffer too small");
+                memcpy(seqs + total, b.seqs.data() + b.offsets[i], len);
+                total += len;
+                offsets[++reads] = total;
+            }
+        }
+        n = (int64_t)reads;
+    });
+    return n;
+}
+
 int emu_lcs(const char* sbwt_path, int with_variant, uint8_t* out, uint64_t cap) {
     return guarded([&] {
         SbwtHost s = load_sbwt_file(sbwt_path, with_variant != 0);

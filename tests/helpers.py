@@ -133,6 +133,9 @@ def emu_lib() -> C.CDLL:
     lib.emu_search.argtypes = [C.c_char_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
                                C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p]
     lib.emu_lcs.argtypes = [C.c_char_p, C.c_int, C.c_void_p, C.c_uint64]
+    lib.emu_read_sequences.restype = C.c_int64
+    lib.emu_read_sequences.argtypes = [C.c_char_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                       C.c_void_p]
     lib.emu_build.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64]
     lib.emu_builder_open.restype = C.c_void_p
     lib.emu_builder_open.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, C.c_int]
@@ -174,6 +177,21 @@ def emu_search(prefix, seqs, offs, n_strands=2, runs=False, prefilter_s=0, strea
                       streamed.ctypes.data if streamed is not None else None):
         raise RuntimeError("emu: " + lib.emu_last_error().decode())
     return out, counts, dict(zip(COUNTER_NAMES[:8], (int(x) for x in access))), int(flags[0])
+
+
+def emu_read_sequences(path, chunk_bytes=16 << 20, max_reads=1 << 62, max_bases=1 << 62):
+    """The product's incremental sequence reader (finito_b200/csrc/seqio.hpp) -> (list of byte strings, number of batches)."""
+    lib = emu_lib()
+    cap = max(1024, 40 * os.path.getsize(path))  # gzip of a repetitive file can expand a lot
+    seqs = np.zeros(cap, dtype=np.uint8)
+    offs = np.zeros(cap // 2 + 2, dtype=np.uint64)
+    nb = np.zeros(1, dtype=np.uint64)
+    n = lib.emu_read_sequences(os.fsencode(path), chunk_bytes, max_reads, max_bases, seqs.ctypes.data, cap, offs.ctypes.data, len(offs),
+                               nb.ctypes.data)
+    if n < 0:
+        raise RuntimeError("emu: " + lib.emu_last_error().decode())
+    raw = seqs.tobytes()
+    return [raw[int(offs[i]):int(offs[i + 1])] for i in range(n)], int(nb[0])
 
 
 def emu_build(sbwt, unitigs, prefix, per_chunk=0):
