@@ -2,6 +2,7 @@
 // test-suite: unitig packing and permutation (PackedStrings.hh:36-64,104-137), the work plan of the
 // build stream, and the assembly of the index files (FinimizerIndex.hh:301-306, :187-207).
 #pragma once
+#include <thread>
 #include <algorithm>
 #include <numeric>
 
@@ -169,16 +170,29 @@ inline std::vector<uint64_t> tuples_per_owner(const uint64_t* tuples /* {colex, 
 }
 
 // global_offsets of the marked columns, packed at the width of the largest one (FinimizerIndex.hh:301-306)
-inline PackedVec pack_offsets(const std::vector<uint32_t>& offs) {
-    uint64_t max_off = 0;
-    for (uint32_t v : offs) max_off = std::max<uint64_t>(max_off, v);
+inline PackedVec pack_offsets(const uint32_t* offs, uint64_t n) {
+    // blocks of 64 entries start on a word boundary whatever the width: the blocks are packed by several threads
+    const unsigned T = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(16, n / (1u << 20)));
+    const uint64_t per = ((n + T - 1) / T + 63) / 64 * 64;
+    std::vector<uint64_t> maxes(T, 0);
+    auto each = [&](auto&& fn) {
+        std::vector<std::thread> pool;
+        for (unsigned t = 1; t < T; t++) pool.emplace_back(fn, t);
+        fn(0u);
+        for (auto& th : pool) th.join();
+    };
+    each([&](unsigned t) {
+        uint64_t m = 0;
+        for (uint64_t i = std::min(n, t * per), e = std::min(n, (t + 1) * per); i < e; i++) m = std::max<uint64_t>(m, offs[i]);
+        maxes[t] = m;
+    });
+    const uint64_t max_off = *std::max_element(maxes.begin(), maxes.end());
     PackedVec p;
     const int w = bit_length(max_off);
-    p.assign(offs.size(), (uint8_t)(w ? w : 1));
-    if (w == 0) {  // sdsl cannot hold width 0 either; only reachable with a single base of text
-        p.width = 1;
-    }
-    for (uint64_t i = 0; i < offs.size(); i++) p.put(i, offs[i]);
+    p.assign(n, (uint8_t)(w ? w : 1));  // sdsl cannot hold width 0 either; only reachable with a single base of text
+    each([&](unsigned t) {
+        for (uint64_t i = std::min(n, t * per), e = std::min(n, (t + 1) * per); i < e; i++) p.put(i, offs[i]);
+    });
     return p;
 }
 
@@ -209,7 +223,7 @@ inline void save_index_from_slices(SbwtHost&& sbwt, PackedVec&& lcs, PackedVec&&
     uint64_t ones = 0;
     for (uint64_t w = 0; w < need; w++) ones += (uint64_t)__builtin_popcountll(out.fmin.words[w]);
     if (ones != n_offsets) throw arg_error("build: the slices disagree on the number of finimizers");
-    out.offsets = pack_offsets(std::vector<uint32_t>(offsets_all, offsets_all + n_offsets));
+    out.offsets = pack_offsets(offsets_all, n_offsets);
     out.sbwt = std::move(sbwt);
     out.lcs = std::move(lcs);
     out.text = std::move(text);

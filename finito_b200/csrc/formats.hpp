@@ -147,7 +147,9 @@ struct SbwtHost {
     int64_t C[4] = {0, 0, 0, 0};
     PackedVec bits[4];                 // A, C, G, T rows of the subset matrix
     std::vector<int64_t> precalc;      // 2 * 4^precalc_k entries: inclusive interval per prefix, {-1,-1} when absent
-    std::vector<uint8_t> body;         // the serialized SBWT without the variant string, verbatim
+    std::vector<uint8_t> file;         // the whole file as read; the serialized SBWT without the variant string is
+    size_t body_off = 0, body_len = 0;  //   file[body_off, body_off + body_len), written verbatim as <prefix>.sbwt
+    const uint8_t* body() const { return file.data() + body_off; }
 };
 
 inline std::string read_len_string(Cursor& c) {  // SBWT/src/globals.cpp:56-62 load_string
@@ -185,7 +187,9 @@ inline SbwtHost load_sbwt_file(const std::string& path, bool with_variant) {
     for (int ch = 0; ch < 4; ch++)
         if ((int64_t)s.bits[ch].n_bits != s.n_nodes) throw format_error("bit vector length differs from n_nodes in " + path);
     if (s.k < 1 || s.k > 255) throw format_error("k out of range in " + path);
-    s.body.assign(body_begin, c.p);
+    s.body_off = (size_t)(body_begin - buf.data());
+    s.body_len = (size_t)(c.p - body_begin);
+    s.file = std::move(buf);  // no second copy of the (up to 2 GB) body
     return s;
 }
 

@@ -68,8 +68,8 @@ inline void save_index_files(const IndexHost& ix, const std::string& prefix) {  
         const std::string path = prefix + ".sbwt";
         FILE* f = fopen(path.c_str(), "wb");
         if (!f) throw io_error("cannot write " + path);
-        const size_t n = ix.sbwt.body.size();
-        const bool ok = fwrite(ix.sbwt.body.data(), 1, n, f) == n;
+        const size_t n = ix.sbwt.body_len;
+        const bool ok = fwrite(ix.sbwt.body(), 1, n, f) == n;
         if (fclose(f) != 0 || !ok) throw io_error("short write on " + path);
     };
     std::vector<std::function<void()>> jobs = {

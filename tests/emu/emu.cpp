@@ -377,7 +377,7 @@ int emu_build(const char* sbwt_path, const char* unitig_path, const char* out_pr
                 out.fmin.words[i >> 6] |= 1ULL << (i & 63);
                 offs.push_back(fmin_key_offset(table[i]));
             }
-        out.offsets = pack_offsets(offs);
+        out.offsets = pack_offsets(offs.data(), offs.size());
         text.words.resize(text.disk_words() + 1);
         out.sbwt = std::move(sbwt);
         out.lcs = std::move(lcs_file);
