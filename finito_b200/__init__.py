@@ -87,6 +87,8 @@ ABI = {
                                      C.POINTER(_Counts)]),
     "fin_search_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p,
                                     C.c_int, C.POINTER(_Counts), C.POINTER(C.c_float)]),
+    "fin_search_device_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p,
+                                            C.c_int, C.POINTER(_Counts)]),
     "fin_search_batch_runs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, _u64p,
                                         C.POINTER(_Counts)]),
     "fin_search_device_runs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p,
@@ -129,6 +131,8 @@ ABI = {
 # fin_run (include/finito_b200.h): merged k-mer positions [first_kmer, first_kmer + len) of a read -> one unitig
 RUN_DTYPE = np.dtype([("first_kmer", np.uint32), ("len_rc", np.uint32), ("unitig", np.uint32), ("first_offset", np.uint32)])
 RUN_RC = 0x80000000
+NOALLOC_MAX_READS = 65536  # include/finito_b200.h FIN_NOALLOC_MAX_READS / _BASES
+NOALLOC_MAX_BASES = 16777216
 
 _lib = None
 
@@ -287,6 +291,15 @@ class FinimizerIndex:
         _check(lib().fin_search_device(self._h, d_seqs, d_offsets, n_reads, n_bases, total_kmers, d_out, hit_bytes,
                                        C.byref(c), C.byref(ms)))
         return SearchCounts(c.found_fwd, c.found_rc, c.positive, c.n_queries), float(ms.value)
+
+    def search_device_noalloc(self, d_seqs: int, d_offsets: int, n_reads: int, n_bases: int, total_kmers: int, d_out: int,
+                              hit_bytes: int = 4):
+        """search_device through fin_search_device_noalloc: scratch in the library's fixed static device array, no
+        allocation; at most NOALLOC_MAX_READS reads / NOALLOC_MAX_BASES bases per call.  Returns SearchCounts."""
+        c = _Counts()
+        _check(lib().fin_search_device_noalloc(self._h, d_seqs, d_offsets, n_reads, n_bases, total_kmers, d_out, hit_bytes,
+                                               C.byref(c)))
+        return SearchCounts(c.found_fwd, c.found_rc, c.positive, c.n_queries)
 
     def set_counting(self, enabled: bool) -> None:
         _check(lib().fin_search_set_counting(self._h, int(enabled)))

@@ -122,6 +122,16 @@ fin_status fin_search_device(fin_index* index, const void* d_seqs, const uint64_
     });
 }
 
+fin_status fin_search_device_noalloc(fin_index* index, const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads,
+                                     uint64_t n_bases, uint64_t total_kmers, void* d_out, int hit_bytes,
+                                     fin_search_counts* counts) {
+    return guarded([&] {
+        require(index && d_read_offsets && (d_seqs || n_bases == 0) && (d_out || total_kmers == 0),
+                "fin_search_device_noalloc: null argument");
+        index->dev->search_device_noalloc(d_seqs, d_read_offsets, n_reads, n_bases, total_kmers, d_out, hit_bytes, counts);
+    });
+}
+
 fin_status fin_search_batch_runs(fin_index* index, const char* seqs, const uint64_t* read_offsets, uint64_t n_reads,
                                  uint64_t* run_offsets, fin_run* runs, uint64_t runs_capacity, uint64_t* n_runs,
                                  fin_search_counts* counts) {

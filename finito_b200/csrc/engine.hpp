@@ -83,6 +83,9 @@ class DeviceIndex {
     uint64_t search_device_runs(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases,
                                 uint64_t* d_run_offsets, fin_run* d_runs, uint64_t runs_capacity, fin_search_counts* counts,
                                 float* kernel_ms);
+    // search_device (dense hits) with every scratch array inside a fixed file-scope __device__ array: no allocation at all
+    void search_device_noalloc(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases,
+                               uint64_t total_kmers, void* d_out, int hit_bytes, fin_search_counts* counts);
     fin_access_counters last_access{};
     bool count_accesses = false;
     fin_search_timing last_timing{};

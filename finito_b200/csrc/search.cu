@@ -5,6 +5,8 @@
 #include <chrono>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <string>
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -417,6 +419,112 @@ uint64_t DeviceIndex::search_device_runs(const void* d_seqs, const uint64_t* d_r
     SearchTotals tot;
     finish_device_batch(t, counts, kernel_ms, tot);
     return n_runs;
+}
+
+// -------------------------------------------------------------------------------------------------------
+// device-resident batch without any allocation (include/finito_b200.h fin_search_device_noalloc)
+// -------------------------------------------------------------------------------------------------------
+// Everything search_device keeps in DevBufs (2-bit reads, output offsets, found mask, strand flags, totals) is carved out
+// of ONE file-scope device array of fixed size; the cub scan (whose temporary storage has no compile-time bound) is
+// replaced by a single-block scan.  Every GPU that loads the library holds the array (8 MiB) until the process exits.
+// All calls share it: it keeps the last call's contents (the totals are cleared here, the other parts are fully written
+// before they are read), and two calls that overlap on one GPU race.
+constexpr uint64_t kNoAllocMaxReads = FIN_NOALLOC_MAX_READS;
+constexpr uint64_t kNoAllocMaxBases = FIN_NOALLOC_MAX_BASES;
+constexpr size_t noalloc_round(size_t b) { return (b + 255) & ~(size_t)255; }
+constexpr size_t kNaTotals = 0;
+constexpr size_t kNaOutOffsets = kNaTotals + noalloc_round(sizeof(SearchTotals));
+constexpr size_t kNaStrandFlags = kNaOutOffsets + noalloc_round((kNoAllocMaxReads + 2) * 8);
+constexpr size_t kNaPacked = kNaStrandFlags + noalloc_round(kNoAllocMaxReads + 1);
+constexpr size_t kNaFmask = kNaPacked + noalloc_round((kNoAllocMaxBases / 32 + 2) * 8);
+constexpr size_t kNaEnd = kNaFmask + noalloc_round(((kNoAllocMaxBases >> 5) + kNoAllocMaxReads + 2) * 4);
+constexpr size_t kNoAllocScratchBytes = (size_t)8 << 20;
+static_assert(kNaEnd <= kNoAllocScratchBytes, "the scratch parts must fit the static array");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+// exclusive prefix sum of a[0..n) in place, one block: every thread owns a contiguous slice
+static __global__ void __launch_bounds__(1024) scan_offsets_block_kernel(uint64_t* __restrict__ a, uint32_t n) {
+    __shared__ uint64_t part[1024];
+    const uint32_t per = (n + blockDim.x - 1) / blockDim.x;
+    const uint32_t lo = min(n, threadIdx.x * per), hi = min(n, lo + per);
+    uint64_t sum = 0;
+    for (uint32_t i = lo; i < hi; i++) sum += a[i];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    for (uint32_t d = 1; d < blockDim.x; d <<= 1) {  // Hillis-Steele over the 1024 slice sums
+        const uint64_t add = threadIdx.x >= d ? part[threadIdx.x - d] : 0;
+        __syncthreads();
+        part[threadIdx.x] += add;
+        __syncthreads();
+    }
+    uint64_t run = part[threadIdx.x] - sum;
+    for (uint32_t i = lo; i < hi; i++) {
+        const uint64_t x = a[i];
+        a[i] = run;
+        run += x;
+    }
+}
+
+// device address of the array on `device` (current): the symbol's name is only a host-side stand-in, never a pointer
+// a kernel may be given.  Resolved once per device.
+static unsigned char* noalloc_scratch_on(int device) {
+    static std::mutex mu;
+    static unsigned char* ptr[64] = {nullptr};
+    if (device < 0 || device >= 64) throw arg_error("CUDA device ordinal out of range");
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr[device]) {
+        void* p = nullptr;
+        FIN_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p || ((uintptr_t)p & 255)) throw cuda_error("cudaGetSymbolAddress returned an unusable address for the static scratch");
+        ptr[device] = (unsigned char*)p;
+    }
+    return ptr[device];
+}
+
+void DeviceIndex::search_device_noalloc(const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads, uint64_t n_bases,
+                                        uint64_t total_kmers, void* d_out, int hit_bytes, fin_search_counts* counts) {
+    if (hit_bytes != 4 && hit_bytes != 8) throw arg_error("hit_bytes must be 4 or 8");
+    if (hit_bytes == 4 && !fits32_) throw limit_error("this index needs 64-bit hits");
+    if (n_reads > kNoAllocMaxReads || n_bases > kNoAllocMaxBases)
+        throw limit_error("fin_search_device_noalloc: at most " + std::to_string(kNoAllocMaxReads) + " reads and " +
+                          std::to_string(kNoAllocMaxBases) + " bases per call (the static scratch is fixed); got " +
+                          std::to_string(n_reads) + " reads, " + std::to_string(n_bases) + " bases");
+    FIN_CUDA(cudaSetDevice(device_));
+    unsigned char* base = noalloc_scratch_on(device_);
+    SearchTotals* d_totals = (SearchTotals*)(base + kNaTotals);
+    uint64_t* d_out_offsets = (uint64_t*)(base + kNaOutOffsets);
+    uint64_t* d_packed = (uint64_t*)(base + kNaPacked);
+    FIN_CUDA(cudaMemsetAsync(d_totals, 0, sizeof(SearchTotals), 0));
+    const uint64_t n_words = (n_bases + 31) / 32 + 1;
+    const unsigned threads = 256;
+    pack_reads_kernel<<<(unsigned)((n_words + threads - 1) / threads), threads, 0, 0>>>((const uint8_t*)d_seqs, n_bases, d_packed, n_words,
+                                                                                         d_totals);
+    kmer_counts_kernel<<<(unsigned)((n_reads + 1 + threads - 1) / threads), threads, 0, 0>>>(d_read_offsets, n_reads, n_bases, view_.k,
+                                                                                              d_out_offsets, d_totals);
+    scan_offsets_block_kernel<<<1, 1024, 0, 0>>>(d_out_offsets, (uint32_t)(n_reads + 1));
+    g_launches += 3;
+    FIN_CUDA(cudaGetLastError());
+    uint64_t total = 0;
+    unsigned flags = 0;
+    FIN_CUDA(cudaMemcpyAsync(&total, d_out_offsets + n_reads, 8, cudaMemcpyDeviceToHost, 0));
+    FIN_CUDA(cudaMemcpyAsync(&flags, &d_totals->error_flags, 4, cudaMemcpyDeviceToHost, 0));
+    FIN_CUDA(cudaStreamSynchronize(0));
+    check_flags(flags & kErrBadOffsets);
+    if (total > total_kmers) throw arg_error("total_kmers (the capacity of d_out) is smaller than the number of k-mer positions of the batch");
+    PipelineOut po;
+    po.hit_bytes = hit_bytes;
+    po.d_hits = d_out;
+    po.d_fmask = (uint32_t*)(base + kNaFmask);
+    po.d_strand_flags = base + kNaStrandFlags;
+    launch_search(view_, d_packed, d_read_offsets, n_reads, d_out_offsets, po, d_totals, count_accesses, 2, 0);
+    SearchTotals tot;
+    FIN_CUDA(cudaMemcpy(&tot, d_totals, sizeof tot, cudaMemcpyDeviceToHost));
+    check_flags(tot.error_flags);
+    fin_search_counts c{};
+    last_access = fin_access_counters{};
+    accumulate(tot, c, last_access);
+    if (counts) *counts = c;
 }
 
 // -------------------------------------------------------------------------------------------------------

@@ -110,6 +110,23 @@ fin_status fin_search_device(fin_index* index, const void* d_seqs, const uint64_
                              uint64_t n_bases, uint64_t total_kmers, void* d_out, int hit_bytes,
                              fin_search_counts* counts, float* kernel_ms);
 
+/* fin_search_device for callers that cannot tolerate an allocation (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  This entry point has NO counterpart in the reference.
+ * Same arguments, same answers and same errors as fin_search_device, but the call
+ * issues no cudaMalloc / cudaFree / allocating library routine: every scratch array of the search (2-bit reads, output
+ * offsets, found mask, strand flags, accumulators) lives in ONE static __device__ array of 8 MiB inside the library,
+ * which every GPU that loads the library holds until the process exits.  Limits per call: n_reads <=
+ * FIN_NOALLOC_MAX_READS and n_bases <= FIN_NOALLOC_MAX_BASES, otherwise FIN_ERR_LIMIT and nothing is launched.
+ * All calls (all handles, all threads) on one GPU share the array: it keeps the last call's contents (the call clears
+ * what must start at zero) and calls that overlap on the same GPU race - serialise them.  Runs on the default stream
+ * and returns after the kernels have finished.  (The first call on a device resolves the array's device address with
+ * cudaGetSymbolAddress; a call with n_reads == 0 can serve as that set-up.) */
+#define FIN_NOALLOC_MAX_READS 65536ull
+#define FIN_NOALLOC_MAX_BASES 16777216ull
+fin_status fin_search_device_noalloc(fin_index* index, const void* d_seqs, const uint64_t* d_read_offsets, uint64_t n_reads,
+                                     uint64_t n_bases, uint64_t total_kmers, void* d_out, int hit_bytes,
+                                     fin_search_counts* counts);
+
 /* ---- run-length hits -----------------------------------------------------------------------------
  * 98 % of the found k-mers of a read come out of walk_in_unitigs (include/FinimizerIndex.hh:47-102): consecutive
  * k-mer positions at consecutive offsets of one unitig.  A run says that for one maximal stretch the search produced in
