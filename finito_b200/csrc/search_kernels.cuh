@@ -352,6 +352,9 @@ FIN_D void run_append(const RunSink& sink, const bool want, const uint64_t key, 
 #define FIN_PHASE_FENCE() __syncwarp()
 #endif
 
+#ifndef FIN_DQ_BK2
+#define FIN_DQ_BK2 1  // cache the entry below the back of the candidate window in a register (measured: profiles/r2_sweep_closed_form_shrink.log)
+#endif
 enum : int { ST_EXT = 0, ST_EXTK = 1, ST_POST = 2, ST_SHRINK = 3, ST_EMIT = 4, ST_IDLE = 5 };
 
 #ifndef FIN_SEARCH_THREADS
@@ -406,7 +409,7 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS, int G = 1> struct Chain {
     uint64_t tword = 0;
     int walk_j = 0;
     int run_len = 0;          // runs mode: length of the open run (it ends at the previous k-mer position)
-    uint64_t fr = 0, bk = 0;  // front and back of the candidate window, cached in registers
+    uint64_t fr = 0, bk = 0, bk2 = 0;  // front, back and the entry below the back of the candidate window, cached in registers
 
     FIN_D void begin_strand(const IndexView& ix) {
         start = kmer_start = 0;
@@ -550,15 +553,15 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
     // ---- B: both intervals stand for this character.  Decisions first (pure arithmetic), then every load of this
     //         phase and of the drops in one batch, so that the chain waits for memory once, not five times.
     const bool post = st == ST_POST;
+    bool shrink0 = false;  // the shrink loop of this character starts in this iteration
     const bool single = post && Ik.l == Ik.r;  // :167 rightmost unitig start among the singleton k-mer intervals
     const idx_t ucol = Ik.l;
     if (post) {
         emit = end - kmer_start + 1 == k;  // :170
         if (emit) set_drop_K(k - 1);       // :181, independent of the shrink below
-        if (I.l == I.r) {                  // :145-154 shrink to the shortest unique suffix
-            cur = cand_pack(end - start + 1, I.l, end);
-            start++;
-            set_drop_I(end - start + 1);
+        if (I.l == I.r) {                  // :145-154 shrink to the shortest unique suffix (closed form in phase F)
+            shrink0 = true;
+            set_drop_I(1);                 // the real new_len comes out of the two LCS bytes loaded below
             st = ST_SHRINK;
         } else {
             st = ST_EMIT;
@@ -606,6 +609,25 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
             if (pendK & kDropLeft) w_kl = __ldg(lw + lcs_word_index(kl));
             if (pendK & kDropRight) w_kr = __ldg(lw + lcs_word_index(kr));
         }
+        if (shrink0) {
+            // The reference's shrink loop (:146-154) drops one character at a time while the interval stays the single
+            // column l: new_len = L0-1, L0-2, ... and a drop leaves {l} alone exactly when LCS[l] < new_len and
+            // LCS[l+1] < new_len (LCS[0] = 0 and the pad behind the last column = 0 stand for the two bound checks).
+            // So the loop ends at new_len = min(L0 - 1, max(LCS[l], LCS[l+1])), its last candidate is one longer, and
+            // only that last drop moves the interval: one word step instead of one iteration per dropped character.
+            const int lcs_l = (int)((w_il >> (8u * (il & 7u))) & 0xFFu), lcs_r = (int)((w_ir >> (8u * (ir & 7u))) & 0xFFu);
+            const int L0 = end - start + 1;
+            const int nl = min(L0 - 1, max(lcs_l, lcs_r));
+            if (COUNT) rc.c_lcs += (unsigned)(L0 - 1 - nl) * ((il > 0 ? 1u : 0u) + (I.r < N - 1 ? 1u : 0u));  // the drops that left {l} alone
+            cur = cand_pack(nl + 1, I.l, end);
+            start = end - nl + 1;
+            lenI = nl;
+            if (nl <= 0) {  // :39-41
+                I.l = 0;
+                I.r = N - 1;
+                pendI = 0;
+            }
+        }
         if (single) {
             if (COUNT) rc.c_ustart++;
             if ((uw >> (ucol & 31)) & 1u) {
@@ -642,9 +664,15 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
         } else {
             // monotone window: drop the candidates that are larger than the new one, then append it.  Front and
             // back live in registers, so only a pop touches the slots.
+            // (the entry below the back is cached too: the usual single pop then ends without waiting for a slot load)
             while (dq_n > 0 && bk > cur) {
                 dq_n--;
+#if FIN_DQ_BK2
+                bk = bk2;
+                if (dq_n > 1) bk2 = dq[(dq_head + dq_n - 2) & (KCAP - 1)];
+#else
                 if (dq_n > 0) bk = dq[(dq_head + dq_n - 1) & (KCAP - 1)];
+#endif
             }
             // an empty ring restarts at slot 0: the live entries then stay in the first few slots instead of rotating
             // through all KCAP of them, which keeps the thread-local footprint (and its share of the L1) small
@@ -658,11 +686,12 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
                 if (dq_n == KCAP) {  // cannot happen for live entries; keeps memory safe out of domain
                     rc.err |= kErrWindowUnderflow;
                     dq_n--;
-                    bk = 0;
+                    bk = bk2 = 0;
                 }
             }
             dq[(dq_head + dq_n) & (KCAP - 1)] = cur;
             dq_n++;
+            bk2 = bk;
             bk = cur;
             if (dq_n == 1) fr = cur;
             st = ST_EMIT;
