@@ -491,6 +491,7 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
 
     // ---- A: extend both intervals with the current character (common.hh:114-143).  ST_EXTK = the finimizer
     //         interval is already extended, only the k-mer interval is being contracted and retried.
+    bool contrI = false, contrK = false;  // this iteration starts a contraction drop of I / of the k-mer interval
     if ((pendI | pendK) == 0 && st <= ST_EXTK) {
         if (fresh) {
             fetch_base(packed);
@@ -529,6 +530,7 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
                 st = ST_EMIT;
             } else {
                 set_drop_I(end - start);
+                contrI = true;
             }
         } else {
             if (both) I = JI;
@@ -540,6 +542,7 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
                 if (is_empty(JK)) {
                     kmer_start++;
                     set_drop_K(end - kmer_start);
+                    contrK = true;
                     st = ST_EXTK;
                 } else {
                     Ik = JK;
@@ -626,6 +629,45 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
                 I.l = 0;
                 I.r = N - 1;
                 pendI = 0;
+            }
+        }
+        // The contraction loops (:116-126, :136-140) drop one character and retry the extension.  A drop that leaves the
+        // interval [l, r] as it is (LCS[l] and LCS[r+1] both below new_len) leads to the same empty extension, so the
+        // reference just goes on to the next shorter length: jump straight to the first length that moves the interval,
+        // new_len = min(new_len, max(LCS[l], LCS[r+1])) (typically ~18 of the ~19 contractions of a k-mer interval
+        // after a read error).
+        if (contrI && pendI) {
+            const int lcs_l = (int)((w_il >> (8u * (il & 7u))) & 0xFFu), lcs_r = (int)((w_ir >> (8u * (ir & 7u))) & 0xFFu);
+            const int nl = min(lenI, max(lcs_l, lcs_r));
+            const int skipped = lenI - nl;
+            if (COUNT) {
+                rc.c_lcs += (unsigned)skipped * ((il > 0 ? 1u : 0u) + (I.r < N - 1 ? 1u : 0u));
+                rc.c_rank += 2u * (unsigned)skipped;
+            }
+            start += skipped;
+            kmer_start = start;
+            lenI = nl;
+            if (nl <= 0) {
+                I.l = 0;
+                I.r = N - 1;
+                pendI = 0;
+            }
+        }
+        if (contrK && pendK) {
+            const int lcs_l = (int)((w_kl >> (8u * (kl & 7u))) & 0xFFu), lcs_r = (int)((w_kr >> (8u * (kr & 7u))) & 0xFFu);
+            // never past the finimizer interval's own length (in the parity domain the k-mer interval has moved by then)
+            const int nl = max(min(lenK, max(lcs_l, lcs_r)), min(lenK, end - start));
+            const int skipped = lenK - nl;
+            if (COUNT) {
+                rc.c_lcs += (unsigned)skipped * ((kl > 0 ? 1u : 0u) + (Ik.r < N - 1 ? 1u : 0u));
+                rc.c_rank += 2u * (unsigned)skipped;
+            }
+            kmer_start += skipped;
+            lenK = nl;
+            if (nl <= 0) {
+                Ik.l = 0;
+                Ik.r = N - 1;
+                pendK = 0;
             }
         }
         if (single) {
