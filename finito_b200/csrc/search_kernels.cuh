@@ -392,6 +392,7 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS, int G = 1> struct Chain {
     unsigned sflags = 0;         // strands of this read that are streamed (strand prefilter)
     // stream state (common.hh:80-103)
     int st = ST_IDLE, end = 0, c = 0;
+    uint32_t rword = 0;  // the 16 bases of the read around `end`
     int start = 0, kmer_start = 0;
     Ival I{0, 0}, Ik{0, 0};
     unsigned pendI = 0, pendK = 0;  // sides of the pending drops
@@ -428,8 +429,10 @@ template <int KCAP, class HitT, bool COUNT, bool RUNS, int G = 1> struct Chain {
     // 2-bit code of the character at `end` of the current strand (reverse complement: read backwards, complemented)
     FIN_D void fetch_base(const uint64_t* __restrict__ packed) {
         const uint64_t b = b0 + (uint64_t)(strand ? len - 1 - end : end);
-        const uint32_t w = __ldg(reinterpret_cast<const uint32_t*>(packed) + (b >> 4));
-        c = (int)((w >> (2 * (b & 15))) & 3u) ^ (strand ? 3 : 0);
+        // the 16-base word of the read stays in a register: one load per 16 characters, and the character (which the
+        // rank row addresses wait for) is there without a load in between
+        if (end == 0 || ((uint32_t)b & 15u) == (strand ? 15u : 0u)) rword = __ldg(reinterpret_cast<const uint32_t*>(packed) + (b >> 4));
+        c = (int)((rword >> (2 * (b & 15))) & 3u) ^ (strand ? 3 : 0);
     }
 
     // takes a new read; returns false (and stays idle) when the read has no k-mer
