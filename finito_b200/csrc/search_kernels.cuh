@@ -198,6 +198,33 @@ enum : unsigned { kDropLeft = 1u, kDropRight = 2u };
 // u64 index of the aligned 8-byte LCS word of column p inside the lines array (< n_nodes / 4: fits 32 bits)
 FIN_D uint32_t lcs_word_index(const idx_t p) { return ((p >> 6) << 4) | 8u | ((p >> 3) & 7u); }
 
+// 8 LCS bytes around column p, aligned to FOUR bytes inside the LCS half of p's line (two 4-byte loads): a left scan then
+// always has 5..8 columns at and below p in its window, a right scan 5..8 at and above p (fewer only in the first / last
+// four columns of a line), where the aligned 8-byte word leaves 1..8.  Returns the first column of the window (mod 64).
+FIN_D uint32_t lcs_win_left_start(const idx_t p) {
+    const uint32_t lo = p & 63u;
+    return lo >= 4u ? ((lo - 4u) & ~3u) : 0u;
+}
+FIN_D uint32_t lcs_win_right_start(const idx_t p) {
+    const uint32_t lo = (p & 63u) & ~3u;
+    return lo < 56u ? lo : 56u;
+}
+FIN_D uint64_t lcs_win_load(const uint32_t* __restrict__ l32, const idx_t p, const uint32_t start) {
+    const uint32_t idx = ((p >> 6) << 5) | 16u | (start >> 2);  // 32 u32 per line, the LCS bytes are its second half
+    return (uint64_t)__ldg(l32 + idx) | ((uint64_t)__ldg(l32 + idx + 1u) << 32);
+}
+// word steps on a window: j = byte of the window that holds LCS[l] (left) / LCS[r + 1] (right)
+template <bool WIDE> FIN_D idx_t drop_left_window(const uint64_t w, const idx_t l, const uint32_t j, const int new_len, bool& found) {
+    const uint64_t stop = bytes_below<WIDE>(w, new_len) << (8u * (7u - j));
+    found = stop != 0;
+    return found ? l - (idx_t)(__clzll((long long)stop) >> 3) : l - j - 1u;
+}
+template <bool WIDE> FIN_D idx_t drop_right_window(const uint64_t w, const idx_t r, const uint32_t j, const int new_len, bool& found) {
+    const uint64_t stop = bytes_below<WIDE>(w, new_len) >> (8u * j);
+    found = stop != 0;
+    return found ? r + (idx_t)((__ffsll((long long)stop) - 1) >> 3) : r + (8u - j);
+}
+
 // Left end: w = the LCS word of column l.  Returns the new l; found = the scan stopped inside this word.
 template <bool WIDE> FIN_D idx_t drop_left_word(const uint64_t w, const idx_t l, const int new_len, bool& found) {
     const uint32_t j = l & 7u;
@@ -352,6 +379,9 @@ FIN_D void run_append(const RunSink& sink, const bool want, const uint64_t key, 
 #define FIN_PHASE_FENCE() __syncwarp()
 #endif
 
+#ifndef FIN_LCS_WIN4
+#define FIN_LCS_WIN4 1  // 4-byte aligned LCS windows for the word steps of the search (profiles/r2_sweep_closed_form_shrink.log)
+#endif
 #ifndef FIN_DQ_BK2
 #define FIN_DQ_BK2 1  // cache the entry below the back of the candidate window in a register (measured: profiles/r2_sweep_closed_form_shrink.log)
 #endif
@@ -590,6 +620,7 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
         const idx_t il = I.l, ir = I.r + 1, kl = Ik.l, kr = Ik.r + 1;
         uint32_t uw = 0;
         uint64_t w_il = 0, w_ir = 0, w_kl = 0, w_kr = 0;
+        uint32_t j_il = il & 7u, j_ir = ir & 7u, j_kl = kl & 7u, j_kr = kr & 7u;  // byte of LCS[il] .. LCS[kr] in its word / window
 #if defined(__CUDACC__) && !defined(FIN_EMU)
         if (G > 1) {  // the five loads of the phase dealt out over the lanes of the group
             const int sub = (int)coop_sub<G>();
@@ -610,10 +641,21 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
 #endif
         {
             if (single) uw = __ldg(l32 + (((ucol >> 6) << 5) | ((ucol >> 3) & 4u) | 3u));
+#if FIN_LCS_WIN4
+            const uint32_t a_il = lcs_win_left_start(il), a_ir = lcs_win_right_start(ir);
+            j_il = (il & 63u) - a_il; j_ir = (ir & 63u) - a_ir;
+            if (pendI & kDropLeft) w_il = lcs_win_load(l32, il, a_il);
+            if (pendI & kDropRight) w_ir = lcs_win_load(l32, ir, a_ir);
+            const uint32_t a_kl = lcs_win_left_start(kl), a_kr = lcs_win_right_start(kr);
+            j_kl = (kl & 63u) - a_kl; j_kr = (kr & 63u) - a_kr;
+            if (pendK & kDropLeft) w_kl = lcs_win_load(l32, kl, a_kl);
+            if (pendK & kDropRight) w_kr = lcs_win_load(l32, kr, a_kr);
+#else
             if (pendI & kDropLeft) w_il = __ldg(lw + lcs_word_index(il));
             if (pendI & kDropRight) w_ir = __ldg(lw + lcs_word_index(ir));
             if (pendK & kDropLeft) w_kl = __ldg(lw + lcs_word_index(kl));
             if (pendK & kDropRight) w_kr = __ldg(lw + lcs_word_index(kr));
+#endif
         }
         if (shrink0) {
             // The reference's shrink loop (:146-154) drops one character at a time while the interval stays the single
@@ -621,7 +663,7 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
             // LCS[l+1] < new_len (LCS[0] = 0 and the pad behind the last column = 0 stand for the two bound checks).
             // So the loop ends at new_len = min(L0 - 1, max(LCS[l], LCS[l+1])), its last candidate is one longer, and
             // only that last drop moves the interval: one word step instead of one iteration per dropped character.
-            const int lcs_l = (int)((w_il >> (8u * (il & 7u))) & 0xFFu), lcs_r = (int)((w_ir >> (8u * (ir & 7u))) & 0xFFu);
+            const int lcs_l = (int)((w_il >> (8u * j_il)) & 0xFFu), lcs_r = (int)((w_ir >> (8u * j_ir)) & 0xFFu);
             const int L0 = end - start + 1;
             const int nl = min(L0 - 1, max(lcs_l, lcs_r));
             if (COUNT) rc.c_lcs += (unsigned)(L0 - 1 - nl) * ((il > 0 ? 1u : 0u) + (I.r < N - 1 ? 1u : 0u));  // the drops that left {l} alone
@@ -640,7 +682,7 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
         // new_len = min(new_len, max(LCS[l], LCS[r+1])) (typically ~18 of the ~19 contractions of a k-mer interval
         // after a read error).
         if (contrI && pendI) {
-            const int lcs_l = (int)((w_il >> (8u * (il & 7u))) & 0xFFu), lcs_r = (int)((w_ir >> (8u * (ir & 7u))) & 0xFFu);
+            const int lcs_l = (int)((w_il >> (8u * j_il)) & 0xFFu), lcs_r = (int)((w_ir >> (8u * j_ir)) & 0xFFu);
             const int nl = min(lenI, max(lcs_l, lcs_r));
             const int skipped = lenI - nl;
             if (COUNT) {
@@ -657,7 +699,7 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
             }
         }
         if (contrK && pendK) {
-            const int lcs_l = (int)((w_kl >> (8u * (kl & 7u))) & 0xFFu), lcs_r = (int)((w_kr >> (8u * (kr & 7u))) & 0xFFu);
+            const int lcs_l = (int)((w_kl >> (8u * j_kl)) & 0xFFu), lcs_r = (int)((w_kr >> (8u * j_kr)) & 0xFFu);
             // never past the finimizer interval's own length (in the parity domain the k-mer interval has moved by then)
             const int nl = max(min(lenK, max(lcs_l, lcs_r)), min(lenK, end - start));
             const int skipped = lenK - nl;
@@ -682,8 +724,8 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
         }
         // all four word steps computed by every lane, committed by select: no divergent regions in this phase
         bool f_il, f_ir, f_kl, f_kr;
-        const idx_t n_il = drop_left_word<WIDE>(w_il, I.l, lenI, f_il), n_ir = drop_right_word<WIDE>(w_ir, I.r, lenI, f_ir);
-        const idx_t n_kl = drop_left_word<WIDE>(w_kl, Ik.l, lenK, f_kl), n_kr = drop_right_word<WIDE>(w_kr, Ik.r, lenK, f_kr);
+        const idx_t n_il = drop_left_window<WIDE>(w_il, I.l, j_il, lenI, f_il), n_ir = drop_right_window<WIDE>(w_ir, I.r, j_ir, lenI, f_ir);
+        const idx_t n_kl = drop_left_window<WIDE>(w_kl, Ik.l, j_kl, lenK, f_kl), n_kr = drop_right_window<WIDE>(w_kr, Ik.r, j_kr, lenK, f_kr);
         const bool d_il = pendI & kDropLeft, d_ir = pendI & kDropRight, d_kl = pendK & kDropLeft, d_kr = pendK & kDropRight;
         if (COUNT) {
             if (d_il) rc.c_lcs += (I.l - n_il) + (f_il && n_il > 0 ? 1u : 0u);
