@@ -42,7 +42,7 @@ class _Counts(C.Structure):
 class _Access(C.Structure):
     _fields_ = [(n, C.c_int64) for n in
                 ("n_rank", "n_lcs_reads", "n_ustart_reads", "n_anchor", "n_anchor_branch", "n_walk_words", "n_bases",
-                 "n_kmers", "n_filter_lookups")]
+                 "n_kmers", "n_filter_lookups", "n_lcs_skipped", "n_rank_skipped")]
 
 
 class _Timing(C.Structure):

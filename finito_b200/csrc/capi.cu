@@ -48,7 +48,7 @@ extern "C" {
 
 const char* fin_last_error(void) { return g_error.c_str(); }
 
-int fin_abi_version(void) { return 2; }
+int fin_abi_version(void) { return 3; }
 
 int fin_device_count(void) {
     int n = 0;

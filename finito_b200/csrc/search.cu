@@ -311,6 +311,8 @@ static void accumulate(const SearchTotals& t, fin_search_counts& c, fin_access_c
     a.n_bases += (int64_t)t.n_bases;
     a.n_kmers += (int64_t)t.n_kmers;
     a.n_filter_lookups += (int64_t)t.n_filter;
+    a.n_lcs_skipped += (int64_t)t.n_skip_lcs;
+    a.n_rank_skipped += (int64_t)t.n_skip_rank;
 }
 
 // -------------------------------------------------------------------------------------------------------

@@ -22,6 +22,9 @@ struct SearchTotals {  // device-side accumulators of one launch
     unsigned long long next_read;  // work counter of the persistent search kernel
     unsigned long long n_runs;     // runs mode: records appended (RunSink::count)
     unsigned long long n_filter;   // s-mer table lookups of the strand prefilter (counting mode only)
+    // of n_lcs_reads / n_rank (the reference's tally): accesses of drops and retried extensions that the closed forms of
+    // the shrink and contraction loops never issue (counting mode only)
+    unsigned long long n_skip_lcs, n_skip_rank;
 };
 
 enum : unsigned { kErrBadBase = 1u, kErrWindowUnderflow = 2u, kErrLookupRange = 4u, kErrReadTooLong = 8u, kErrBadOffsets = 16u };
@@ -29,6 +32,7 @@ enum : unsigned { kErrBadBase = 1u, kErrWindowUnderflow = 2u, kErrLookupRange = 
 struct ReadCounters {  // per-thread tallies, reduced per warp at the end of the kernel
     unsigned found[2] = {0, 0}, positive = 0, n_q = 0, err = 0;
     unsigned c_rank = 0, c_lcs = 0, c_ustart = 0, c_anchor = 0, c_branch = 0, c_walk = 0, c_bases = 0, c_kmers = 0;
+    unsigned c_skip_lcs = 0, c_skip_rank = 0;  // part of c_lcs / c_rank that the closed forms skip
 };
 
 #ifdef __CUDACC__
@@ -666,7 +670,11 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
             const int lcs_l = (int)((w_il >> (8u * j_il)) & 0xFFu), lcs_r = (int)((w_ir >> (8u * j_ir)) & 0xFFu);
             const int L0 = end - start + 1;
             const int nl = min(L0 - 1, max(lcs_l, lcs_r));
-            if (COUNT) rc.c_lcs += (unsigned)(L0 - 1 - nl) * ((il > 0 ? 1u : 0u) + (I.r < N - 1 ? 1u : 0u));  // the drops that left {l} alone
+            if (COUNT) {  // the drops that left {l} alone
+                const unsigned n = (unsigned)(L0 - 1 - nl) * ((il > 0 ? 1u : 0u) + (I.r < N - 1 ? 1u : 0u));
+                rc.c_lcs += n;
+                rc.c_skip_lcs += n;
+            }
             cur = cand_pack(nl + 1, I.l, end);
             start = end - nl + 1;
             lenI = nl;
@@ -686,8 +694,11 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
             const int nl = min(lenI, max(lcs_l, lcs_r));
             const int skipped = lenI - nl;
             if (COUNT) {
-                rc.c_lcs += (unsigned)skipped * ((il > 0 ? 1u : 0u) + (I.r < N - 1 ? 1u : 0u));
+                const unsigned n = (unsigned)skipped * ((il > 0 ? 1u : 0u) + (I.r < N - 1 ? 1u : 0u));
+                rc.c_lcs += n;
+                rc.c_skip_lcs += n;
                 rc.c_rank += 2u * (unsigned)skipped;
+                rc.c_skip_rank += 2u * (unsigned)skipped;
             }
             start += skipped;
             kmer_start = start;
@@ -704,8 +715,11 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
             const int nl = max(min(lenK, max(lcs_l, lcs_r)), min(lenK, end - start));
             const int skipped = lenK - nl;
             if (COUNT) {
-                rc.c_lcs += (unsigned)skipped * ((kl > 0 ? 1u : 0u) + (Ik.r < N - 1 ? 1u : 0u));
+                const unsigned n = (unsigned)skipped * ((kl > 0 ? 1u : 0u) + (Ik.r < N - 1 ? 1u : 0u));
+                rc.c_lcs += n;
+                rc.c_skip_lcs += n;
                 rc.c_rank += 2u * (unsigned)skipped;
+                rc.c_skip_rank += 2u * (unsigned)skipped;
             }
             kmer_start += skipped;
             lenK = nl;
@@ -1009,6 +1023,14 @@ __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) sea
 #pragma unroll
             for (int s = 16; s > 0; s >>= 1) v += __shfl_down_sync(full, v, s);
             if (lane == 0 && v) atomicAdd(dst + i, v);
+        }
+        unsigned long long sk[2] = {rc.c_skip_lcs, rc.c_skip_rank};
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+            unsigned long long v = sk[i];
+#pragma unroll
+            for (int s = 16; s > 0; s >>= 1) v += __shfl_down_sync(full, v, s);
+            if (lane == 0 && v) atomicAdd(&totals->n_skip_lcs + i, v);
         }
     }
 }

@@ -169,6 +169,9 @@ fin_status fin_expand_runs(const uint64_t* read_offsets, uint64_t n_reads, int64
 typedef struct fin_access_counters {
     int64_t n_rank, n_lcs_reads, n_ustart_reads, n_anchor, n_anchor_branch, n_walk_words, n_bases, n_kmers;
     int64_t n_filter_lookups; /* s-mer table lookups of the strand prefilter (not part of the reference's algorithm) */
+    /* n_rank and n_lcs_reads tally what the REFERENCE's loops access.  These two say how many of them this library never
+     * issues: the shrink loop and the contraction loops are evaluated in closed form (one drop instead of one per character). */
+    int64_t n_lcs_skipped, n_rank_skipped;
 } fin_access_counters;
 fin_status fin_search_access_counters(const fin_index* index, fin_access_counters* out);
 fin_status fin_search_set_counting(fin_index* index, int enabled);

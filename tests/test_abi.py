@@ -25,7 +25,7 @@ def test_library_exports_every_symbol():
     lib = fb.lib()
     for name in header_functions():
         assert hasattr(lib, name), name
-    assert lib.fin_abi_version() == 2
+    assert lib.fin_abi_version() == 3
 
 
 def test_count_kmers_is_host_arithmetic():

@@ -132,6 +132,28 @@ def test_long_queries_unitigs_against_themselves(synthetic, gpu_lib):
     assert c.positive == c.n_queries == pos
 
 
+def test_access_counters_equal_the_oracles_tally(synthetic, gpu_lib, monkeypatch):
+    """Counting variant, strand prefilter off: the kernel tallies exactly the ranks / LCS values / Ustart bits / anchors / walk
+    words the reference's loops touch, and says how many of them its closed forms never issue."""
+    fb = gpu_lib
+    ds, prefix = synthetic
+    seqs, offs = ds["reads"]
+    n = 3000
+    sub, so = seqs[: int(offs[n])], offs[: n + 1]
+    orc = H.Oracle(prefix)
+    want, _ = orc.search_reads(sub, so)
+    oc = orc.counters()
+    monkeypatch.setenv("FIN_NO_PREFILTER", "1")  # read when the index is loaded
+    with fb.FinimizerIndex.load(prefix) as ix:
+        ix.set_counting(True)
+        got, _ = ix.search_batch((sub, so))
+        acc = ix.access_counters()
+    assert np.array_equal(got, want)
+    for name in H.COUNTER_NAMES[:8]:
+        assert acc[name] == oc[name], name
+    assert 0 < acc["n_lcs_skipped"] < acc["n_lcs_reads"] and 0 < acc["n_rank_skipped"] < acc["n_rank"]
+
+
 def test_device_resident_entry_point(synthetic, gpu_lib):
     import torch
 
