@@ -124,3 +124,29 @@ def test_stats_mode_bodies_match_oracle_on_synthetic(k, genome_len, t, tmp_path)
     for typ in ("shortest", "verify"):
         want = H.oracle_build(ds["sbwt"], ds["unitigs"], str(tmp_path / f"orc_{typ}"), type=typ, t=t)
         assert H.emu_stats(ds["sbwt"], ds["unitigs"], typ, t) == want, typ
+
+
+@pytest.mark.parametrize("k", [3, 5, 9, 17, 32, 33, 64])
+@pytest.mark.parametrize("seed,genome_len,error", [(1, 300, 0.05), (2, 1200, 0.2), (3, 4000, 0.02), (4, 700, 0.5)])
+def test_closed_forms_on_tiny_repetitive_inputs(k, seed, genome_len, error, tmp_path):
+    """The closed forms of the shrink and contraction loops against the oracle's character-by-character loops where they are
+    stressed most: tiny genomes made of repeats (LCS values at both extremes, intervals that widen to the whole range, new_len
+    reaching 0) and reads with up to 50 % errors (a contraction at almost every character); answers, the four counters and
+    the reference's access tally must agree, dense and as runs."""
+    if genome_len < 4 * k:
+        genome_len = 4 * k + 50
+    ds = make_dataset("tiny", genome_len=genome_len, k=k, n_reads=60, read_len=max(k + 5, 90), seed=100 * k + seed, error=error,
+                      families=3, copies=4, rep_len=max(2 * k, genome_len // 6), divergence=0.03)
+    prefix = str(tmp_path / "orc")
+    H.oracle_build(ds["sbwt"], ds["unitigs"], prefix)
+    seqs, offs = ds["reads"]
+    orc = H.Oracle(prefix)
+    want, wc = orc.search_reads(seqs, offs)
+    oc = orc.counters()
+    got, gc, acc, flags = H.emu_search(prefix, seqs, offs)
+    assert flags == 0 and np.array_equal(got, want) and np.array_equal(gc, wc)
+    for name in ("n_rank", "n_lcs_reads", "n_ustart_reads", "n_anchor", "n_anchor_branch", "n_walk_words"):
+        assert acc[name] == oc[name], name
+    got_r, gc_r, _, flags_r = H.emu_search(prefix, seqs, offs, runs=True, prefilter_s=min(k, 4))
+    assert flags_r == 0 and np.array_equal(got_r, want) and np.array_equal(gc_r, wc)
+    assert 0 < wc[2] < wc[3] or error >= 0.2  # some k-mers found, some not
