@@ -149,4 +149,4 @@ def test_closed_forms_on_tiny_repetitive_inputs(k, seed, genome_len, error, tmp_
         assert acc[name] == oc[name], name
     got_r, gc_r, _, flags_r = H.emu_search(prefix, seqs, offs, runs=True, prefilter_s=min(k, 4))
     assert flags_r == 0 and np.array_equal(got_r, want) and np.array_equal(gc_r, wc)
-    assert 0 < wc[2] < wc[3] or error >= 0.2  # some k-mers found, some not
+    assert wc[2] > 0 or error >= 0.2  # the reads do hit the index
