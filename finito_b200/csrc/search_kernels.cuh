@@ -951,7 +951,10 @@ FIN_D void Chain<KCAP, HitT, COUNT, RUNS, G>::step(const IndexView& ix, const ui
 // Persistent warps: a lane that finishes its read takes the next one from a global counter (one atomic per
 // group of lanes that run dry in the same iteration), so no lane idles while reads remain.
 #ifndef FIN_SEARCH_MIN_BLOCKS
-#define FIN_SEARCH_MIN_BLOCKS 8  // 64 registers; 10 and 12 blocks spill and lose 4-30 % (profiles/r1_sweep_occupancy.log)
+// 7 resident blocks = 72 registers and no spills.  8 blocks (64 registers) were the optimum until the closed forms and the LCS
+// windows added state: with 56-68 bytes of spills they now lose 4-9 % (profiles/r2c_sweep_resident_blocks.log); 9-12 blocks lose
+// 4-30 % (profiles/r2_sweep_occupancy.log), 6 blocks gain nothing over 7.
+#define FIN_SEARCH_MIN_BLOCKS 7
 #endif
 template <int KCAP, class HitT, bool COUNT, bool RUNS, int G = 1>
 __global__ void __launch_bounds__(FIN_SEARCH_THREADS, FIN_SEARCH_MIN_BLOCKS) search_reads_kernel(const IndexView ix, const uint64_t* __restrict__ packed,
